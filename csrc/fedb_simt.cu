@@ -1,0 +1,780 @@
+// fedb200 SIMT fp32 kernels: the shape-generic, bit-reproducible implementation of every hot
+// step of a federated round.  One lane per data row (32-row tiles), activations feature-major
+// in shared memory, weights read warp-uniformly through L1 (they are small and shared by all
+// tiles of a client).  These kernels are (a) the numerics oracle for the tcgen05 kernels,
+// (b) the path for shapes the tensor-core kernels do not cover, and (c) what the sklearn-mode
+// trainer (minibatch 200) and the grid search run on.
+//
+// Reference behaviour being provided (see include/fedb200.h for the citation tags):
+//   k_fwd_bwd     C:68-71 (forward, CrossEntropyLoss, backward); SK:301-393 (_backprop)
+//   k_reduce_opt  C:72-73 (Adam.step, StepLR.step); SKO Adam/SGD updates; SK:235 L2
+//   k_eval        C:75-83, S:104 (predict) ; counts replace the sklearn metric calls C:85-90
+//   k_fedavg      C:101-120, S:108-122, H:24-46 (aggregation) + C:165-192 (global metrics,
+//                 early stop)
+#include "common.cuh"
+
+namespace fedb {
+
+thread_local char g_err[512] = "";
+
+constexpr int LDS = FEDB_TILE_ROWS + 1;  // 33: feature-major rows, conflict-free both ways
+constexpr int NTHREADS = 256;
+
+struct SmemPlan {
+  int a_off[FEDB_MAX_LAYERS + 1];  // float offsets of activation buffers a[0..L]
+  int dz_off[2];
+  int misc_off;
+  int total_floats;
+};
+
+__host__ __device__ inline SmemPlan smem_plan(const int32_t* dims, int L) {
+  SmemPlan p;
+  int off = 0, maxw = 4;
+  for (int l = 0; l <= FEDB_MAX_LAYERS; ++l) {
+    p.a_off[l] = off;
+    if (l <= L) {
+      off += ru4(dims[l]) * LDS;
+      if (l >= 1 && ru4(dims[l]) > maxw) maxw = ru4(dims[l]);
+    }
+  }
+  p.dz_off[0] = off; off += maxw * LDS;
+  p.dz_off[1] = off; off += maxw * LDS;
+  p.misc_off = off; off += 64;
+  p.total_floats = off;
+  return p;
+}
+
+// ---------------------------------------------------------------------------------------
+// device building blocks
+// ---------------------------------------------------------------------------------------
+
+// z[j][r] = act(b[j] + sum_k a_in[k][r] * W[j][k]);  W row-major [d_out][ld], pad cols zero.
+// Rows j in [d_out, ru4(d_out)) of a_out are written as 0 (they are the next layer's K pad).
+__device__ void layer_forward(const float* __restrict__ W, const float* __restrict__ b, int ld, int d_out,
+                              const float* a_in, float* a_out, int act, bool apply_act) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int njb = (d_out + 3) >> 2;
+  for (int jb = warp; jb < njb; jb += nwarps) {
+    const int j0 = jb * 4;
+    const float* w[4];
+    float acc[4];
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      int j = min(j0 + jj, d_out - 1);
+      w[jj] = W + (size_t)j * ld;
+      acc[jj] = __ldg(b + j);
+    }
+#pragma unroll 2
+    for (int k = 0; k < ld; k += 4) {
+      const float a0 = a_in[(k + 0) * LDS + lane], a1 = a_in[(k + 1) * LDS + lane];
+      const float a2 = a_in[(k + 2) * LDS + lane], a3 = a_in[(k + 3) * LDS + lane];
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(w[jj] + k));
+        acc[jj] = fmaf(a0, q.x, acc[jj]);
+        acc[jj] = fmaf(a1, q.y, acc[jj]);
+        acc[jj] = fmaf(a2, q.z, acc[jj]);
+        acc[jj] = fmaf(a3, q.w, acc[jj]);
+      }
+    }
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = j0 + jj;
+      float v = 0.f;
+      if (j < d_out) v = apply_act ? act_fwd(acc[jj], act) : acc[jj];
+      a_out[j * LDS + lane] = v;
+    }
+  }
+}
+
+// dW[j][k] = sum_r dz[j][r] a[k][r]  (tile partial), db[j] = sum_r dz[j][r]
+__device__ void layer_wgrad(const float* dz, const float* a, int d_in_ld, int d_out, float* __restrict__ gW,
+                            float* __restrict__ gb) {
+  const int njb = (d_out + 3) >> 2, nkb = d_in_ld >> 2;
+  for (int blk = threadIdx.x; blk < njb * nkb; blk += blockDim.x) {
+    const int jb = blk / nkb, kb = blk - jb * nkb;
+    const int j0 = jb * 4, k0 = kb * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+    for (int r = 0; r < FEDB_TILE_ROWS; ++r) {
+      float d[4], x[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        d[i] = dz[(j0 + i) * LDS + r];
+        x[i] = a[(k0 + i) * LDS + r];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(d[i], x[j], acc[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (j0 + i < d_out)
+        *reinterpret_cast<float4*>(gW + (size_t)(j0 + i) * d_in_ld + k0) =
+            make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  }
+  for (int j = threadIdx.x; j < ru4(d_out); j += blockDim.x) {
+    float s = 0.f;
+    if (j < d_out) {
+#pragma unroll 8
+      for (int r = 0; r < FEDB_TILE_ROWS; ++r) s += dz[j * LDS + r];
+    }
+    gb[j] = s;
+  }
+}
+
+// dz_prev[k][r] = act'(a_l[k][r]) * sum_j dz[j][r] W[j][k]
+__device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d_out, const float* dz,
+                            const float* a_l, float* dz_prev, int act) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int nkb = ld >> 2;
+  for (int kb = warp; kb < nkb; kb += nwarps) {
+    const int k0 = kb * 4;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int j = 0; j < d_out; ++j) {
+      const float d = dz[j * LDS + lane];
+      const float4 q = __ldg(reinterpret_cast<const float4*>(W + (size_t)j * ld + k0));
+      acc[0] = fmaf(d, q.x, acc[0]);
+      acc[1] = fmaf(d, q.y, acc[1]);
+      acc[2] = fmaf(d, q.z, acc[2]);
+      acc[3] = fmaf(d, q.w, acc[3]);
+    }
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      const int k = k0 + kk;
+      const float av = a_l[k * LDS + lane];
+      dz_prev[k * LDS + lane] = (k < d_in) ? acc[kk] * act_bwd(av, act) : 0.f;
+    }
+  }
+}
+
+// Loads the tile's rows, feature-major, into a0; labels into ylab. Rows >= nvalid replicate
+// the last valid row (finite values; their dz is forced to 0 later).
+__device__ void load_tile(const float* __restrict__ X, int ldx, const int32_t* __restrict__ y,
+                          const int32_t* __restrict__ idx, int64_t base, int nvalid, int ld0, float* a0,
+                          int* ylab) {
+  const int q4 = ld0 >> 2;
+  for (int e = threadIdx.x; e < FEDB_TILE_ROWS * q4; e += blockDim.x) {
+    const int r = e / q4, q = e - r * q4;
+    const int row = __ldg(idx + base + min(r, nvalid - 1));
+    const float4 v = __ldg(reinterpret_cast<const float4*>(X + (size_t)row * ldx) + q);
+    a0[(4 * q + 0) * LDS + r] = v.x;
+    a0[(4 * q + 1) * LDS + r] = v.y;
+    a0[(4 * q + 2) * LDS + r] = v.z;
+    a0[(4 * q + 3) * LDS + r] = v.w;
+  }
+  if (threadIdx.x < FEDB_TILE_ROWS) {
+    const int row = __ldg(idx + base + min((int)threadIdx.x, nvalid - 1));
+    ylab[threadIdx.x] = __ldg(y + row);
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------
+// K4: init
+// ---------------------------------------------------------------------------------------
+__global__ void k_init(const FedbGroup* __restrict__ groups, float* __restrict__ params,
+                       const int32_t* __restrict__ streams, int kind, uint32_t k0, uint32_t k1) {
+  const FedbGroup& G = groups[blockIdx.y];
+  const int sid = streams[blockIdx.y];
+  if (sid < 0) return;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q * 4 >= G.slab_size) return;
+  const SlabLayout lay = slab_layout(G.dims, G.n_layers);
+  uint32_t c[4] = {(uint32_t)q, (uint32_t)sid, 0u, 0u};
+  philox4x32(c, k0, k1);
+  float out[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int e = q * 4 + i;
+    float bound = 0.f;
+    for (int l = 0; l < G.n_layers; ++l) {
+      const int fi = G.dims[l], fo = G.dims[l + 1];
+      float s;
+      if (kind == FEDB_INIT_TORCH_DEFAULT) s = (float)(1.0 / sqrt((double)fi));
+      else if (kind == FEDB_INIT_SKLEARN_GLOROT)
+        s = (float)sqrt((G.act == FEDB_ACT_LOGISTIC ? 2.0 : 6.0) / (double)(fi + fo));
+      else s = 0.f;
+      if (e >= lay.w_off[l] && e < lay.b_off[l]) {
+        const int col = (e - lay.w_off[l]) % lay.ld[l];
+        if (col < fi) bound = s;
+      } else if (e >= lay.b_off[l] && e < lay.b_off[l] + fo) {
+        bound = s;
+      }
+    }
+    const float u = (float)(c[i] >> 8) * 5.9604644775390625e-08f;  // 2^-24
+    out[i] = __fmul_rn(__fsub_rn(__fmul_rn(2.0f, u), 1.0f), bound);
+  }
+  *reinterpret_cast<float4*>(params + G.slab_off + (size_t)q * 4) = make_float4(out[0], out[1], out[2], out[3]);
+}
+
+// ---------------------------------------------------------------------------------------
+// round begin
+// ---------------------------------------------------------------------------------------
+__global__ void k_round_begin(const FedbFed* __restrict__ feds, FedbFedState* __restrict__ st, int n_feds,
+                              int32_t* __restrict__ conf, int n_conf) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_feds) {
+    if (st[i].stop_pending) st[i].stop = 1;
+    if (!st[i].stop) st[i].round += 1;
+  }
+  for (int k = i; k < n_conf; k += gridDim.x * blockDim.x) conf[k] = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// shuffle: keyed Feistel bijection on [0, n) by cycle walking
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n, int half_bits, uint32_t ka, uint32_t kb) {
+  const uint32_t mask = (1u << half_bits) - 1u;
+  uint32_t x = i;
+  do {
+    uint32_t l = x >> half_bits, r = x & mask;
+#pragma unroll
+    for (int round = 0; round < 4; ++round) {
+      uint32_t c[4] = {r, (uint32_t)round, ka, kb};
+      philox4x32(c, 0xA511E9B3u, 0x5851F42Du);
+      const uint32_t nl = r, nr = l ^ (c[0] & mask);
+      l = nl; r = nr;
+    }
+    x = (l << half_bits) | r;
+  } while (x >= n);
+  return x;
+}
+
+__global__ void k_shuffle(const FedbGroup* __restrict__ groups, const int32_t* __restrict__ idx_in,
+                          int32_t* __restrict__ idx_out, const int32_t* __restrict__ epoch,
+                          const int32_t* __restrict__ active, uint32_t s0, uint32_t s1) {
+  const int g = blockIdx.y;
+  if (active && !active[g]) return;
+  const FedbGroup& G = groups[g];
+  const uint32_t n = (uint32_t)G.n_rows;
+  int bits = 1;
+  while ((1u << bits) < n) ++bits;
+  const int half = (bits + 1) >> 1;
+  const uint32_t ka = s0 ^ (uint32_t)(g * 0x9E3779B1u), kb = s1 + (uint32_t)epoch[g];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    idx_out[G.idx_off + i] = idx_in[G.idx_off + feistel_perm(i, n, half, ka, kb)];
+}
+
+// ---------------------------------------------------------------------------------------
+// K2 part 1: forward + loss + backward, one 32-row tile per CTA
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NTHREADS)
+k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ tiles, const float* __restrict__ params,
+          const float* __restrict__ X, int ldx, const int32_t* __restrict__ y, const int32_t* __restrict__ idx,
+          int batch, float* __restrict__ scratch, int32_t* __restrict__ step, const int32_t* __restrict__ active,
+          const FedbFedState* __restrict__ fed_state) {
+  extern __shared__ __align__(16) float smem[];
+  const FedbTile T = tiles[blockIdx.x];
+  const int g = T.owner;
+  const FedbGroup& G = groups[g];
+  if (active && !active[g]) return;
+  if (fed_state && fed_state[G.fed].stop) return;
+  const int n = G.n_rows;
+  const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
+  const int b0 = batch * bs;
+  if (b0 >= n) return;
+  const int nb = min(bs, n - b0);
+  const int r0 = T.tile * FEDB_TILE_ROWS;
+  if (r0 >= nb) return;
+  const int nvalid = min(FEDB_TILE_ROWS, nb - r0);
+  const int L = G.n_layers;
+  const SlabLayout lay = slab_layout(G.dims, L);
+  const SmemPlan sp = smem_plan(G.dims, L);
+  const float* P = params + G.slab_off;
+  float* rec = scratch + G.scratch_off + (size_t)T.tile * (G.slab_size + FEDB_LOSS_SLOTS);
+  int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
+  const int lane = threadIdx.x & 31;
+
+  if (T.tile == 0 && threadIdx.x == 0) step[g] += 1;  // optimizer step counter (t in Adam)
+
+  load_tile(X, ldx, y, idx, G.idx_off + b0 + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
+  __syncthreads();
+
+  for (int l = 0; l < L; ++l) {
+    layer_forward(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                  smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    __syncthreads();
+  }
+
+  // head: loss and dz of the output layer, warp 0, lane = row
+  float* zL = smem + sp.a_off[L];
+  float* dz = smem + sp.dz_off[0];
+  const float inv_n = 1.f / (float)nb;
+  const int C = G.dims[L];
+  if (threadIdx.x < 32) {
+    float loss = 0.f;
+    const bool valid = lane < nvalid;
+    const int yl = ylab[lane];
+    if (G.head == FEDB_HEAD_SOFTMAX_CE) {
+      float mx = -INFINITY;
+      for (int c = 0; c < C; ++c) mx = fmaxf(mx, zL[c * LDS + lane]);
+      float se = 0.f;
+      for (int c = 0; c < C; ++c) se += expf(zL[c * LDS + lane] - mx);
+      const float lse = mx + logf(se);
+      loss = valid ? (lse - zL[yl * LDS + lane]) : 0.f;
+      for (int c = 0; c < ru4(C); ++c) {
+        float d = 0.f;
+        if (c < C && valid) d = (expf(zL[c * LDS + lane] - lse) - (c == yl ? 1.f : 0.f)) * inv_n;
+        dz[c * LDS + lane] = d;
+      }
+    } else {
+      const float z = zL[lane];
+      const float p = 1.f / (1.f + expf(-z));
+      const float eps = 1.1920929e-07f;  // SKB:273-274 clips probabilities at dtype eps
+      const float pc = fminf(fmaxf(p, eps), 1.f - eps);
+      const float yt = (float)yl;
+      loss = valid ? -(yt * logf(pc) + (1.f - yt) * logf(1.f - pc)) : 0.f;
+      dz[lane] = valid ? (p - yt) * inv_n : 0.f;
+      for (int c = 1; c < 4; ++c) dz[c * LDS + lane] = 0.f;
+    }
+    loss = warp_sum(loss);
+    if (lane == 0) rec[G.slab_size] = loss;  // sum (not mean) of row losses of this tile
+  }
+  __syncthreads();
+
+  int cur = 0;
+  for (int l = L - 1; l >= 0; --l) {
+    const float* dzc = smem + sp.dz_off[cur];
+    layer_wgrad(dzc, smem + sp.a_off[l], lay.ld[l], G.dims[l + 1], rec + lay.w_off[l], rec + lay.b_off[l]);
+    if (l > 0)
+      layer_dgrad(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+                  smem + sp.dz_off[cur ^ 1], G.act);
+    __syncthreads();
+    cur ^= 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K2 part 2: fixed-order reduction over tiles + L2 + optimizer
+// ---------------------------------------------------------------------------------------
+struct StepScalars {
+  float lr_eff;   // torch Adam: lr / (1 - b1^t) ; sklearn Adam: lr*sqrt(1-b2^t)/(1-b1^t) ; SGD: lr
+  float inv_sqrt_bc2;  // torch Adam: 1/sqrt(1 - b2^t)
+};
+
+__device__ inline StepScalars step_scalars(const FedbGroup& G, int t) {
+  StepScalars s;
+  double lr = (double)G.lr;
+  if (G.lr_step_size > 0) lr *= pow((double)G.lr_gamma, (double)((t - 1) / G.lr_step_size));
+  if (G.opt == FEDB_OPT_ADAM_TORCH) {
+    const double bc1 = 1.0 - pow((double)G.beta1, (double)t), bc2 = 1.0 - pow((double)G.beta2, (double)t);
+    s.lr_eff = (float)(lr / bc1);
+    s.inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  } else if (G.opt == FEDB_OPT_ADAM_SKLEARN) {
+    const double bc1 = 1.0 - pow((double)G.beta1, (double)t), bc2 = 1.0 - pow((double)G.beta2, (double)t);
+    s.lr_eff = (float)(lr * sqrt(bc2) / bc1);
+    s.inv_sqrt_bc2 = 1.f;
+  } else {
+    s.lr_eff = (float)lr;
+    s.inv_sqrt_bc2 = 1.f;
+  }
+  return s;
+}
+
+__device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalars& sc, float w, float g, float& m,
+                                            float& v) {
+  if (G.opt == FEDB_OPT_ADAM_TORCH) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    const float denom = sqrtf(v) * sc.inv_sqrt_bc2 + G.eps;
+    return w - sc.lr_eff * (m / denom);
+  } else if (G.opt == FEDB_OPT_ADAM_SKLEARN) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    return w - sc.lr_eff * m / (sqrtf(v) + G.eps);
+  } else {
+    // SKO SGDOptimizer: velocity = momentum*velocity - lr*g ; nesterov looks ahead
+    m = G.momentum * m - sc.lr_eff * g;
+    const float upd = G.nesterov ? (G.momentum * m - sc.lr_eff * g) : m;
+    return w + upd;
+  }
+}
+
+__global__ void __launch_bounds__(NTHREADS)
+k_reduce_opt(const FedbGroup* __restrict__ groups, float* __restrict__ params, float* __restrict__ m,
+             float* __restrict__ v, const float* __restrict__ scratch, int batch, const int32_t* __restrict__ step,
+             const int32_t* __restrict__ active, const FedbFedState* __restrict__ fed_state,
+             float* __restrict__ loss_out, double* __restrict__ batch_stats, int max_batches) {
+  const int g = blockIdx.y;
+  const FedbGroup& G = groups[g];
+  if (active && !active[g]) return;
+  if (fed_state && fed_state[G.fed].stop) return;
+  const int n = G.n_rows;
+  const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
+  const int b0 = batch * bs;
+  if (b0 >= n) return;
+  const int nb = min(bs, n - b0);
+  const int ntiles = (nb + FEDB_TILE_ROWS - 1) / FEDB_TILE_ROWS;
+  const int P = G.slab_size, stride = P + FEDB_LOSS_SLOTS;
+  const SlabLayout lay = slab_layout(G.dims, G.n_layers);
+  const float* rec = scratch + G.scratch_off;
+
+  __shared__ StepScalars sc_s;
+  __shared__ float red[NTHREADS / 32];
+  if (threadIdx.x == 0) sc_s = step_scalars(G, step[g]);
+  __syncthreads();
+  const StepScalars sc = sc_s;
+
+  float sumsq = 0.f;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q * 4 < lay.end) {
+    const int e = q * 4;
+    bool is_w = false;
+    for (int l = 0; l < G.n_layers; ++l) is_w |= (e >= lay.w_off[l] && e < lay.b_off[l]);
+    float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t = 0; t < ntiles; ++t) {
+      const float4 p = *reinterpret_cast<const float4*>(rec + (size_t)t * stride + e);
+      gsum.x += p.x; gsum.y += p.y; gsum.z += p.z; gsum.w += p.w;
+    }
+    float4 w = *reinterpret_cast<float4*>(params + G.slab_off + e);
+    if (is_w) {
+      sumsq = w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
+      if (G.alpha != 0.f) {
+        const float a = G.alpha / (float)nb;  // SK:235: (a^T delta + alpha W)/n
+        gsum.x = fmaf(a, w.x, gsum.x); gsum.y = fmaf(a, w.y, gsum.y);
+        gsum.z = fmaf(a, w.z, gsum.z); gsum.w = fmaf(a, w.w, gsum.w);
+      }
+    }
+    float4 mm = make_float4(0.f, 0.f, 0.f, 0.f), vv = mm;
+    if (m) mm = *reinterpret_cast<float4*>(m + G.slab_off + e);
+    if (v && G.opt != FEDB_OPT_SGD) vv = *reinterpret_cast<float4*>(v + G.slab_off + e);
+    w.x = opt_update(G, sc, w.x, gsum.x, mm.x, vv.x);
+    w.y = opt_update(G, sc, w.y, gsum.y, mm.y, vv.y);
+    w.z = opt_update(G, sc, w.z, gsum.z, mm.z, vv.z);
+    w.w = opt_update(G, sc, w.w, gsum.w, mm.w, vv.w);
+    *reinterpret_cast<float4*>(params + G.slab_off + e) = w;
+    if (m) *reinterpret_cast<float4*>(m + G.slab_off + e) = mm;
+    if (v && G.opt != FEDB_OPT_SGD) *reinterpret_cast<float4*>(v + G.slab_off + e) = vv;
+  }
+
+  // loss + sum of squares bookkeeping (deterministic: fixed tree, fixed block order)
+  if (batch_stats) {
+    sumsq = warp_sum(sumsq);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sumsq;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.f;
+      for (int i = 0; i < NTHREADS / 32; ++i) s += red[i];
+      // per (group, batch): slot 0 = data loss sum, slots 1.. = per-block sumsq
+      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + gridDim.x);
+      bsrow[2 + blockIdx.x] = (double)s;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float ls = 0.f;
+    for (int t = 0; t < ntiles; ++t) ls += rec[(size_t)t * stride + P];
+    if (loss_out) loss_out[g] = ls / (float)nb;
+    if (batch_stats) {
+      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + gridDim.x);
+      bsrow[0] = (double)ls;
+      bsrow[1] = (double)nb;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// sklearn epoch end: loss curve + tol / n_iter_no_change (SK:750-777)
+// ---------------------------------------------------------------------------------------
+__global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, const double* __restrict__ batch_stats,
+                            int max_batches, int nblk, double tol, int n_iter_no_change, int max_iter,
+                            int32_t* __restrict__ active, int32_t* __restrict__ epoch, int32_t* __restrict__ no_improve,
+                            double* __restrict__ best_loss, double* __restrict__ last_loss) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_groups || !active[g]) return;
+  const FedbGroup& G = groups[g];
+  const int n = G.n_rows;
+  const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
+  const int nbatches = (n + bs - 1) / bs;
+  double accumulated = 0.0;
+  for (int b = 0; b < nbatches; ++b) {
+    const double* row = batch_stats + ((size_t)g * max_batches + b) * (2 + nblk);
+    double ss = 0.0;
+    for (int k = 0; k < nblk; ++k) ss += row[2 + k];
+    // batch_loss = mean logloss + 0.5*alpha*||W||^2 / n_b ; accumulated += batch_loss * n_b
+    accumulated += row[0] + 0.5 * (double)G.alpha * ss;
+  }
+  const double loss = accumulated / (double)n;
+  last_loss[g] = loss;
+  epoch[g] += 1;
+  if (loss > best_loss[g] - tol) no_improve[g] += 1; else no_improve[g] = 0;
+  if (loss < best_loss[g]) best_loss[g] = loss;
+  if (no_improve[g] > n_iter_no_change || epoch[g] >= max_iter) active[g] = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// K3: eval
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NTHREADS)
+k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ jobs, const FedbTile* __restrict__ tiles,
+       const float* __restrict__ params, const float* __restrict__ global, const float* __restrict__ X, int ldx,
+       const int32_t* __restrict__ y, const int32_t* __restrict__ idx, int32_t* __restrict__ conf,
+       const FedbFedState* __restrict__ fed_state) {
+  extern __shared__ __align__(16) float smem[];
+  const FedbTile T = tiles[blockIdx.x];
+  const FedbEvalJob J = jobs[T.owner];
+  const FedbGroup& G = groups[J.group];
+  if (fed_state && fed_state[G.fed].stop) return;
+  const int r0 = T.tile * FEDB_TILE_ROWS;
+  if (r0 >= J.n_rows) return;
+  const int nvalid = min(FEDB_TILE_ROWS, J.n_rows - r0);
+  const int L = G.n_layers;
+  const SlabLayout lay = slab_layout(G.dims, L);
+  const SmemPlan sp = smem_plan(G.dims, L);
+  const float* P = (J.from_global ? global : params) + J.slab_off;
+  int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
+  load_tile(X, ldx, y, idx, J.idx_off + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
+  __syncthreads();
+  for (int l = 0; l < L; ++l) {
+    layer_forward(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                  smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    __syncthreads();
+  }
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    const float* zL = smem + sp.a_off[L];
+    int pred;
+    if (G.head == FEDB_HEAD_SOFTMAX_CE) {
+      // torch.max(outputs, 1): first maximal index (C:81)
+      pred = 0;
+      float best = zL[lane];
+      for (int c = 1; c < G.dims[L]; ++c) {
+        const float z = zL[c * LDS + lane];
+        if (z > best) { best = z; pred = c; }
+      }
+    } else {
+      pred = zL[lane] > 0.f ? 1 : 0;  // sigmoid(z) > 0.5 (SK:1283-1290)
+    }
+    if (lane < nvalid) {
+      const int yt = ylab[lane];
+      if (yt >= 0 && yt < FEDB_MAX_CLASSES && pred < FEDB_MAX_CLASSES)
+        atomicAdd(conf + (size_t)J.conf_slot * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + yt * FEDB_MAX_CLASSES + pred, 1);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K1 + K5: FedAvg, metrics, early stop
+// ---------------------------------------------------------------------------------------
+__device__ void metrics_from_conf(const int32_t* cm, int C, double out[4]) {
+  double total = 0, tr = 0;
+  double sup[FEDB_MAX_CLASSES], prd[FEDB_MAX_CLASSES];
+  for (int c = 0; c < C; ++c) { sup[c] = 0; prd[c] = 0; }
+  for (int i = 0; i < C; ++i)
+    for (int j = 0; j < C; ++j) {
+      const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
+      total += x; sup[i] += x; prd[j] += x;
+      if (i == j) tr += x;
+    }
+  out[0] = out[1] = out[2] = out[3] = 0.0;
+  if (total == 0) return;
+  out[0] = tr / total;
+  for (int c = 0; c < C; ++c) {
+    const double tp = (double)cm[c * FEDB_MAX_CLASSES + c];
+    const double w = sup[c] / total;
+    const double p = prd[c] > 0 ? tp / prd[c] : 0.0;
+    const double r = sup[c] > 0 ? tp / sup[c] : 0.0;
+    const double den = sup[c] + prd[c];
+    const double f = den > 0 ? 2.0 * tp / den : 0.0;
+    out[1] += p * w; out[2] += r * w; out[3] += f * w;
+  }
+}
+
+__device__ __noinline__ void round_metrics(const FedbGroup* groups, const FedbFed& F, FedbFedState& S, int f, int n_groups,
+                              const int32_t* conf, float* hist_local, float* hist_global) {
+  const int C = F.n_classes;
+  const int r = S.round - 1;  // 0-based index of the round in progress
+  double glob[4] = {0, 0, 0, 0};
+  int32_t pooled[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+  for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] = 0;
+  for (int k = 0; k < F.n_clients; ++k) {
+    const int g = F.first_group + k;
+    const int32_t* cm = conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+    double mloc[4];
+    metrics_from_conf(cm, C, mloc);
+    if (hist_local && r >= 0 && r < F.max_rounds)
+      for (int i = 0; i < 4; ++i) hist_local[((size_t)r * n_groups + g) * 4 + i] = (float)mloc[i];
+    for (int i = 0; i < 4; ++i) glob[i] += mloc[i];
+    for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] += cm[i];
+  }
+  if (F.metric_mode == FEDB_METRIC_POOLED) metrics_from_conf(pooled, C, glob);
+  else for (int i = 0; i < 4; ++i) glob[i] /= (double)F.n_clients;
+  for (int i = 0; i < 4; ++i) S.last[i] = glob[i];
+  if (hist_global && r >= 0 && r < F.max_rounds)
+    for (int i = 0; i < 4; ++i) hist_global[((size_t)f * F.max_rounds + r) * 4 + i] = (float)glob[i];
+  if (F.patience > 0) {
+    bool close = S.has_anchor != 0;
+    if (close)
+      for (int i = 0; i < 4; ++i)
+        close = close && (fabs(glob[i] - S.anchor[i]) <= (double)F.atol + (double)F.rtol * fabs(S.anchor[i]));
+    if (close) {
+      S.count -= 1;
+      if (S.count == 0) S.stop_pending = 1;
+    } else {
+      for (int i = 0; i < 4; ++i) S.anchor[i] = glob[i];
+      S.has_anchor = 1;
+      S.count = F.patience;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NTHREADS)
+k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds, FedbFedState* __restrict__ state,
+         int n_groups, float* __restrict__ params, float* __restrict__ global, const int32_t* __restrict__ conf,
+         float* __restrict__ hist_local, float* __restrict__ hist_global, int write_back, int do_metrics) {
+  const int f = blockIdx.y;
+  const FedbFed& F = feds[f];
+  if (state[f].stop) return;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q * 4 < F.slab_size) {
+    const int e = q * 4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < F.n_clients; ++k) {
+      const FedbGroup& G = groups[F.first_group + k];
+      const float4 w = *reinterpret_cast<const float4*>(params + G.slab_off + e);
+      // reference arithmetic, term by term: (w * n_k) / N, accumulated in client order
+      acc.x += __fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den);
+      acc.y += __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den);
+      acc.z += __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den);
+      acc.w += __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den);
+    }
+    *reinterpret_cast<float4*>(global + F.global_off + e) = acc;
+    if (write_back)
+      for (int k = 0; k < F.n_clients; ++k)
+        *reinterpret_cast<float4*>(params + groups[F.first_group + k].slab_off + e) = acc;
+  }
+  if (do_metrics && blockIdx.x == 0 && threadIdx.x == 0)
+    round_metrics(groups, F, state[f], f, n_groups, conf, hist_local, hist_global);
+}
+
+}  // namespace fedb
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+using namespace fedb;
+
+extern "C" const char* fedb_last_error(void) { return g_err; }
+extern "C" int fedb_version(void) { return 100; }
+extern "C" void fedb_struct_sizes(int32_t* out) {
+  out[0] = (int32_t)sizeof(FedbGroup); out[1] = (int32_t)sizeof(FedbFed); out[2] = (int32_t)sizeof(FedbFedState);
+  out[3] = (int32_t)sizeof(FedbEvalJob); out[4] = (int32_t)sizeof(FedbTile);
+}
+
+extern "C" int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers) {
+  if (n_layers < 1 || n_layers > FEDB_MAX_LAYERS) return -1;
+  const SmemPlan sp = smem_plan(dims, n_layers);
+  const int64_t bytes = (int64_t)sp.total_floats * 4;
+  return bytes <= 227 * 1024 ? bytes : -1;
+}
+
+static int set_smem(const void* fn, int64_t bytes) {
+  if (bytes > 48 * 1024) FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return FEDB_OK;
+}
+
+extern "C" int32_t fedb_batch_stats_stride(int32_t max_slab) { return 2 + (max_slab / 4 + NTHREADS - 1) / NTHREADS; }
+
+extern "C" int fedb_init_params(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, float* params,
+                                const int32_t* streams, int32_t kind, uint64_t seed, void* stream) {
+  FEDB_REQUIRE(n_groups > 0 && max_slab > 0, "bad sizes");
+  dim3 grid((max_slab / 4 + 127) / 128, n_groups);
+  k_init<<<grid, 128, 0, (cudaStream_t)stream>>>(groups, params, streams, kind, (uint32_t)seed, (uint32_t)(seed >> 32));
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_round_begin(const FedbFed* feds, FedbFedState* state, int32_t n_feds, int32_t* conf,
+                                int32_t conf_slots_total, void* stream) {
+  const int n_conf = conf_slots_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  const int work = n_conf > n_feds ? n_conf : n_feds;
+  int blocks = (work + 255) / 256;
+  if (blocks > 1024) blocks = 1024;
+  if (blocks * 256 < n_feds) return set_err(FEDB_E_ARG, "too many federations for fedb_round_begin");
+  k_round_begin<<<blocks, 256, 0, (cudaStream_t)stream>>>(feds, state, n_feds, conf, n_conf);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_shuffle(const FedbGroup* groups, int32_t n_groups, const int32_t* idx_in, int32_t* idx_out,
+                            const int32_t* epoch, const int32_t* active, uint64_t seed, void* stream) {
+  dim3 grid(8, n_groups);
+  k_shuffle<<<grid, 256, 0, (cudaStream_t)stream>>>(groups, idx_in, idx_out, epoch, active, (uint32_t)seed,
+                                                    (uint32_t)(seed >> 32));
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_fwd_bwd(const FedbGroup* groups, const FedbTile* tiles, int32_t n_tiles, const float* params,
+                            const float* X, int32_t ldx, const int32_t* y, const int32_t* idx, int32_t batch,
+                            float* scratch, int32_t* step, const int32_t* active, const FedbFedState* fed_state,
+                            int64_t smem_bytes, void* stream) {
+  FEDB_REQUIRE(n_tiles > 0, "n_tiles must be positive");
+  FEDB_REQUIRE(ldx % 4 == 0, "ldx must be a multiple of 4");
+  FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
+  if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
+  k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, tiles, params, X, ldx, y, idx, batch,
+                                                                     scratch, step, active, fed_state);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_reduce_opt(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, float* params, float* m,
+                               float* v, const float* scratch, int32_t batch, const int32_t* step,
+                               const int32_t* active, const FedbFedState* fed_state, float* loss_out,
+                               double* batch_stats, int32_t max_batches, void* stream) {
+  FEDB_REQUIRE(n_groups > 0 && max_slab > 0, "bad sizes");
+  dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_groups);
+  k_reduce_opt<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups, params, m, v, scratch, batch, step, active,
+                                                            fed_state, loss_out, batch_stats, max_batches);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_epoch_end(const FedbGroup* groups, int32_t n_groups, const double* batch_stats, int32_t max_batches,
+                              int32_t max_slab, double tol, int32_t n_iter_no_change, int32_t max_iter, int32_t* active,
+                              int32_t* epoch, int32_t* no_improve, double* best_loss, double* last_loss,
+                              void* stream) {
+  const int nblk = (max_slab / 4 + NTHREADS - 1) / NTHREADS;
+  k_epoch_end<<<(n_groups + 127) / 128, 128, 0, (cudaStream_t)stream>>>(groups, n_groups, batch_stats, max_batches, nblk,
+                                                                      tol, n_iter_no_change, max_iter, active, epoch,
+                                                                      no_improve, best_loss, last_loss);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const FedbTile* tiles, int32_t n_tiles,
+                         const float* params, const float* global, const float* X, int32_t ldx, const int32_t* y,
+                         const int32_t* idx, int32_t* conf, const FedbFedState* fed_state, int64_t smem_bytes,
+                         void* stream) {
+  FEDB_REQUIRE(n_tiles > 0, "n_tiles must be positive");
+  FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
+  if (int rc = set_smem((const void*)k_eval, smem_bytes)) return rc;
+  k_eval<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, jobs, tiles, params, global, X, ldx, y, idx,
+                                                                  conf, fed_state);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+extern "C" int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
+                           int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
+                           float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
+                           void* stream) {
+  FEDB_REQUIRE(n_feds > 0 && max_slab > 0, "bad sizes");
+  dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_feds);
+  k_fedavg<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups, feds, state, n_groups, params, global, conf, hist_local,
+                                                        hist_global, write_back, do_metrics);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}

@@ -1,0 +1,4 @@
+from fedb200.cli import main
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -1,0 +1,402 @@
+"""Round engine: many simulated clients (and many federations) per process, all state resident
+on the device, one short fixed kernel sequence per round.
+
+What the reference does per round with ~10 collectives, 4 host<->device dataset copies, 12
+weight copies and 4 sklearn metric calls per rank (C:130-201) is here:
+
+    round_begin -> E x [fwd_bwd -> reduce_opt] -> eval -> fedavg(+metrics +early stop)
+
+enqueued on one stream, captured once into a CUDA graph and replayed.  Nothing returns to the
+host inside a round; the stop flag (C:132-136, C:181-195) lives on the device and kernels of a
+stopped federation exit immediately, so the host only polls it every few rounds.  The
+sklearn-style "fit until the loss stalls" local training (S:101, H:91) is `fit_local`.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from ..models import init as minit
+from ..models.spec import MLPSpec
+from ..ops import _native as nat
+from ..ops import kernels as K
+from .metrics import METRIC_NAMES
+from .problem import FedProblem
+
+TILE = nat.TILE_ROWS
+
+
+def _ru(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class FedEngine:
+    def __init__(self, problems: Sequence[FedProblem], X_train: np.ndarray, y_train: np.ndarray,
+                 X_test: Optional[np.ndarray] = None, y_test: Optional[np.ndarray] = None,
+                 device: Optional[str] = None, max_rounds: int = 300, seed: int = 0):
+        self.problems = list(problems)
+        if device is None:
+            device = "cuda" if torch.cuda.is_available() else "cpu"
+        self.device = torch.device(device)
+        if self.device.type == "cuda":
+            nat.lib(required=True)  # fail loudly rather than run a fallback on a GPU box
+        self.max_rounds = int(max_rounds)
+        self.seed = int(seed)
+        self.n_train = len(X_train)
+        self.n_test = 0 if X_test is None else len(X_test)
+        nf = X_train.shape[1]
+        self.ldx = max(16, _ru(nf, 4))
+        Xall = np.zeros((self.n_train + self.n_test, self.ldx), dtype=np.float32)
+        Xall[: self.n_train, :nf] = X_train
+        yall = np.zeros(self.n_train + self.n_test, dtype=np.int32)
+        yall[: self.n_train] = y_train
+        if self.n_test:
+            Xall[self.n_train:, :nf] = X_test
+            yall[self.n_train:] = y_test
+        self.X = torch.from_numpy(Xall).to(self.device)
+        self.y = torch.from_numpy(yall).to(self.device)
+        self._build_tables()
+        self._alloc_state()
+        self._graphs: Dict[str, object] = {}
+        self.init_params()
+
+    # ------------------------------------------------------------------------------ tables
+    def _build_tables(self) -> None:
+        G = sum(p.n_clients for p in self.problems)
+        F = len(self.problems)
+        groups = np.zeros(G, dtype=nat.GROUP_DTYPE)
+        feds = np.zeros(F, dtype=nat.FED_DTYPE)
+        idx_parts: List[np.ndarray] = []
+        slab_off = idx_off = scratch_off = global_off = 0
+        g = 0
+        self.group_of: List[List[int]] = []
+        for f, p in enumerate(self.problems):
+            s, h = p.spec, p.hyper
+            P = s.slab_size
+            sizes = [len(sh) for sh in p.shards]
+            total = float(sum(sizes))
+            feds[f] = (g, p.n_clients, P, s.n_classes, global_off, nat.METRIC_IDS[p.metric_mode], p.patience,
+                       p.atol, p.rtol, self.max_rounds, 0)
+            global_off += P
+            members = []
+            for k, sh in enumerate(p.shards):
+                sh = np.asarray(sh, dtype=np.int32)
+                if len(sh) == 0:
+                    raise ValueError(f"client {k} of federation {f} has an empty shard (the reference would deadlock: S:91-93)")
+                rows_per_step = min(h.batch_size, len(sh)) if h.batch_size > 0 else len(sh)
+                max_tiles = (rows_per_step + TILE - 1) // TILE
+                r = groups[g]
+                r["n_layers"] = s.n_layers
+                r["dims"][: len(s.dims)] = s.dims
+                r["head"], r["act"] = nat.HEAD_IDS[s.head], nat.ACT_IDS[s.activation]
+                r["slab_size"], r["fed"], r["slab_off"], r["idx_off"] = P, f, slab_off, idx_off
+                r["n_rows"], r["batch_size"] = len(sh), h.batch_size
+                r["opt"], r["nesterov"] = nat.OPT_IDS[h.opt], int(h.nesterov)
+                r["lr"], r["beta1"], r["beta2"], r["eps"] = h.lr, h.beta1, h.beta2, h.eps
+                r["momentum"], r["alpha"] = h.momentum, h.alpha
+                r["lr_step_size"], r["lr_gamma"] = h.lr_step_size, h.lr_gamma
+                if p.weighting == "samples":
+                    r["agg_num"], r["agg_den"] = float(len(sh)), total
+                else:
+                    r["agg_num"], r["agg_den"] = 1.0, float(p.n_clients)
+                r["scratch_off"], r["max_tiles"], r["client"] = scratch_off, max_tiles, k
+                slab_off += P
+                idx_off += len(sh)
+                scratch_off += max_tiles * (P + nat.LOSS_SLOTS)
+                idx_parts.append(sh)
+                members.append(g)
+                g += 1
+            self.group_of.append(members)
+        self.n_groups, self.n_feds = G, F
+        self.params_total, self.global_total, self.scratch_total = slab_off, global_off, scratch_off
+        # evaluation index sets appended after the shards: the whole test set, the whole train set
+        self.test_idx_off = idx_off
+        if self.n_test:
+            idx_parts.append(np.arange(self.n_train, self.n_train + self.n_test, dtype=np.int32))
+            idx_off += self.n_test
+        self.train_idx_off = idx_off
+        idx_parts.append(np.arange(self.n_train, dtype=np.int32))
+        self.idx_host = np.concatenate(idx_parts)
+        self.tb = K.DeviceTables.build(groups, feds, self.device)
+        self.idx = torch.from_numpy(self.idx_host).to(self.device)
+        # training tiles
+        tiles = [(gi, t) for gi in range(G) for t in range(int(groups[gi]["max_tiles"]))]
+        self.train_tiles_np = np.array(tiles, dtype=np.int32).view(nat.TILE_DTYPE).reshape(-1)
+        self.train_tiles = K.upload_table(self.train_tiles_np, self.device)
+        self.n_batches = max(
+            1 if p.hyper.batch_size <= 0 else max(math.ceil(len(sh) / min(p.hyper.batch_size, len(sh))) for sh in p.shards)
+            for p in self.problems)
+        # local evaluation: every client's own slab on its own shard -> confusion slot g
+        self.local_jobs_np, self.local_jobs, self.local_tiles, self.n_local_tiles = self._make_jobs(
+            [(gi, int(groups[gi]["n_rows"]), int(groups[gi]["slab_off"]), int(groups[gi]["idx_off"]), gi, 0) for gi in range(G)])
+        # held-out evaluation of each federation's global model -> slots G+f (test), G+F+f (train)
+        self.n_conf_slots = G + 2 * F
+        self._global_jobs = {}
+        for which, off, n in (("test", self.test_idx_off, self.n_test), ("train", self.train_idx_off, self.n_train)):
+            if n == 0:
+                continue
+            base = G if which == "test" else G + F
+            self._global_jobs[which] = self._make_jobs(
+                [(int(feds[f]["first_group"]), n, int(feds[f]["global_off"]), off, base + f, 1) for f in range(F)])
+
+    def _make_jobs(self, rows):
+        jobs = np.zeros(len(rows), dtype=nat.EVALJOB_DTYPE)
+        tiles = []
+        for j, (grp, n, slab_off, idx_off, slot, from_global) in enumerate(rows):
+            jobs[j] = (grp, n, slab_off, idx_off, slot, from_global)
+            tiles += [(j, t) for t in range((n + TILE - 1) // TILE)]
+        tiles_np = np.array(tiles, dtype=np.int32).view(nat.TILE_DTYPE).reshape(-1)
+        return jobs, K.upload_table(jobs, self.device), K.upload_table(tiles_np, self.device), len(tiles_np)
+
+    # ------------------------------------------------------------------------------- state
+    def _alloc_state(self) -> None:
+        d, G, F = self.device, self.n_groups, self.n_feds
+        z = lambda n, dt=torch.float32: torch.zeros(n, dtype=dt, device=d)
+        self.params, self.m, self.v = z(self.params_total), z(self.params_total), z(self.params_total)
+        self.global_ = z(self.global_total)
+        self.scratch = z(self.scratch_total)
+        self.step = z(G, torch.int32)
+        self.active = torch.ones(G, dtype=torch.int32, device=d)
+        self.loss = z(G)
+        self.conf = z(self.n_conf_slots * nat.MAX_CLASSES ** 2, torch.int32)
+        self.hist_local = z(self.max_rounds * G * 4)
+        self.hist_global = z(F * self.max_rounds * 4)
+        st = np.zeros(F, dtype=nat.FEDSTATE_DTYPE)
+        st["count"] = self.tb.feds["patience"]
+        self.fed_state = K.upload_table(st, d)
+        # sklearn-style fit state
+        self.epoch, self.no_improve = z(G, torch.int32), z(G, torch.int32)
+        self.best_loss = torch.full((G,), float("inf"), dtype=torch.float64, device=d)
+        self.last_loss = z(G, torch.float64)
+        self.bs_stride = K.batch_stats_stride(self.tb.max_slab)
+        self.batch_stats = z(G * self.n_batches * self.bs_stride, torch.float64)
+        self.idx_epoch = self.idx.clone()
+
+    def init_params(self) -> None:
+        """(Re-)initialise every client's parameters and clear optimizer state (K4)."""
+        by_kind: Dict[str, np.ndarray] = {}
+        for f, p in enumerate(self.problems):
+            if p.init == "sklearn_exact":
+                slab = torch.from_numpy(minit.init_slab_sklearn_exact(p.spec, p.init_seed))
+                for gi in self.group_of[f]:
+                    o = int(self.tb.groups[gi]["slab_off"])
+                    self.params[o: o + p.spec.slab_size].copy_(slab)
+                continue
+            streams = by_kind.setdefault(p.init, np.full(self.n_groups, -1, dtype=np.int32))
+            for k, gi in enumerate(self.group_of[f]):
+                # one Philox stream per (federation seed, client); identical streams when the
+                # federation asks for a shared init
+                streams[gi] = (p.init_seed * 1000003 + (k if p.init_per_client else 0)) & 0x7FFFFFFF
+        for kind, streams in by_kind.items():
+            K.init_params(self.tb, self.params, torch.from_numpy(streams).to(self.device), kind, self.seed)
+        self.m.zero_()
+        self.v.zero_()
+        self.step.zero_()
+
+    # ------------------------------------------------------------------------------ rounds
+    def enqueue_local_step(self, batch: int = 0, idx: Optional[torch.Tensor] = None, stats: bool = False) -> None:
+        """One optimizer step of every active client on minibatch ``batch`` (2 launches)."""
+        idx = self.idx if idx is None else idx
+        K.fwd_bwd(self.tb, self.train_tiles, len(self.train_tiles_np), self.params, self.X, self.y, idx, batch,
+                  self.scratch, self.step, self.active, self.fed_state)
+        K.reduce_opt(self.tb, self.params, self.m, self.v, self.scratch, batch, self.step, self.active, self.fed_state,
+                     self.loss, self.batch_stats if stats else None, self.n_batches)
+
+    def enqueue_eval_local(self) -> None:
+        K.evaluate(self.tb, self.local_jobs_np, self.local_jobs, self.local_tiles, self.n_local_tiles, self.params,
+                   self.global_, self.X, self.y, self.idx, self.conf, self.fed_state)
+
+    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True) -> None:
+        K.fedavg(self.tb, self.fed_state, self.params, self.global_, self.conf, self.hist_local, self.hist_global,
+                 write_back, do_metrics)
+
+    def enqueue_round(self) -> None:
+        """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg."""
+        K.round_begin(self.tb, self.fed_state, self.conf)
+        E = max(p.hyper.local_epochs for p in self.problems)
+        for _ in range(E):
+            for b in range(self.n_batches):
+                self.enqueue_local_step(b)
+        self.enqueue_eval_local()
+        self.enqueue_aggregate()
+
+    @property
+    def launches_per_round(self) -> int:
+        E = max(p.hyper.local_epochs for p in self.problems)
+        return 1 + 2 * E * self.n_batches + 2
+
+    def _graph(self, key: str, fn, unroll: int = 1):
+        """Capture ``unroll`` repetitions of ``fn`` into a CUDA graph (cached)."""
+        gk = f"{key}x{unroll}"
+        if gk not in self._graphs:
+            fn()  # warm-up outside capture: sets function attributes, touches every buffer
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(unroll):
+                    fn()
+            self._graphs[gk] = g
+        return self._graphs[gk]
+
+    def fed_state_host(self) -> np.ndarray:
+        return self.fed_state.cpu().numpy().view(nat.FEDSTATE_DTYPE).copy()
+
+    def run(self, rounds: int, use_graph: Optional[bool] = None, unroll: int = 8, poll: bool = True) -> Dict[str, np.ndarray]:
+        """Run up to ``rounds`` rounds (early stop per federation, C:181-195).  Returns
+        :meth:`history`.  On CUDA the round is replayed from a graph, ``unroll`` rounds per
+        launch; the stop flags are polled once per replay."""
+        st = self.fed_state_host()
+        done = int(st["round"].max()) if len(st) else 0
+        rounds = min(rounds, self.max_rounds - done)
+        use_graph = (self.device.type == "cuda") if use_graph is None else use_graph
+        if not use_graph:
+            for _ in range(rounds):
+                self.enqueue_round()
+                if poll and bool(self.fed_state_host()["stop"].all()):
+                    break
+            return self.history()
+        # Graph capture runs one warm-up round eagerly; snapshot and restore state around it so
+        # capture itself is invisible to the training trajectory.
+        left = rounds
+        while left > 0:
+            u = unroll if left >= unroll else 1
+            if f"roundx{u}" not in self._graphs:
+                snap = self._snapshot()
+                self._graph("round", self.enqueue_round, u)
+                self._restore(snap)
+            self._graphs[f"roundx{u}"].replay()
+            left -= u
+            if poll and bool(self.fed_state_host()["stop"].all()):
+                break
+        return self.history()
+
+    def _snapshot(self):
+        names = ("params", "m", "v", "global_", "step", "active", "loss", "conf", "hist_local", "hist_global",
+                 "fed_state", "epoch", "no_improve", "best_loss", "last_loss", "batch_stats", "idx_epoch")
+        return {n: getattr(self, n).clone() for n in names}
+
+    def _restore(self, snap) -> None:
+        for n, t in snap.items():
+            getattr(self, n).copy_(t)
+
+    # ------------------------------------------------------------- sklearn-style local fit
+    def reset_fit_state(self, keep_no_improvement: bool = False) -> None:
+        """What a non-incremental sklearn ``fit`` resets: a new optimizer (SK:622-640) and,
+        unless ``keep_no_improvement`` (sklearn's warm_start behaviour, SK:433-441), the loss
+        curve bookkeeping."""
+        self.m.zero_()
+        self.v.zero_()
+        self.step.zero_()
+        self.epoch.zero_()
+        self.active.fill_(1)
+        if not keep_no_improvement:
+            self.no_improve.zero_()
+            self.best_loss.fill_(float("inf"))
+
+    def enqueue_epoch(self, shuffle: bool = True) -> None:
+        if shuffle:
+            K.shuffle(self.tb, self.idx, self.idx_epoch, self.epoch, self.active, self.seed + 0x5EED)
+        src = self.idx_epoch if shuffle else self.idx
+        for b in range(self.n_batches):
+            self.enqueue_local_step(b, src, stats=True)
+        h = self.problems[0].hyper
+        K.epoch_end(self.tb, self.batch_stats, self.n_batches, h.tol, h.n_iter_no_change, h.max_iter, self.active,
+                    self.epoch, self.no_improve, self.best_loss, self.last_loss)
+
+    def fit_local(self, max_iter: Optional[int] = None, shuffle: bool = True, check_every: int = 8) -> np.ndarray:
+        """Train every client until its loss stalls (SK:750-777) or ``max_iter`` epochs.
+        Returns the number of epochs each client ran (sklearn's ``n_iter_``)."""
+        max_iter = max_iter or max(p.hyper.max_iter for p in self.problems)
+        use_graph = self.device.type == "cuda"
+        if use_graph and "epochx1" not in self._graphs:
+            snap = self._snapshot()
+            self._graph("epoch", lambda: self.enqueue_epoch(shuffle), 1)
+            self._restore(snap)
+        it = 0
+        while it < max_iter:
+            n = min(check_every, max_iter - it)
+            for _ in range(n):
+                if use_graph:
+                    self._graphs["epochx1"].replay()
+                else:
+                    self.enqueue_epoch(shuffle)
+            it += n
+            if not bool(self.active.any()):
+                break
+        self.active.fill_(1)
+        return self.epoch.cpu().numpy().copy()
+
+    # ----------------------------------------------------------------------------- results
+    def history(self) -> Dict[str, np.ndarray]:
+        st = self.fed_state_host()
+        R = int(st["round"].max()) if len(st) else 0
+        hg = self.hist_global.cpu().numpy().reshape(self.n_feds, self.max_rounds, 4)[:, :R].astype(np.float64)
+        hl = self.hist_local.cpu().numpy().reshape(self.max_rounds, self.n_groups, 4)[:R].astype(np.float64)
+        return {"global": hg, "local": hl, "rounds": st["round"].copy(), "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool),
+                "last": st["last"].copy(), "metric_names": np.asarray(METRIC_NAMES)}
+
+    def confusion(self) -> np.ndarray:
+        return self.conf.cpu().numpy().reshape(self.n_conf_slots, nat.MAX_CLASSES, nat.MAX_CLASSES).copy()
+
+    def global_slab(self, f: int = 0) -> torch.Tensor:
+        o = int(self.tb.feds[f]["global_off"])
+        return self.global_[o: o + self.problems[f].spec.slab_size]
+
+    def client_slab(self, f: int, k: int) -> torch.Tensor:
+        o = int(self.tb.groups[self.group_of[f][k]]["slab_off"])
+        return self.params[o: o + self.problems[f].spec.slab_size]
+
+    def evaluate_global(self, which: str = "test") -> List[Dict[str, float]]:
+        """Metrics of every federation's *global* model on the held-out test split (or the
+        whole train set).  The reference broadcasts X_test/y_test and never uses them
+        (C:245-246); this is the extension BASELINE.md's accuracy band was measured with."""
+        from .metrics import metrics_from_confusion
+        jobs_np, d_jobs, tiles, n_tiles = self._global_jobs[which]
+        base = self.n_groups if which == "test" else self.n_groups + self.n_feds
+        C2 = nat.MAX_CLASSES ** 2
+        self.conf[base * C2: (base + self.n_feds) * C2].zero_()
+        K.evaluate(self.tb, jobs_np, d_jobs, tiles, n_tiles, self.params, self.global_, self.X, self.y, self.idx,
+                   self.conf, None)
+        cm = self.confusion()
+        return [metrics_from_confusion(cm[base + f][: p.spec.n_classes, : p.spec.n_classes]) for f, p in enumerate(self.problems)]
+
+    def save_checkpoint(self, path: str, f: int = 0, resume: bool = False) -> None:
+        from ..models.checkpoint import save_checkpoint
+        p = self.problems[f]
+        opt = None
+        if resume:
+            gs = self.group_of[f]
+            P = p.spec.slab_size
+            o = int(self.tb.groups[gs[0]]["slab_off"])
+            n = len(gs) * P
+            opt = {"m": self.m[o: o + n].view(len(gs), P), "v": self.v[o: o + n].view(len(gs), P),
+                   "step": self.step[gs[0]: gs[0] + len(gs)], "params": self.params[o: o + n].view(len(gs), P)}
+        save_checkpoint(path, p.spec, self.global_slab(f), int(self.fed_state_host()[f]["round"]),
+                        extras={"name": p.name}, opt_state=opt)
+
+    def load_checkpoint(self, path: str, f: int = 0) -> Dict:
+        """Load global weights into every client slab of federation ``f`` (and optimizer state
+        when the file has it)."""
+        from ..models.checkpoint import load_checkpoint
+        p = self.problems[f]
+        spec, coefs, inter, meta, opt = load_checkpoint(path)
+        if spec.dims != p.spec.dims or spec.head != p.spec.head:
+            raise ValueError(f"checkpoint is {spec.describe()}, federation is {p.spec.describe()}")
+        slab = torch.zeros(spec.slab_size)
+        spec.from_coefs_intercepts(coefs, inter, slab)
+        self.global_slab(f).copy_(slab)
+        gs = self.group_of[f]
+        for k in range(len(gs)):
+            self.client_slab(f, k).copy_(slab)
+        if opt:
+            P, o = spec.slab_size, int(self.tb.groups[gs[0]]["slab_off"])
+            n = len(gs) * P
+            self.m[o: o + n].copy_(torch.from_numpy(opt["m"]).reshape(-1))
+            self.v[o: o + n].copy_(torch.from_numpy(opt["v"]).reshape(-1))
+            self.params[o: o + n].copy_(torch.from_numpy(opt["params"]).reshape(-1))
+            self.step[gs[0]: gs[0] + len(gs)].copy_(torch.from_numpy(opt["step"]))
+        return meta

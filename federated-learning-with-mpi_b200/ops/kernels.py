@@ -1,0 +1,176 @@
+"""Launchers for the native kernels (one Python function per C entry point).
+
+Each function takes the device-resident tables of :class:`DeviceTables` plus torch tensors
+and enqueues exactly one kernel on the current CUDA stream (graph-capturable: no allocation,
+no synchronisation).  With CPU tensors it runs the fp32 restatement in ops/reference.py on
+the same buffers instead — that is the CPU test path, not a second backend: on a machine
+with a GPU the native library is mandatory (ops/_native.lib raises if it is missing).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native as nat
+from . import reference as ref
+
+# launches enqueued through this module since import (bench.py reports the delta)
+launch_count = 0
+
+
+def _count(n: int = 1) -> None:
+    global launch_count
+    launch_count += n
+
+
+@dataclass
+class DeviceTables:
+    """Host (NumPy structured) and device (uint8 tensor) copies of the group / federation
+    descriptor tables."""
+
+    groups: np.ndarray          # GROUP_DTYPE[G]
+    feds: np.ndarray            # FED_DTYPE[F]
+    d_groups: torch.Tensor
+    d_feds: torch.Tensor
+    max_slab: int
+    smem_bytes: int
+
+    @property
+    def n_groups(self) -> int:
+        return len(self.groups)
+
+    @property
+    def n_feds(self) -> int:
+        return len(self.feds)
+
+    @staticmethod
+    def build(groups: np.ndarray, feds: np.ndarray, device) -> "DeviceTables":
+        max_slab = int(groups["slab_size"].max())
+        smem = 0
+        for g in groups:
+            smem = max(smem, simt_smem_bytes(g["dims"], int(g["n_layers"])))
+        d_groups = torch.from_numpy(groups.view(np.uint8).copy()).to(device)
+        d_feds = torch.from_numpy(feds.view(np.uint8).copy()).to(device)
+        return DeviceTables(groups, feds, d_groups, d_feds, max_slab, smem)
+
+    def refresh(self) -> None:
+        """Re-upload the host tables after editing hyper-parameters in place."""
+        self.d_groups.copy_(torch.from_numpy(self.groups.view(np.uint8).copy()))
+        self.d_feds.copy_(torch.from_numpy(self.feds.view(np.uint8).copy()))
+
+
+def simt_smem_bytes(dims, n_layers: int) -> int:
+    d = [int(x) for x in dims[: n_layers + 1]]
+    ru4 = lambda x: (x + 3) // 4 * 4
+    maxw = max([4] + [ru4(x) for x in d[1:]])
+    total = (sum(ru4(x) for x in d) + 2 * maxw) * 33 + 64
+    b = total * 4
+    if b > 227 * 1024:
+        raise ValueError(f"MLP {d} needs {b} bytes of shared memory per CTA in the SIMT kernels (max 232448); "
+                         "use the wide (layer-wise tcgen05 GEMM) path")
+    return b
+
+
+def upload_table(arr: np.ndarray, device) -> torch.Tensor:
+    return torch.from_numpy(np.ascontiguousarray(arr).view(np.uint8).copy()).to(device)
+
+
+def _cuda(t: torch.Tensor) -> bool:
+    return t.is_cuda
+
+
+def _L():
+    l = nat.lib(required=True)
+    return l
+
+
+def init_params(tb: DeviceTables, params, streams: torch.Tensor, kind: str, seed: int) -> None:
+    k = nat.INIT_IDS[kind]
+    if _cuda(params):
+        nat.check(_L().fedb_init_params(nat.ptr(tb.d_groups), tb.n_groups, tb.max_slab, nat.ptr(params), nat.ptr(streams),
+                                        k, seed & (2 ** 64 - 1), nat.cuda_stream()))
+        _count()
+    else:
+        ref.init_params(tb.groups, tb.max_slab, params, streams.numpy(), k, seed)
+
+
+def round_begin(tb: DeviceTables, fed_state, conf) -> None:
+    if _cuda(conf):
+        nat.check(_L().fedb_round_begin(nat.ptr(tb.d_feds), nat.ptr(fed_state), tb.n_feds, nat.ptr(conf),
+                                        conf.numel() // (nat.MAX_CLASSES ** 2), nat.cuda_stream()))
+        _count()
+    else:
+        ref.round_begin(tb.feds, fed_state, conf)
+
+
+def shuffle(tb: DeviceTables, idx_in, idx_out, epoch, active, seed: int) -> None:
+    if _cuda(idx_in):
+        nat.check(_L().fedb_shuffle(nat.ptr(tb.d_groups), tb.n_groups, nat.ptr(idx_in), nat.ptr(idx_out), nat.ptr(epoch),
+                                    nat.ptr(active), seed & (2 ** 64 - 1), nat.cuda_stream()))
+        _count()
+    else:
+        ref.shuffle(tb.groups, idx_in, idx_out, epoch, active, seed)
+
+
+def fwd_bwd(tb: DeviceTables, tiles, n_tiles: int, params, X, y, idx, batch: int, scratch, step, active, fed_state) -> None:
+    if _cuda(params):
+        nat.check(_L().fedb_fwd_bwd(nat.ptr(tb.d_groups), nat.ptr(tiles), n_tiles, nat.ptr(params), nat.ptr(X), X.shape[1],
+                                    nat.ptr(y), nat.ptr(idx), batch, nat.ptr(scratch), nat.ptr(step), nat.ptr(active),
+                                    nat.ptr(fed_state), tb.smem_bytes, nat.cuda_stream()))
+        _count()
+    else:
+        ref.fwd_bwd(tb.groups, tiles, params, X, X.shape[1], y, idx, batch, scratch, step, active, fed_state)
+
+
+def reduce_opt(tb: DeviceTables, params, m, v, scratch, batch: int, step, active, fed_state, loss_out,
+               batch_stats=None, max_batches: int = 0) -> None:
+    if _cuda(params):
+        nat.check(_L().fedb_reduce_opt(nat.ptr(tb.d_groups), tb.n_groups, tb.max_slab, nat.ptr(params), nat.ptr(m), nat.ptr(v),
+                                       nat.ptr(scratch), batch, nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
+                                       nat.ptr(loss_out), nat.ptr(batch_stats), max_batches, nat.cuda_stream()))
+        _count()
+    else:
+        ref.reduce_opt(tb.groups, tb.max_slab, params, m, v, scratch, batch, step, active, fed_state, loss_out,
+                       batch_stats, max_batches)
+
+
+def epoch_end(tb: DeviceTables, batch_stats, max_batches: int, tol: float, n_iter_no_change: int, max_iter: int,
+              active, epoch, no_improve, best_loss, last_loss) -> None:
+    if _cuda(batch_stats):
+        nat.check(_L().fedb_epoch_end(nat.ptr(tb.d_groups), tb.n_groups, nat.ptr(batch_stats), max_batches, tb.max_slab,
+                                      float(tol), n_iter_no_change, max_iter, nat.ptr(active), nat.ptr(epoch),
+                                      nat.ptr(no_improve), nat.ptr(best_loss), nat.ptr(last_loss), nat.cuda_stream()))
+        _count()
+    else:
+        ref.epoch_end(tb.groups, batch_stats, max_batches, tb.max_slab, tol, n_iter_no_change, max_iter, active, epoch,
+                      no_improve, best_loss, last_loss)
+
+
+def batch_stats_stride(max_slab: int) -> int:
+    return ref.batch_stats_stride(max_slab)
+
+
+def evaluate(tb: DeviceTables, jobs_np: np.ndarray, d_jobs, tiles, n_tiles: int, params, global_, X, y, idx, conf,
+             fed_state) -> None:
+    if _cuda(params):
+        nat.check(_L().fedb_eval(nat.ptr(tb.d_groups), nat.ptr(d_jobs), nat.ptr(tiles), n_tiles, nat.ptr(params),
+                                 nat.ptr(global_), nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx), nat.ptr(conf),
+                                 nat.ptr(fed_state), tb.smem_bytes, nat.cuda_stream()))
+        _count()
+    else:
+        ref.evaluate(tb.groups, jobs_np, tiles, params, global_, X, X.shape[1], y, idx, conf, fed_state)
+
+
+def fedavg(tb: DeviceTables, fed_state, params, global_, conf, hist_local, hist_global, write_back: bool = True,
+           do_metrics: bool = True) -> None:
+    if _cuda(params):
+        nat.check(_L().fedb_fedavg(nat.ptr(tb.d_groups), nat.ptr(tb.d_feds), nat.ptr(fed_state), tb.n_feds, tb.n_groups,
+                                   tb.max_slab, nat.ptr(params), nat.ptr(global_), nat.ptr(conf), nat.ptr(hist_local),
+                                   nat.ptr(hist_global), int(write_back), int(do_metrics), nat.cuda_stream()))
+        _count()
+    else:
+        ref.fedavg(tb.groups, tb.feds, fed_state, tb.max_slab, params, global_, conf, hist_local, hist_global,
+                   write_back, do_metrics)

@@ -1,0 +1,172 @@
+/*
+ * fedb200 — C ABI of the native library (libfedb200.so), sm_100a only.
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on (as void*),
+ * returns 0 on success or a negative FEDB_E_* code, and never synchronises the device unless
+ * its comment says so.  fedb_last_error() returns a human-readable description of the last
+ * failure on the calling thread.  Python binds these with ctypes
+ * (federated-learning-with-mpi_b200/ops/_native.py); the same header serves C/C++ callers.
+ *
+ * Citations of the form "C:", "S:", "H:" refer to the reference scripts
+ *   C: FL_CustomMLPCLassifierImplementation_Multiple_Rounds.py
+ *   S: FL_SkLearn_MLPClassifier_Limitation.py
+ *   H: hyperparameters_tuning.py
+ * and "SK:" to sklearn/neural_network/_multilayer_perceptron.py, whose behaviour S:/H: rely on.
+ */
+#ifndef FEDB200_H
+#define FEDB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEDB_MAX_LAYERS 6  /* Linear layers per MLP */
+#define FEDB_MAX_CLASSES 8 /* confusion matrix is FEDB_MAX_CLASSES^2 counters per slot */
+#define FEDB_TILE_ROWS 32  /* rows per CTA in the SIMT kernels (one lane per row) */
+#define FEDB_LOSS_SLOTS 32 /* floats appended to every partial-gradient record */
+
+enum { FEDB_OK = 0, FEDB_E_CUDA = -1, FEDB_E_ARG = -2, FEDB_E_UNSUPPORTED = -3, FEDB_E_TIMEOUT = -4 };
+enum { FEDB_HEAD_SOFTMAX_CE = 0, FEDB_HEAD_SIGMOID_LOGLOSS = 1 };
+enum { FEDB_ACT_RELU = 0, FEDB_ACT_LOGISTIC = 1, FEDB_ACT_TANH = 2, FEDB_ACT_IDENTITY = 3 };
+enum { FEDB_OPT_SGD = 0, FEDB_OPT_ADAM_TORCH = 1, FEDB_OPT_ADAM_SKLEARN = 2 };
+enum { FEDB_METRIC_MEAN_OF_LOCAL = 0, FEDB_METRIC_POOLED = 1 };
+enum { FEDB_INIT_ZEROS = 0, FEDB_INIT_TORCH_DEFAULT = 1, FEDB_INIT_SKLEARN_GLOROT = 2 };
+
+/* One simulated client of one federation ("group").  The reference has one OS process per
+ * client (C:30-46, S:11-15); here a client is a row of this table and all of them are
+ * trained by the same grouped launches.  Groups of one federation are contiguous. */
+typedef struct FedbGroup {
+  int32_t n_layers;
+  int32_t dims[FEDB_MAX_LAYERS + 1]; /* in, h1.., out (out = #classes, or 1 for sigmoid) */
+  int32_t head;
+  int32_t act;
+  int32_t slab_size;   /* P: padded floats per client, multiple of 32 */
+  int32_t fed;         /* federation index */
+  int64_t slab_off;    /* float offset of this client's slab in the params/m/v arenas */
+  int64_t idx_off;     /* offset of this client's shard in the row-index array */
+  int32_t n_rows;      /* shard length */
+  int32_t batch_size;  /* 0 = full batch (C:63-73); 200 = sklearn default (SK:691-692) */
+  int32_t opt;
+  int32_t nesterov;
+  float lr, beta1, beta2, eps;
+  float momentum;
+  float alpha;         /* L2 penalty, sklearn semantics (SK:235, SK:353-361) */
+  int32_t lr_step_size; /* StepLR (C:46); 0 = constant */
+  float lr_gamma;
+  float agg_num;       /* FedAvg weight numerator (n_k, C:110-115) or 1 (S:114-117) */
+  float agg_den;       /* denominator (N, or number of clients) */
+  int64_t scratch_off; /* float offset of this client's partial-gradient records */
+  int32_t max_tiles;   /* records reserved at scratch_off, each slab_size+FEDB_LOSS_SLOTS floats */
+  int32_t client;      /* client index inside the federation */
+} FedbGroup;
+
+/* One federation (one FedAvg problem; the grid search packs 90 of them, H:83-84). */
+typedef struct FedbFed {
+  int32_t first_group;
+  int32_t n_clients;
+  int32_t slab_size;
+  int32_t n_classes;
+  int64_t global_off;  /* float offset of the federation's global slab in the global arena */
+  int32_t metric_mode; /* mean of local metrics (C:169) or pooled predictions (S:130-134) */
+  int32_t patience;    /* C:122 termination_patience; 0 disables early stopping */
+  float atol, rtol;    /* np.allclose(atol=tolerance) with its default rtol=1e-5 (C:181-184) */
+  int32_t max_rounds;  /* capacity of the history buffers */
+  int32_t pad_;
+} FedbFed;
+
+/* Device-resident, kernel-updated state of a federation. */
+typedef struct FedbFedState {
+  int32_t stop;      /* set at the top of the round after stop_pending was raised (C:132-136) */
+  int32_t stop_pending;
+  int32_t round;     /* rounds started so far */
+  int32_t count;     /* C:124 termination_count */
+  int32_t has_anchor;
+  int32_t pad_;
+  double anchor[4];  /* C:125 prev_metric */
+  double last[4];    /* last global metrics */
+} FedbFedState;
+
+/* Evaluate `n_rows` rows (indices at idx_off) with the parameters at slab_off, using the
+ * shape of `group`; counts go to confusion slot `conf_slot`. */
+typedef struct FedbEvalJob {
+  int32_t group;
+  int32_t n_rows;
+  int64_t slab_off;
+  int64_t idx_off;
+  int32_t conf_slot;
+  int32_t from_global; /* 1: slab_off indexes the global arena instead of the params arena */
+} FedbEvalJob;
+
+typedef struct FedbTile {
+  int32_t owner; /* group (training) or job (evaluation) */
+  int32_t tile;  /* tile index inside the owner's current batch */
+} FedbTile;
+
+const char* fedb_last_error(void);
+int fedb_version(void);
+void fedb_struct_sizes(int32_t* out5); /* sizeof of the five structs above, for binding checks */
+/* Dynamic shared memory (bytes) k_fwd_bwd / k_eval need for a model; <0 if it cannot run. */
+int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers);
+int32_t fedb_batch_stats_stride(int32_t max_slab);
+
+/* K4 — parameter init (C:18-21 torch default; SK:445-460 Glorot).  Philox4x32-10, key =
+ * seed, counter = (element/4, stream, 0, 0).  streams[g] < 0 leaves group g untouched. */
+int fedb_init_params(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, float* params,
+                     const int32_t* streams, int32_t kind, uint64_t seed, void* stream);
+
+/* Top of a round: promote stop_pending -> stop, count the round, clear the confusion
+ * counters of the federation's slots (C:130-142). conf_slots_per_fed slots per federation. */
+int fedb_round_begin(const FedbFed* feds, FedbFedState* state, int32_t n_feds, int32_t* conf,
+                     int32_t conf_slots_total, void* stream);
+
+/* Per-epoch reshuffle of every client's shard order (SK:704-718): order_out = shard indices
+ * permuted by a keyed Feistel bijection of (seed, group, epoch[group]). */
+int fedb_shuffle(const FedbGroup* groups, int32_t n_groups, const int32_t* idx_in, int32_t* idx_out,
+                 const int32_t* epoch, const int32_t* active, uint64_t seed, void* stream);
+
+/* K2 (SIMT fp32) part 1 — forward, loss, backward of one optimizer step for every group:
+ * per 32-row tile, writes a partial-gradient record (+ loss sum) to `scratch`
+ * (C:68-71; SK:301-393).  batch = minibatch index inside the epoch (0 for full batch). */
+int fedb_fwd_bwd(const FedbGroup* groups, const FedbTile* tiles, int32_t n_tiles, const float* params,
+                 const float* X, int32_t ldx, const int32_t* y, const int32_t* idx, int32_t batch,
+                 float* scratch, int32_t* step, const int32_t* active, const FedbFedState* fed_state,
+                 int64_t smem_bytes, void* stream);
+
+/* K2 part 2 — fixed-order reduction of the tile records, L2, optimizer update (C:72-73 Adam +
+ * StepLR; SKO AdamOptimizer / SGDOptimizer).  loss_out[g] = mean data loss of the step;
+ * batch_stats (optional; fedb_batch_stats_stride(max_slab) doubles per (group, batch)) receives
+ * {sum of row losses, n_b, per-block sum W^2...} for the sklearn stopping rule (SK:353-361). */
+int fedb_reduce_opt(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, float* params, float* m,
+                    float* v, const float* scratch, int32_t batch, const int32_t* step,
+                    const int32_t* active, const FedbFedState* fed_state, float* loss_out,
+                    double* batch_stats, int32_t max_batches, void* stream);
+
+/* End of an sklearn-style epoch: loss curve, tol / n_iter_no_change rule (SK:750-777). */
+int fedb_epoch_end(const FedbGroup* groups, int32_t n_groups, const double* batch_stats,
+                   int32_t max_batches, int32_t max_slab, double tol, int32_t n_iter_no_change, int32_t max_iter,
+                   int32_t* active, int32_t* epoch, int32_t* no_improve, double* best_loss,
+                   double* last_loss, void* stream);
+
+/* K3 — forward + argmax / threshold + confusion counts (C:75-83, S:104; SK:1283-1290). */
+int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const FedbTile* tiles, int32_t n_tiles,
+              const float* params, const float* global, const float* X, int32_t ldx, const int32_t* y,
+              const int32_t* idx, int32_t* conf, const FedbFedState* fed_state, int64_t smem_bytes,
+              void* stream);
+
+/* K1 (single GPU) + K5 — FedAvg: global = sum_k (w_k * n_k) / N in client order (C:108-116;
+ * unweighted: S:114-117, H:37), written to the global arena and back into every client slab
+ * (C:119-120); block 0 of each federation also turns the round's confusion counts into
+ * accuracy / weighted precision / recall / F1 (C:85-90), appends them to the history and
+ * runs the early-stop rule (C:181-192).  hist_local: [max_rounds][n_groups][4] floats,
+ * hist_global: [n_feds][max_rounds][4].  write_back=0 leaves client slabs untouched. */
+int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
+                int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
+                float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDB200_H */
