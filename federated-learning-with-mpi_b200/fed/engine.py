@@ -400,3 +400,55 @@ class FedEngine:
             self.params[o: o + n].copy_(torch.from_numpy(opt["params"]).reshape(-1))
             self.step[gs[0]: gs[0] + len(gs)].copy_(torch.from_numpy(opt["step"]))
         return meta
+
+    # ------------------------------------------------------------------ end-to-end stepping
+    def pinned_train_inputs(self):
+        """Pinned host copies of the training rows / labels, in the device layout (features
+        padded to ``ldx``) — the per-step inputs of :meth:`step_e2e`."""
+        xh = torch.empty((self.n_train, self.ldx), dtype=torch.float32).pin_memory() if self.device.type == "cuda" \
+            else torch.empty((self.n_train, self.ldx), dtype=torch.float32)
+        yh = torch.empty(self.n_train, dtype=torch.int32)
+        yh = yh.pin_memory() if self.device.type == "cuda" else yh
+        xh.copy_(self.X[: self.n_train].cpu())
+        yh.copy_(self.y[: self.n_train].cpu())
+        return xh, yh
+
+    def step_e2e(self, x_host: torch.Tensor, y_host: torch.Tensor) -> np.ndarray:
+        """One round the way a caller that streams data would run it: upload this step's
+        inputs from (pinned) host memory, run the round, read the round's result (federation
+        state: stop flag + the four global metrics) back to the host.  Returns the
+        ``FedbFedState`` records.  This mirrors what the reference does every round
+        (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic."""
+        self.X[: self.n_train].copy_(x_host, non_blocking=True)
+        self.y[: self.n_train].copy_(y_host, non_blocking=True)
+        if self.device.type == "cuda":
+            if "roundx1" not in self._graphs:
+                snap = self._snapshot()
+                self._graph("round", self.enqueue_round, 1)
+                self._restore(snap)
+            self._graphs["roundx1"].replay()
+            if not hasattr(self, "_state_pinned"):
+                self._state_pinned = torch.empty(self.fed_state.numel(), dtype=torch.uint8).pin_memory()
+            self._state_pinned.copy_(self.fed_state, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return self._state_pinned.numpy().view(nat.FEDSTATE_DTYPE)
+        self.enqueue_round()
+        return self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
+
+    def e2e_bytes(self):
+        return self.n_train * self.ldx * 4 + self.n_train * 4, int(self.fed_state.numel())
+
+    # ------------------------------------------------------------------- bench conveniences
+    precision_name = "fp32"
+    kernel_names = ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]
+
+    def step_graph(self) -> None:
+        """Enqueue exactly one round (graph replay on CUDA); no host synchronisation."""
+        if self.device.type != "cuda":
+            self.enqueue_round()
+            return
+        if "roundx1" not in self._graphs:
+            snap = self._snapshot()
+            self._graph("round", self.enqueue_round, 1)
+            self._restore(snap)
+        self._graphs["roundx1"].replay()
