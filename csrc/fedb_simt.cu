@@ -778,3 +778,70 @@ extern "C" int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFed
   FEDB_LAUNCH_OK();
   return FEDB_OK;
 }
+
+// =========================================================================================
+// Allocation-free local step
+// =========================================================================================
+// Scratch for fedb_local_step_noalloc.  It lives in the library image, so every GPU that loads
+// libfedb200.so carries these 16 MiB from load until the process exits, whether or not the entry
+// point is ever called.  In host code `g_noalloc_scratch` is only a handle for the runtime: the
+// address kernels may dereference is the one cudaGetSymbolAddress returns for the current device.
+#define FEDB_NOALLOC_SCRATCH_FLOATS (4u * 1024u * 1024u)
+static __device__ __align__(256) float g_noalloc_scratch[FEDB_NOALLOC_SCRATCH_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+}  // namespace
+
+extern "C" int64_t fedb_noalloc_scratch_floats(void) { return (int64_t)FEDB_NOALLOC_SCRATCH_FLOATS; }
+
+extern "C" int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbGroup* groups_dev, int32_t n_groups,
+                                       const FedbTile* tiles, int32_t n_tiles, int32_t max_slab, float* params, float* m,
+                                       float* v, const float* X, int32_t ldx, const int32_t* y, const int32_t* idx,
+                                       int32_t batch, int32_t* step, const int32_t* active,
+                                       const FedbFedState* fed_state, float* loss_out, int64_t smem_bytes,
+                                       void* stream) {
+  FEDB_REQUIRE(groups_host && groups_dev && n_groups > 0 && n_tiles > 0 && max_slab > 0, "bad arguments");
+  FEDB_REQUIRE(ldx % 4 == 0, "ldx must be a multiple of 4");
+  FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
+  // The records of all groups must fit in the fixed array: check the host copy of the table.
+  int64_t need = 0;
+  for (int g = 0; g < n_groups; ++g) {
+    const FedbGroup& G = groups_host[g];
+    if (G.scratch_off < 0 || G.max_tiles < 0 || G.slab_size <= 0)
+      return set_err(FEDB_E_ARG, "fedb_local_step_noalloc: malformed group table");
+    const int64_t end = G.scratch_off + (int64_t)G.max_tiles * (G.slab_size + FEDB_LOSS_SLOTS);
+    if (end > need) need = end;
+  }
+  if (need > (int64_t)FEDB_NOALLOC_SCRATCH_FLOATS) {
+    snprintf(g_err, sizeof(g_err),
+             "fedb_local_step_noalloc: this step needs %lld floats of gradient records but the built-in scratch holds "
+             "%lld; use fedb_fwd_bwd + fedb_reduce_opt with a caller-provided buffer",
+             (long long)need, (long long)FEDB_NOALLOC_SCRATCH_FLOATS);
+    return FEDB_E_UNSUPPORTED;
+  }
+  int dev = -1;
+  FEDB_CUDA_OK(cudaGetDevice(&dev));
+  FEDB_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  if (g_noalloc_ptr[dev] == nullptr) {
+    // Once per device, with that device current: translate the symbol into a device address.
+    float* p = nullptr;
+    FEDB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    FEDB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  float* scratch = g_noalloc_ptr[dev];
+  // Nothing in the scratch has to start at zero: k_fwd_bwd overwrites every float of every record
+  // (and its loss slot) that k_reduce_opt reads for the same step, so stale contents of an earlier
+  // call are never observed.
+  if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
+  k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups_dev, tiles, params, X, ldx, y, idx, batch,
+                                                                     scratch, step, active, fed_state);
+  FEDB_LAUNCH_OK();
+  dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_groups);
+  k_reduce_opt<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups_dev, params, m, v, scratch, batch, step, active,
+                                                            fed_state, loss_out, nullptr, 0);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}

@@ -166,6 +166,36 @@ int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* stat
                 float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
                 void* stream);
 
+/* One optimizer step of every group (the work of fedb_fwd_bwd followed by fedb_reduce_opt) for
+ * callers that must not allocate device memory.  No counterpart in the reference.
+ *
+ * Who needs it: a host that has handed all device memory to its own pool up front (an inference
+ * server, a simulator with a fixed budget), code that runs where cudaMalloc is off limits because
+ * it synchronises the whole device (a latency-critical loop, a callback on a stream), and
+ * embedders that may not link an allocator at all.  Such callers own params/m/v/X/... already, but
+ * the step also needs room for per-tile gradient records; here that room is a fixed 16 MiB array
+ * inside the library (fedb_noalloc_scratch_floats() floats), resident on every GPU that loads the
+ * library until the process exits.  The call performs no cudaMalloc/cudaFree and uses no allocating
+ * library routine.
+ *
+ * groups_host is a host copy of the table at groups_dev; it is used to check that every group's
+ * records (scratch_off + max_tiles * (slab_size + FEDB_LOSS_SLOTS)) fit in the array.  A step that
+ * needs more returns FEDB_E_UNSUPPORTED with an explanatory fedb_last_error(); nothing is launched.
+ *
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ * that device current) and remembers it; make that first call outside any stream capture.
+ * All calls on a device share the one array and it keeps whatever the last call left in it.  The
+ * step does not rely on its initial contents (every record it reads is written first), but two
+ * calls whose kernels can overlap on the GPU — different streams, or different host threads — race
+ * on it: serialise them on one stream.  Results are bit-identical to fedb_fwd_bwd + fedb_reduce_opt
+ * with a caller-provided buffer (batch_stats is not produced). */
+int64_t fedb_noalloc_scratch_floats(void);
+int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbGroup* groups_dev, int32_t n_groups,
+                            const FedbTile* tiles, int32_t n_tiles, int32_t max_slab, float* params, float* m,
+                            float* v, const float* X, int32_t ldx, const int32_t* y, const int32_t* idx,
+                            int32_t batch, int32_t* step, const int32_t* active, const FedbFedState* fed_state,
+                            float* loss_out, int64_t smem_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
