@@ -50,6 +50,19 @@ __host__ __device__ inline SmemPlan smem_plan(const int32_t* dims, int L) {
 
 // z[j][r] = act(b[j] + sum_k a_in[k][r] * W[j][k]);  W row-major [d_out][ld], pad cols zero.
 // Rows j in [d_out, ru4(d_out)) of a_out are written as 0 (they are the next layer's K pad).
+// WS = weights staged in shared memory (plain loads) vs read through L1 from global (__ldg).
+template <bool WS>
+__device__ __forceinline__ float4 ldw4(const float* p) {
+  if constexpr (WS) return *reinterpret_cast<const float4*>(p);
+  else return __ldg(reinterpret_cast<const float4*>(p));
+}
+template <bool WS>
+__device__ __forceinline__ float ldw1(const float* p) {
+  if constexpr (WS) return *p;
+  else return __ldg(p);
+}
+
+template <bool WS>
 __device__ void layer_forward(const float* __restrict__ W, const float* __restrict__ b, int ld, int d_out,
                               const float* a_in, float* a_out, int act, bool apply_act) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -62,7 +75,7 @@ __device__ void layer_forward(const float* __restrict__ W, const float* __restri
     for (int jj = 0; jj < 4; ++jj) {
       int j = min(j0 + jj, d_out - 1);
       w[jj] = W + (size_t)j * ld;
-      acc[jj] = __ldg(b + j);
+      acc[jj] = ldw1<WS>(b + j);
     }
 #pragma unroll 2
     for (int k = 0; k < ld; k += 4) {
@@ -70,7 +83,7 @@ __device__ void layer_forward(const float* __restrict__ W, const float* __restri
       const float a2 = a_in[(k + 2) * LDS + lane], a3 = a_in[(k + 3) * LDS + lane];
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) {
-        const float4 q = __ldg(reinterpret_cast<const float4*>(w[jj] + k));
+        const float4 q = ldw4<WS>(w[jj] + k);
         acc[jj] = fmaf(a0, q.x, acc[jj]);
         acc[jj] = fmaf(a1, q.y, acc[jj]);
         acc[jj] = fmaf(a2, q.z, acc[jj]);
@@ -129,6 +142,7 @@ __device__ void layer_wgrad(const float* dz, const float* a, int d_in_ld, int d_
 }
 
 // dz_prev[k][r] = act'(a_l[k][r]) * sum_j dz[j][r] W[j][k]
+template <bool WS>
 __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d_out, const float* dz,
                             const float* a_l, float* dz_prev, int act) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -139,7 +153,7 @@ __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d
 #pragma unroll 4
     for (int j = 0; j < d_out; ++j) {
       const float d = dz[j * LDS + lane];
-      const float4 q = __ldg(reinterpret_cast<const float4*>(W + (size_t)j * ld + k0));
+      const float4 q = ldw4<WS>(W + (size_t)j * ld + k0);
       acc[0] = fmaf(d, q.x, acc[0]);
       acc[1] = fmaf(d, q.y, acc[1]);
       acc[2] = fmaf(d, q.z, acc[2]);
@@ -173,6 +187,14 @@ __device__ void load_tile(const float* __restrict__ X, int ldx, const int32_t* _
     const int row = __ldg(idx + base + min((int)threadIdx.x, nvalid - 1));
     ylab[threadIdx.x] = __ldg(y + row);
   }
+}
+
+// Cooperative, fully coalesced copy of a client's slab into shared memory (one L2 round trip
+// with every thread's loads in flight) so that the layer loops read weights at smem latency.
+__device__ void stage_weights(const float* __restrict__ src, float* dst, int n_floats) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (int i = threadIdx.x; i < (n_floats >> 2); i += blockDim.x) d4[i] = __ldg(s4 + i);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -274,7 +296,7 @@ __global__ void __launch_bounds__(NTHREADS)
 k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ tiles, const float* __restrict__ params,
           const float* __restrict__ X, int ldx, const int32_t* __restrict__ y, const int32_t* __restrict__ idx,
           int batch, float* __restrict__ scratch, int32_t* __restrict__ step, const int32_t* __restrict__ active,
-          const FedbFedState* __restrict__ fed_state) {
+          const FedbFedState* __restrict__ fed_state, int smem_floats) {
   extern __shared__ __align__(16) float smem[];
   const FedbTile T = tiles[blockIdx.x];
   const int g = T.owner;
@@ -292,6 +314,7 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
   const int L = G.n_layers;
   const SlabLayout lay = slab_layout(G.dims, L);
   const SmemPlan sp = smem_plan(G.dims, L);
+  const bool ws = sp.total_floats + lay.end <= smem_floats;  // weights fit next to the activations
   const float* P = params + G.slab_off;
   float* rec = scratch + G.scratch_off + (size_t)T.tile * (G.slab_size + FEDB_LOSS_SLOTS);
   int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
@@ -299,12 +322,18 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
 
   if (T.tile == 0 && threadIdx.x == 0) step[g] += 1;  // optimizer step counter (t in Adam)
 
+  if (ws) {
+    stage_weights(P, smem + sp.total_floats, lay.end);
+    P = smem + sp.total_floats;
+  }
   load_tile(X, ldx, y, idx, G.idx_off + b0 + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
   __syncthreads();
 
   for (int l = 0; l < L; ++l) {
-    layer_forward(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
-                  smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    if (ws) layer_forward<true>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                                smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    else layer_forward<false>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                              smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
   }
 
@@ -348,9 +377,12 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
   for (int l = L - 1; l >= 0; --l) {
     const float* dzc = smem + sp.dz_off[cur];
     layer_wgrad(dzc, smem + sp.a_off[l], lay.ld[l], G.dims[l + 1], rec + lay.w_off[l], rec + lay.b_off[l]);
-    if (l > 0)
-      layer_dgrad(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
-                  smem + sp.dz_off[cur ^ 1], G.act);
+    if (l > 0) {
+      if (ws) layer_dgrad<true>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+                                smem + sp.dz_off[cur ^ 1], G.act);
+      else layer_dgrad<false>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+                              smem + sp.dz_off[cur ^ 1], G.act);
+    }
     __syncthreads();
     cur ^= 1;
   }
@@ -520,7 +552,7 @@ __global__ void __launch_bounds__(NTHREADS)
 k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ jobs, const FedbTile* __restrict__ tiles,
        const float* __restrict__ params, const float* __restrict__ global, const float* __restrict__ X, int ldx,
        const int32_t* __restrict__ y, const int32_t* __restrict__ idx, int32_t* __restrict__ conf,
-       const FedbFedState* __restrict__ fed_state) {
+       const FedbFedState* __restrict__ fed_state, int smem_floats) {
   extern __shared__ __align__(16) float smem[];
   const FedbTile T = tiles[blockIdx.x];
   const FedbEvalJob J = jobs[T.owner];
@@ -533,12 +565,19 @@ k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ job
   const SlabLayout lay = slab_layout(G.dims, L);
   const SmemPlan sp = smem_plan(G.dims, L);
   const float* P = (J.from_global ? global : params) + J.slab_off;
+  const bool ws = sp.total_floats + lay.end <= smem_floats;
   int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
+  if (ws) {
+    stage_weights(P, smem + sp.total_floats, lay.end);
+    P = smem + sp.total_floats;
+  }
   load_tile(X, ldx, y, idx, J.idx_off + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
   __syncthreads();
   for (int l = 0; l < L; ++l) {
-    layer_forward(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
-                  smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    if (ws) layer_forward<true>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                                smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    else layer_forward<false>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                              smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
   }
   if (threadIdx.x < 32) {
@@ -675,12 +714,20 @@ extern "C" void fedb_struct_sizes(int32_t* out) {
 extern "C" int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers) {
   if (n_layers < 1 || n_layers > FEDB_MAX_LAYERS) return -1;
   const SmemPlan sp = smem_plan(dims, n_layers);
-  const int64_t bytes = (int64_t)sp.total_floats * 4;
+  const SlabLayout lay = slab_layout(dims, n_layers);
+  const int64_t bytes = (int64_t)sp.total_floats * 4, with_w = bytes + (int64_t)lay.end * 4;
+  if (with_w <= 227 * 1024) return with_w;  // weights staged in shared memory
   return bytes <= 227 * 1024 ? bytes : -1;
 }
 
+// Opt in to >48 KB of dynamic shared memory once per function (always the 227 KB maximum, so the
+// call is not repeated inside a stream capture after the first, eager, launch).
 static int set_smem(const void* fn, int64_t bytes) {
-  if (bytes > 48 * 1024) FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  static const void* done[8] = {nullptr};
+  if (bytes <= 48 * 1024) return FEDB_OK;
+  for (int i = 0; i < 8; ++i) if (done[i] == fn) return FEDB_OK;
+  FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  for (int i = 0; i < 8; ++i) if (done[i] == nullptr) { done[i] = fn; break; }
   return FEDB_OK;
 }
 
@@ -725,7 +772,8 @@ extern "C" int fedb_fwd_bwd(const FedbGroup* groups, const FedbTile* tiles, int3
   FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
   if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
   k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, tiles, params, X, ldx, y, idx, batch,
-                                                                     scratch, step, active, fed_state);
+                                                                     scratch, step, active, fed_state,
+                                                                     (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();
   return FEDB_OK;
 }
@@ -762,7 +810,7 @@ extern "C" int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const
   FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
   if (int rc = set_smem((const void*)k_eval, smem_bytes)) return rc;
   k_eval<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, jobs, tiles, params, global, X, ldx, y, idx,
-                                                                  conf, fed_state);
+                                                                  conf, fed_state, (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();
   return FEDB_OK;
 }
@@ -837,7 +885,8 @@ extern "C" int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbG
   // call are never observed.
   if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
   k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups_dev, tiles, params, X, ldx, y, idx, batch,
-                                                                     scratch, step, active, fed_state);
+                                                                     scratch, step, active, fed_state,
+                                                                     (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();
   dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_groups);
   k_reduce_opt<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups_dev, params, m, v, scratch, batch, step, active,

@@ -68,6 +68,9 @@ def simt_smem_bytes(dims, n_layers: int) -> int:
     maxw = max([4] + [ru4(x) for x in d[1:]])
     total = (sum(ru4(x) for x in d) + 2 * maxw) * 33 + 64
     b = total * 4
+    n_w = sum(d[l + 1] * ru4(d[l]) + ru4(d[l + 1]) for l in range(n_layers))
+    if b + n_w * 4 <= 227 * 1024:
+        return b + n_w * 4  # room to stage the client's weights in shared memory too
     if b > 227 * 1024:
         raise ValueError(f"MLP {d} needs {b} bytes of shared memory per CTA in the SIMT kernels (max 232448); "
                          "use the wide (layer-wise tcgen05 GEMM) path")
