@@ -108,4 +108,49 @@ __device__ __forceinline__ float act_bwd(float a, int act) {
   }
 }
 
+// ---- optimizer arithmetic shared by the SIMT and tensor-core kernels ----------------------
+struct StepScalars {
+  float lr_eff;   // torch Adam: lr / (1 - b1^t) ; sklearn Adam: lr*sqrt(1-b2^t)/(1-b1^t) ; SGD: lr
+  float inv_sqrt_bc2;  // torch Adam: 1/sqrt(1 - b2^t)
+};
+
+__device__ inline StepScalars step_scalars(const FedbGroup& G, int t) {
+  StepScalars s;
+  double lr = (double)G.lr;
+  if (G.lr_step_size > 0) lr *= pow((double)G.lr_gamma, (double)((t - 1) / G.lr_step_size));
+  if (G.opt == FEDB_OPT_ADAM_TORCH) {
+    const double bc1 = 1.0 - pow((double)G.beta1, (double)t), bc2 = 1.0 - pow((double)G.beta2, (double)t);
+    s.lr_eff = (float)(lr / bc1);
+    s.inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  } else if (G.opt == FEDB_OPT_ADAM_SKLEARN) {
+    const double bc1 = 1.0 - pow((double)G.beta1, (double)t), bc2 = 1.0 - pow((double)G.beta2, (double)t);
+    s.lr_eff = (float)(lr * sqrt(bc2) / bc1);
+    s.inv_sqrt_bc2 = 1.f;
+  } else {
+    s.lr_eff = (float)lr;
+    s.inv_sqrt_bc2 = 1.f;
+  }
+  return s;
+}
+
+__device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalars& sc, float w, float g, float& m,
+                                            float& v) {
+  if (G.opt == FEDB_OPT_ADAM_TORCH) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    const float denom = sqrtf(v) * sc.inv_sqrt_bc2 + G.eps;
+    return w - sc.lr_eff * (m / denom);
+  } else if (G.opt == FEDB_OPT_ADAM_SKLEARN) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    return w - sc.lr_eff * m / (sqrtf(v) + G.eps);
+  } else {
+    // SKO SGDOptimizer: velocity = momentum*velocity - lr*g ; nesterov looks ahead
+    m = G.momentum * m - sc.lr_eff * g;
+    const float upd = G.nesterov ? (G.momentum * m - sc.lr_eff * g) : m;
+    return w + upd;
+  }
+}
+
+
 }  // namespace fedb

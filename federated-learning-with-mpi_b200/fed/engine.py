@@ -37,8 +37,9 @@ def _ru(x: int, m: int) -> int:
 class FedEngine:
     def __init__(self, problems: Sequence[FedProblem], X_train: np.ndarray, y_train: np.ndarray,
                  X_test: Optional[np.ndarray] = None, y_test: Optional[np.ndarray] = None,
-                 device: Optional[str] = None, max_rounds: int = 300, seed: int = 0):
+                 device: Optional[str] = None, max_rounds: int = 300, seed: int = 0, precision: Optional[str] = None):
         self.problems = list(problems)
+        self._precision_req = precision
         if device is None:
             device = "cuda" if torch.cuda.is_available() else "cpu"
         self.device = torch.device(device)
@@ -62,7 +63,30 @@ class FedEngine:
         self._build_tables()
         self._alloc_state()
         self._graphs: Dict[str, object] = {}
+        self._select_precision()
         self.init_params()
+
+    def _select_precision(self) -> None:
+        """'fp32' = SIMT kernels; 'bf16' = fused tcgen05 local-round kernel (bf16 operands, fp32
+        accumulate / master weights / optimizer).  Default: bf16 when every model is eligible and
+        training is full-batch on a GPU, else fp32."""
+        from ..ops import tc
+        full_batch = all(p.hyper.batch_size <= 0 and p.hyper.max_iter <= 0 for p in self.problems)
+        ok = self.device.type == "cuda" and full_batch and tc.tc_eligible(self.tb.groups)
+        req = self._precision_req
+        if req in (None, "auto"):
+            req = "bf16" if ok else "fp32"
+        if req in ("bf16", "tc", "tf32"):
+            if not ok:
+                raise ValueError("the tensor-core path needs a CUDA device, full-batch steps and 3-layer ReLU MLPs with "
+                                 "in<=15, h1<=63, h2<=256, out<=8")
+            self.precision_name = "bf16"
+            self.tc_cluster = tc.tc_cluster_size(self.tb.groups)
+            self.kernel_names = ["k_round_begin", "k_local_round_tc", "k_fedavg"]
+        elif req == "fp32":
+            self.precision_name = "fp32"
+        else:
+            raise ValueError(f"unknown precision {req!r}")
 
     # ------------------------------------------------------------------------------ tables
     def _build_tables(self) -> None:
@@ -218,15 +242,22 @@ class FedEngine:
         """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg."""
         K.round_begin(self.tb, self.fed_state, self.conf)
         E = max(p.hyper.local_epochs for p in self.problems)
-        for _ in range(E):
-            for b in range(self.n_batches):
-                self.enqueue_local_step(b)
-        self.enqueue_eval_local()
+        if self.precision_name == "bf16":
+            from ..ops import tc
+            tc.local_round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step,
+                              self.active, self.fed_state, self.loss, self.conf, 0, E, True)
+        else:
+            for _ in range(E):
+                for b in range(self.n_batches):
+                    self.enqueue_local_step(b)
+            self.enqueue_eval_local()
         self.enqueue_aggregate()
 
     @property
     def launches_per_round(self) -> int:
         E = max(p.hyper.local_epochs for p in self.problems)
+        if self.precision_name == "bf16":
+            return 3
         return 1 + 2 * E * self.n_batches + 2
 
     def _graph(self, key: str, fn, unroll: int = 1):

@@ -216,8 +216,14 @@ def _declare(l: ctypes.CDLL) -> None:
             fn.restype = res
 
 
-# filled in by the modules that own the corresponding kernels (ops/tc.py, parallel/p2p.py, …)
-OPTIONAL_SIGS = {}
+# entry points that exist only once their translation unit is part of the build
+OPTIONAL_SIGS = {
+    "fedb_tc_probe": ([_P, _P, ctypes.POINTER(_I32), _P, _P], _I32),
+    "fedb_tc_probe_args_size": ([], _I32),
+    "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
+    "fedb_tc_smem_bytes": ([], _I64),
+    "fedb_noalloc_scratch_floats": ([], _I64),
+}
 
 
 def ptr(t) -> Optional[int]:

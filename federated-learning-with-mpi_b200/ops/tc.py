@@ -11,8 +11,6 @@ import torch
 from . import _native as nat
 
 _P, _I32 = ctypes.c_void_p, ctypes.c_int32
-nat.OPTIONAL_SIGS["fedb_tc_probe"] = ([_P, _P, ctypes.POINTER(_I32), _P, _P], _I32)
-nat.OPTIONAL_SIGS["fedb_tc_probe_args_size"] = ([], _I32)
 
 PANEL_COLS = 64
 
@@ -66,3 +64,40 @@ def probe(a_img: torch.Tensor, b_img: torch.Tensor, N: int, a_steps: Sequence[in
                                 nat.cuda_stream()))
     torch.cuda.synchronize()
     return out
+
+
+# ---- fused tensor-core local round (csrc/fedb_tc.cu) -----------------------------------------
+TC_ROWS = 128
+
+
+def tc_eligible(groups: np.ndarray) -> bool:
+    """True when every group fits the fused tcgen05 kernel: 2 hidden ReLU layers,
+    in <= 15, h1 <= 63, h2 <= 256, out <= 8, slab small enough for the smem staging area."""
+    for g in groups:
+        d = g["dims"]
+        if int(g["n_layers"]) != 3 or int(g["act"]) != nat.ACT_IDS["relu"]:
+            return False
+        if not (d[0] <= 15 and d[1] <= 63 and d[2] <= 256 and d[3] <= 8):
+            return False
+        if int(g["slab_size"]) > 24000:
+            return False
+    return True
+
+
+def tc_cluster_size(groups: np.ndarray) -> int:
+    rows = 1
+    for g in groups:
+        n = int(g["n_rows"])
+        rows = max(rows, min(int(g["batch_size"]), n) if int(g["batch_size"]) > 0 else n)
+    return int(min(8, max(1, (rows + TC_ROWS - 1) // TC_ROWS)))
+
+
+def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf,
+                   batch: int = 0, n_steps: int = 1, do_eval: bool = True) -> None:
+    lib = nat.lib(required=True)
+    nat.check(lib.fedb_local_round_tc(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y),
+                                      nat.ptr(idx), nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active),
+                                      nat.ptr(fed_state), nat.ptr(loss_out), nat.ptr(conf), batch, n_steps, int(do_eval),
+                                      nat.cuda_stream()))
+    from . import kernels as K
+    K._count()

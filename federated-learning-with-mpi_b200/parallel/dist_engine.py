@@ -44,4 +44,4 @@ def make_local_engine(data, rows: Sequence[np.ndarray], max_rounds: int = 300, p
                       patience: int = 0, device: Optional[str] = None) -> FedEngine:
     X, y, shards = _compact(data, rows)
     prob = FedProblem.custom(data.n_features, data.n_classes, shards, patience=patience)
-    return FedEngine([prob], X, y, data.X_test, data.y_test, device=device, max_rounds=max_rounds)
+    return FedEngine([prob], X, y, data.X_test, data.y_test, device=device, max_rounds=max_rounds, precision=precision)
