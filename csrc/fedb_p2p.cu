@@ -1,0 +1,196 @@
+// K1b: cross-GPU FedAvg inside ONE kernel per rank, over NVLink peer memory — no NCCL call and no
+// separate elementwise kernel on the aggregation path (the reference's gather -> rank-0 mean ->
+// bcast: C:101-120, S:108-122, H:24-46).
+//
+// Every rank owns a "symmetric" buffer (same layout on every GPU, mapped into every peer through
+// CUDA IPC):   partial[2][P_total] fp32 | conf[2][slots][64] int32 | flags[8] u64
+// One launch per round on every rank:
+//   A  local reduction: partial[par] = sum over the rank's resident clients of (w_k * n_k) / N,
+//      in client order (the reference's arithmetic, term by term); local confusion counts are
+//      published next to it.
+//   -  grid barrier, then flag words are stored (st.release.sys) into EVERY peer's buffer.
+//   B  spin (ld.acquire.sys, bounded by a timeout) until every peer's flag for this round arrived.
+//   C  every rank sums the R partials in rank order with peer loads (ld.relaxed.sys over NVLink;
+//      identical order on every rank => identical global model everywhere, no broadcast needed),
+//      writes the global slab and writes it back into each resident client's slab; block 0 also
+//      gathers all clients' confusion counts from the peers and runs the metric + early-stop
+//      bookkeeping redundantly-but-identically on every rank.
+// Buffers are double-buffered by round parity, so one cross-GPU barrier per round suffices.
+//
+// The same kernel runs R emulated ranks on ONE GPU (gridDim.y = R, cooperative launch), which is
+// how the single-GPU test-suite exercises the protocol (ranks must never be separate launches on
+// one device: nothing guarantees they are co-resident).
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace fedb {
+
+constexpr int P2P_THREADS = 256;
+
+__device__ __forceinline__ uint64_t ld_acquire_sys_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(uint64_t* p, uint64_t v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_relaxed_sys_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int ld_relaxed_sys_i32(const int32_t* p) {
+  int v;
+  asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* __restrict__ ranks) {
+  const FedbP2PRank& R = ranks[blockIdx.y];
+  const int tid = threadIdx.x;
+  const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
+  const int par = (int)(seq & 1);
+  const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  float* my_partial = reinterpret_cast<float*>(R.sym[R.rank] + R.sym_partial_off) + (int64_t)par * R.global_total;
+  int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + par * conf_stride;
+  uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
+  const int gthreads = gridDim.x * blockDim.x, gtid = blockIdx.x * blockDim.x + tid;
+
+  // ---- A: local weighted partial sums -----------------------------------------------------------
+  for (int f = 0; f < R.n_feds; ++f) {
+    const FedbFed& F = R.feds[f];
+    if (R.fed_state[f].stop) continue;
+    for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
+      const int e = e4 * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < F.n_clients; ++k) {
+        const FedbGroup& G = R.groups[F.first_group + k];
+        const float4 w = *reinterpret_cast<const float4*>(R.params + G.slab_off + e);
+        acc.x += __fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den);
+        acc.y += __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den);
+        acc.z += __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den);
+        acc.w += __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den);
+      }
+      *reinterpret_cast<float4*>(my_partial + F.global_off + e) = acc;
+    }
+  }
+  if (blockIdx.x == 0)
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += blockDim.x) my_confx[i] = R.conf[i];
+  __threadfence_system();
+
+  // ---- grid barrier among this rank's blocks, then publish the arrival flag to every peer --------
+  __syncthreads();
+  bool timed_out = false;
+  const long long t0 = clock64();
+  if (tid == 0) {
+    atomicAdd(R.bar, 1u);
+    const uint32_t target = (uint32_t)((seq + 1) * gridDim.x);
+    while ((int32_t)(ld_acquire_gpu_u32(R.bar) - target) < 0)
+      if (clock64() - t0 > R.timeout_cycles) { timed_out = true; break; }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0 && tid < R.world) {
+    uint64_t* peer_flags = reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off);
+    st_release_sys_u64(peer_flags + R.rank, seq + 1);
+  }
+  // ---- B: wait for every peer ---------------------------------------------------------------------
+  if (tid < R.world) {
+    while (ld_acquire_sys_u64(my_flags + tid) < seq + 1)
+      if (clock64() - t0 > R.timeout_cycles) { timed_out = true; break; }
+  }
+  if (timed_out) *R.err = FEDB_E_TIMEOUT;
+  __syncthreads();
+
+  // ---- C: sum the partials of all ranks in rank order; write global + every resident client -------
+  for (int f = 0; f < R.n_feds; ++f) {
+    const FedbFed& F = R.feds[f];
+    if (R.fed_state[f].stop) continue;
+    for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
+      const int e = e4 * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < R.world; ++q) {
+        const float* pq = reinterpret_cast<const float*>(R.sym[q] + R.sym_partial_off) + (int64_t)par * R.global_total;
+        const float4 p = ld_relaxed_sys_f4(pq + F.global_off + e);
+        acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+      }
+      *reinterpret_cast<float4*>(R.global + F.global_off + e) = acc;
+      if (R.write_back)
+        for (int k = 0; k < F.n_clients; ++k)
+          *reinterpret_cast<float4*>(R.params + R.groups[F.first_group + k].slab_off + e) = acc;
+    }
+  }
+  // ---- metrics + early stop, identically on every rank (C:165-192) --------------------------------
+  if (blockIdx.x == 0 && R.do_metrics) {
+    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += blockDim.x) {
+      const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
+      const int q = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[q] + R.sym_conf_off) + par * conf_stride;
+      R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
+    }
+    __syncthreads();
+    if (tid == 0)
+      for (int f = 0; f < R.n_feds; ++f)
+        if (!R.fed_state[f].stop)
+          round_metrics(nullptr, R.feds_global[f], R.fed_state[f], f, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global);
+  }
+  if (blockIdx.x == 0 && tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+extern "C" int32_t fedb_p2p_rank_size(void) { return (int32_t)sizeof(FedbP2PRank); }
+
+extern "C" int fedb_fedavg_p2p(const FedbP2PRank* ranks_dev, int32_t n_ranks_here, int32_t blocks_x, void* stream) {
+  FEDB_REQUIRE(n_ranks_here >= 1 && blocks_x >= 1, "bad grid");
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(blocks_x, n_ranks_here);
+  cfg.blockDim = dim3(P2P_THREADS);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeCooperative;  // blocks spin on each other: they must be co-resident
+  at[0].val.cooperative = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  FEDB_CUDA_OK(cudaLaunchKernelEx(&cfg, k_fedavg_p2p, ranks_dev));
+  return FEDB_OK;
+}
+
+// ---- symmetric memory plumbing (CUDA IPC; handles travel through torch.distributed) --------------
+extern "C" int fedb_symm_alloc(int64_t bytes, void** out) {
+  FEDB_REQUIRE(bytes > 0 && out, "bad arguments");
+  FEDB_CUDA_OK(cudaMalloc(out, (size_t)bytes));
+  FEDB_CUDA_OK(cudaMemset(*out, 0, (size_t)bytes));
+  FEDB_CUDA_OK(cudaDeviceSynchronize());
+  return FEDB_OK;
+}
+extern "C" int fedb_symm_free(void* p) {
+  FEDB_CUDA_OK(cudaFree(p));
+  return FEDB_OK;
+}
+extern "C" int fedb_ipc_get_handle(void* p, uint8_t* handle64) {
+  cudaIpcMemHandle_t h;
+  FEDB_CUDA_OK(cudaIpcGetMemHandle(&h, p));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return FEDB_OK;
+}
+extern "C" int fedb_ipc_open_handle(const uint8_t* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  FEDB_CUDA_OK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return FEDB_OK;
+}
+extern "C" int fedb_ipc_close_handle(void* p) {
+  FEDB_CUDA_OK(cudaIpcCloseMemHandle(p));
+  return FEDB_OK;
+}

@@ -563,68 +563,6 @@ k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ job
 // ---------------------------------------------------------------------------------------
 // K1 + K5: FedAvg, metrics, early stop
 // ---------------------------------------------------------------------------------------
-__device__ void metrics_from_conf(const int32_t* cm, int C, double out[4]) {
-  double total = 0, tr = 0;
-  double sup[FEDB_MAX_CLASSES], prd[FEDB_MAX_CLASSES];
-  for (int c = 0; c < C; ++c) { sup[c] = 0; prd[c] = 0; }
-  for (int i = 0; i < C; ++i)
-    for (int j = 0; j < C; ++j) {
-      const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
-      total += x; sup[i] += x; prd[j] += x;
-      if (i == j) tr += x;
-    }
-  out[0] = out[1] = out[2] = out[3] = 0.0;
-  if (total == 0) return;
-  out[0] = tr / total;
-  for (int c = 0; c < C; ++c) {
-    const double tp = (double)cm[c * FEDB_MAX_CLASSES + c];
-    const double w = sup[c] / total;
-    const double p = prd[c] > 0 ? tp / prd[c] : 0.0;
-    const double r = sup[c] > 0 ? tp / sup[c] : 0.0;
-    const double den = sup[c] + prd[c];
-    const double f = den > 0 ? 2.0 * tp / den : 0.0;
-    out[1] += p * w; out[2] += r * w; out[3] += f * w;
-  }
-}
-
-__device__ __noinline__ void round_metrics(const FedbGroup* groups, const FedbFed& F, FedbFedState& S, int f, int n_groups,
-                              const int32_t* conf, float* hist_local, float* hist_global) {
-  const int C = F.n_classes;
-  const int r = S.round - 1;  // 0-based index of the round in progress
-  double glob[4] = {0, 0, 0, 0};
-  int32_t pooled[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
-  for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] = 0;
-  for (int k = 0; k < F.n_clients; ++k) {
-    const int g = F.first_group + k;
-    const int32_t* cm = conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
-    double mloc[4];
-    metrics_from_conf(cm, C, mloc);
-    if (hist_local && r >= 0 && r < F.max_rounds)
-      for (int i = 0; i < 4; ++i) hist_local[((size_t)r * n_groups + g) * 4 + i] = (float)mloc[i];
-    for (int i = 0; i < 4; ++i) glob[i] += mloc[i];
-    for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] += cm[i];
-  }
-  if (F.metric_mode == FEDB_METRIC_POOLED) metrics_from_conf(pooled, C, glob);
-  else for (int i = 0; i < 4; ++i) glob[i] /= (double)F.n_clients;
-  for (int i = 0; i < 4; ++i) S.last[i] = glob[i];
-  if (hist_global && r >= 0 && r < F.max_rounds)
-    for (int i = 0; i < 4; ++i) hist_global[((size_t)f * F.max_rounds + r) * 4 + i] = (float)glob[i];
-  if (F.patience > 0) {
-    bool close = S.has_anchor != 0;
-    if (close)
-      for (int i = 0; i < 4; ++i)
-        close = close && (fabs(glob[i] - S.anchor[i]) <= (double)F.atol + (double)F.rtol * fabs(S.anchor[i]));
-    if (close) {
-      S.count -= 1;
-      if (S.count == 0) S.stop_pending = 1;
-    } else {
-      for (int i = 0; i < 4; ++i) S.anchor[i] = glob[i];
-      S.has_anchor = 1;
-      S.count = F.patience;
-    }
-  }
-}
-
 __global__ void __launch_bounds__(NTHREADS)
 k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds, FedbFedState* __restrict__ state,
          int n_groups, float* __restrict__ params, float* __restrict__ global, const int32_t* __restrict__ conf,

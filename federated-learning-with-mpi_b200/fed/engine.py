@@ -102,7 +102,7 @@ class FedEngine:
             s, h = p.spec, p.hyper
             P = s.slab_size
             sizes = [len(sh) for sh in p.shards]
-            total = float(sum(sizes))
+            total = float(sum(sizes)) if p.total_weight is None else float(p.total_weight)
             feds[f] = (g, p.n_clients, P, s.n_classes, global_off, nat.METRIC_IDS[p.metric_mode], p.patience,
                        p.atol, p.rtol, self.max_rounds, 0)
             global_off += P
@@ -126,7 +126,7 @@ class FedEngine:
                 if p.weighting == "samples":
                     r["agg_num"], r["agg_den"] = float(len(sh)), total
                 else:
-                    r["agg_num"], r["agg_den"] = 1.0, float(p.n_clients)
+                    r["agg_num"], r["agg_den"] = 1.0, float(p.n_clients if p.total_weight is None else p.total_weight)
                 r["scratch_off"], r["max_tiles"], r["client"] = scratch_off, max_tiles, k
                 slab_off += P
                 idx_off += len(sh)
@@ -214,7 +214,7 @@ class FedEngine:
             for k, gi in enumerate(self.group_of[f]):
                 # one Philox stream per (federation seed, client); identical streams when the
                 # federation asks for a shared init
-                streams[gi] = (p.init_seed * 1000003 + (k if p.init_per_client else 0)) & 0x7FFFFFFF
+                streams[gi] = (p.init_seed * 1000003 + ((k + p.client_offset) if p.init_per_client else 0)) & 0x7FFFFFFF
         for kind, streams in by_kind.items():
             K.init_params(self.tb, self.params, torch.from_numpy(streams).to(self.device), kind, self.seed)
         self.m.zero_()
@@ -240,7 +240,15 @@ class FedEngine:
 
     def enqueue_round(self) -> None:
         """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg."""
+        self.enqueue_round_begin()
+        self.enqueue_local_part()
+        self.enqueue_aggregate()
+
+    def enqueue_round_begin(self) -> None:
         K.round_begin(self.tb, self.fed_state, self.conf)
+
+    def enqueue_local_part(self) -> None:
+        """Everything a round does that involves only resident clients: E local steps + local eval."""
         E = max(p.hyper.local_epochs for p in self.problems)
         if self.precision_name == "bf16":
             from ..ops import tc
@@ -251,7 +259,6 @@ class FedEngine:
                 for b in range(self.n_batches):
                     self.enqueue_local_step(b)
             self.enqueue_eval_local()
-        self.enqueue_aggregate()
 
     @property
     def launches_per_round(self) -> int:

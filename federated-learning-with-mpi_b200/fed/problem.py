@@ -54,6 +54,10 @@ class FedProblem:
     init_seed: int = 0
     init_per_client: bool = True               # reference: every rank draws its own init (C:42)
     name: str = ""
+    # multi-GPU: this process hosts only some clients of the federation; the FedAvg denominator
+    # (total samples N, or total client count) still refers to the whole federation
+    total_weight: Optional[float] = None
+    client_offset: int = 0                     # global index of this process's first client (init streams)
 
     @property
     def n_clients(self) -> int:

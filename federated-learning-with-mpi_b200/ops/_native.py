@@ -223,7 +223,23 @@ OPTIONAL_SIGS = {
     "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
     "fedb_tc_smem_bytes": ([], _I64),
     "fedb_noalloc_scratch_floats": ([], _I64),
+    "fedb_p2p_rank_size": ([], _I32),
+    "fedb_fedavg_p2p": ([_P, _I32, _I32, _P], _I32),
+    "fedb_symm_alloc": ([_I64, ctypes.POINTER(_P)], _I32),
+    "fedb_symm_free": ([_P], _I32),
+    "fedb_ipc_get_handle": ([_P, _P], _I32),
+    "fedb_ipc_open_handle": ([_P, ctypes.POINTER(_P)], _I32),
+    "fedb_ipc_close_handle": ([_P], _I32),
 }
+
+P2PRANK_DTYPE = np.dtype([
+    ("rank", "i4"), ("world", "i4"), ("n_feds", "i4"), ("n_groups_local", "i4"), ("n_groups_total", "i4"),
+    ("conf_slots", "i4"), ("global_total", "i8"), ("groups", "u8"), ("feds", "u8"), ("feds_global", "u8"),
+    ("fed_state", "u8"), ("params", "u8"), ("global", "u8"), ("conf", "u8"), ("conf_all", "u8"), ("hist_local", "u8"),
+    ("hist_global", "u8"), ("conf_src_rank", "u8"), ("conf_src_slot", "u8"), ("sym", "u8", (8,)),
+    ("sym_partial_off", "i8"), ("sym_conf_off", "i8"), ("sym_flag_off", "i8"), ("seq", "u8"), ("bar", "u8"), ("err", "u8"),
+    ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"),
+], align=True)
 
 
 def ptr(t) -> Optional[int]:

@@ -45,3 +45,154 @@ def make_local_engine(data, rows: Sequence[np.ndarray], max_rounds: int = 300, p
     X, y, shards = _compact(data, rows)
     prob = FedProblem.custom(data.n_features, data.n_classes, shards, patience=patience)
     return FedEngine([prob], X, y, data.X_test, data.y_test, device=device, max_rounds=max_rounds, precision=precision)
+
+
+# =================================================================================================
+# multi-GPU
+# =================================================================================================
+from dataclasses import replace as _replace
+from typing import Dict
+
+from ..ops import _native as nat
+from ..ops import kernels as K
+from . import p2p
+
+
+def place_clients(n_clients: int, world: int) -> List[range]:
+    """Contiguous blocks of clients per rank (client k -> rank k*world // n_clients)."""
+    owner = [(k * world) // n_clients for k in range(n_clients)]
+    return [range(owner.index(q), owner.index(q) + owner.count(q)) if q in owner else range(0, 0) for q in range(world)]
+
+
+class DistFedEngine(FedEngine):
+    """A :class:`FedEngine` over the clients placed on this rank, whose aggregation step is the
+    cross-GPU kernel of csrc/fedb_p2p.cu instead of the single-GPU ``k_fedavg``.  Every rank
+    ends each round with the same global model, the same metric history and the same
+    early-stop state (computed redundantly, in the same order, from the same peer data)."""
+
+    def __init__(self, problems: Sequence[FedProblem], X_train: np.ndarray, y_train: np.ndarray, X_test=None, y_test=None,
+                 rank: int = 0, world: int = 1, max_rounds: int = 300, seed: int = 0, precision: Optional[str] = None,
+                 device: Optional[str] = None, sym_ptrs: Optional[Sequence[int]] = None, timeout_s: float = 5.0):
+        self.rank, self.world = rank, world
+        self.global_problems = list(problems)
+        local, used_rows = [], []
+        self._src_rank, self._src_slot, feds_global_rows = [], [], []
+        g_total = 0
+        local_first = 0
+        for f, p in enumerate(problems):
+            blocks = place_clients(p.n_clients, world)
+            mine = blocks[rank]
+            if len(mine) == 0:
+                raise ValueError(f"federation {f} has fewer clients ({p.n_clients}) than ranks ({world})")
+            total = float(sum(len(s) for s in p.shards)) if p.weighting == "samples" else float(p.n_clients)
+            local.append(_replace(p, shards=[p.shards[k] for k in mine], total_weight=total, client_offset=mine[0]))
+            # where every global client's confusion slot lives
+            slot_base = {q: sum(len(place_clients(pp.n_clients, world)[q]) for pp in problems[:f]) for q in range(world)}
+            for q in range(world):
+                for j, _k in enumerate(blocks[q]):
+                    self._src_rank.append(q)
+                    self._src_slot.append(slot_base[q] + j)
+            feds_global_rows.append((g_total, p.n_clients))
+            g_total += p.n_clients
+            local_first += len(mine)
+        self.n_groups_total = g_total
+        # keep only the rows this rank's clients touch
+        rows = np.unique(np.concatenate([s for p in local for s in p.shards]))
+        remap = -np.ones(len(X_train), dtype=np.int64)
+        remap[rows] = np.arange(len(rows))
+        local = [_replace(p, shards=[remap[s].astype(np.int32) for s in p.shards]) for p in local]
+        super().__init__(local, X_train[rows], y_train[rows], X_test, y_test, device=device or "cuda", max_rounds=max_rounds,
+                         seed=seed, precision=precision)
+        d = self.device
+        fg = self.tb.feds.copy()
+        for f, (first, n) in enumerate(feds_global_rows):
+            fg[f]["first_group"], fg[f]["n_clients"] = first, n
+        self.feds_global = K.upload_table(fg, d)
+        self.conf_all = torch.zeros(g_total * p2p.C2, dtype=torch.int32, device=d)
+        self.hist_local = torch.zeros(self.max_rounds * g_total * 4, dtype=torch.float32, device=d)
+        self.src_rank = torch.tensor(self._src_rank, dtype=torch.int32, device=d)
+        self.src_slot = torch.tensor(self._src_slot, dtype=torch.int32, device=d)
+        self.seq = torch.zeros(1, dtype=torch.int64, device=d)
+        self.bar = torch.zeros(1, dtype=torch.int32, device=d)
+        self.err = torch.zeros(1, dtype=torch.int32, device=d)
+        conf_slots = max(sum(len(place_clients(pp.n_clients, world)[q]) for pp in problems) for q in range(world))
+        self.sym_layout = p2p.SymLayout(self.global_total, conf_slots)
+        self._symbuf = None
+        if sym_ptrs is None:
+            self._symbuf = p2p.SymmetricBuffer(self.sym_layout.nbytes)
+            sym_ptrs = self._symbuf.exchange(rank, world)
+        self.sym_ptrs = list(sym_ptrs)
+        self.rank_record = p2p.make_rank_record(self, rank, world, self.sym_layout, self.sym_ptrs, self.feds_global, self.conf_all,
+                                                self.hist_local, self.hist_global, self.src_rank, self.src_slot, self.seq,
+                                                self.bar, self.err, g_total, timeout_s)
+        self.rank_dev = K.upload_table(self.rank_record, d)
+        self.p2p_blocks = p2p.blocks_for(self.tb.max_slab)
+        self.kernel_names = [k for k in self.kernel_names if k != "k_fedavg"] + ["k_fedavg_p2p"]
+
+    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True) -> None:
+        p2p.launch(self.rank_dev, 1, self.p2p_blocks)
+
+    def history(self) -> Dict[str, np.ndarray]:
+        st = self.fed_state_host()
+        R = int(st["round"].max()) if len(st) else 0
+        hg = self.hist_global.cpu().numpy().reshape(self.n_feds, self.max_rounds, 4)[:, :R].astype(np.float64)
+        hl = self.hist_local.cpu().numpy().reshape(self.max_rounds, self.n_groups_total, 4)[:R].astype(np.float64)
+        from ..fed.metrics import METRIC_NAMES
+        return {"global": hg, "local": hl, "rounds": st["round"].copy(),
+                "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool), "last": st["last"].copy(),
+                "metric_names": np.asarray(METRIC_NAMES)}
+
+    def check_errors(self) -> None:
+        if int(self.err.item()) != 0:
+            raise RuntimeError(f"rank {self.rank}: a peer did not arrive at the aggregation barrier within the timeout")
+
+    def close(self) -> None:
+        if self._symbuf is not None:
+            torch.cuda.synchronize()
+            self._symbuf.close()
+            self._symbuf = None
+
+    @staticmethod
+    def custom_income(data, rows: Sequence[np.ndarray], rank: int, world: int, max_rounds: int = 300,
+                      precision: Optional[str] = None, patience: int = 0) -> "DistFedEngine":
+        """The benchmark federation: one custom-MLP federation whose client c owns ``rows[c]``."""
+        prob = FedProblem.custom(data.n_features, data.n_classes, [np.asarray(r, dtype=np.int32) for r in rows], patience=patience)
+        return DistFedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
+                             max_rounds=max_rounds, precision=precision)
+
+
+class EmulatedWorld:
+    """``world`` ranks of a :class:`DistFedEngine` federation on ONE GPU: each rank has its own
+    engine and its own "symmetric" buffer (a plain device tensor), and the aggregation kernel is
+    launched once with gridDim.y = world (cooperative), which is the only safe way to run kernels
+    that wait on each other on a single device.  Used by the single-GPU tests of the protocol."""
+
+    def __init__(self, problems: Sequence[FedProblem], X_train, y_train, X_test=None, y_test=None, world: int = 2,
+                 max_rounds: int = 64, precision: Optional[str] = None, seed: int = 0):
+        dev = torch.device("cuda")
+        # size the symmetric buffers first (layout depends only on the global problem list)
+        global_total = sum(p.spec.slab_size for p in problems)
+        conf_slots = max(sum(len(place_clients(p.n_clients, world)[q]) for p in problems) for q in range(world))
+        lay = p2p.SymLayout(global_total, conf_slots)
+        self.sym = [torch.zeros(lay.nbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
+        ptrs = [s.data_ptr() for s in self.sym]
+        self.ranks = [DistFedEngine(problems, X_train, y_train, X_test, y_test, rank=q, world=world, max_rounds=max_rounds,
+                                    seed=seed, precision=precision, sym_ptrs=ptrs) for q in range(world)]
+        table = np.concatenate([r.rank_record for r in self.ranks])
+        self.table_dev = K.upload_table(table, dev)
+        self.world = world
+        self.blocks = p2p.blocks_for(max(r.tb.max_slab for r in self.ranks), world)
+
+    def enqueue_round(self) -> None:
+        for r in self.ranks:
+            r.enqueue_round_begin()
+            r.enqueue_local_part()
+        p2p.launch(self.table_dev, self.world, self.blocks)
+
+    def run(self, rounds: int):
+        for _ in range(rounds):
+            self.enqueue_round()
+        torch.cuda.synchronize()
+        for r in self.ranks:
+            r.check_errors()
+        return [r.history() for r in self.ranks]

@@ -104,6 +104,36 @@ typedef struct FedbTile {
   int32_t tile;  /* tile index inside the owner's current batch */
 } FedbTile;
 
+/* Per-rank argument block of the cross-GPU aggregation kernel (fedb_fedavg_p2p).  All pointers are
+ * device pointers valid on the launching GPU; sym[q] is rank q's symmetric buffer as mapped into
+ * this process (CUDA IPC).  Symmetric buffer layout (bytes): partial[2][global_total] fp32 at
+ * sym_partial_off, conf[2][conf_slots][64] int32 at sym_conf_off, flags[8] u64 at sym_flag_off. */
+typedef struct FedbP2PRank {
+  int32_t rank, world;
+  int32_t n_feds, n_groups_local;
+  int32_t n_groups_total, conf_slots;   /* conf_slots: slots per parity in the symmetric buffer */
+  int64_t global_total;                 /* floats in the global arena */
+  const FedbGroup* groups;              /* local tables (resident clients only) */
+  const FedbFed* feds;                  /* first_group / n_clients index the local group table */
+  const FedbFed* feds_global;           /* first_group / n_clients index all clients of all ranks */
+  FedbFedState* fed_state;
+  float* params;
+  float* global;
+  const int32_t* conf;                  /* local confusion slots [n_groups_local][64] */
+  int32_t* conf_all;                    /* scratch [n_groups_total][64] */
+  float* hist_local;                    /* [max_rounds][n_groups_total][4] */
+  float* hist_global;                   /* [n_feds][max_rounds][4] */
+  const int32_t* conf_src_rank;         /* [n_groups_total]: which rank hosts global client i */
+  const int32_t* conf_src_slot;         /* [n_groups_total]: its local slot on that rank */
+  uint8_t* sym[8];
+  int64_t sym_partial_off, sym_conf_off, sym_flag_off;
+  uint64_t* seq;                        /* local: launches completed (monotonic) */
+  uint32_t* bar;                        /* local grid-barrier counter (monotonic) */
+  int32_t* err;                         /* set to FEDB_E_TIMEOUT when a peer never arrived */
+  int64_t timeout_cycles;
+  int32_t write_back, do_metrics;
+} FedbP2PRank;
+
 const char* fedb_last_error(void);
 int fedb_version(void);
 void fedb_struct_sizes(int32_t* out5); /* sizeof of the five structs above, for binding checks */
@@ -165,6 +195,29 @@ int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* stat
                 int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
                 float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
                 void* stream);
+
+/* K2a/K3 on tcgen05: n_steps local optimizer steps (+ local evaluation into conf slot g) for every
+ * group in one launch, one thread-block cluster per client (csrc/fedb_tc.cu; C:63-91).  Groups
+ * must have 2 hidden ReLU layers with in <= 15, h1 <= 63, h2 <= 256, out <= 8. */
+int64_t fedb_tc_smem_bytes(void);
+int fedb_local_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X,
+                        int32_t ldx, const int32_t* y, const int32_t* idx, float* params, float* m, float* v,
+                        int32_t* step, const int32_t* active, const FedbFedState* fed_state, float* loss_out,
+                        int32_t* conf, int32_t batch, int32_t n_steps, int32_t do_eval, void* stream);
+
+/* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
+ * peer loads over NVLink of every rank's partial, write-back, metrics and early stop
+ * (csrc/fedb_p2p.cu; C:101-120, C:165-192).  ranks_dev[0..n_ranks_here): one entry in real
+ * multi-GPU use; R entries emulate R ranks on one GPU (tests).  Cooperative launch. */
+int32_t fedb_p2p_rank_size(void);
+int fedb_fedavg_p2p(const FedbP2PRank* ranks_dev, int32_t n_ranks_here, int32_t blocks_x, void* stream);
+/* Symmetric-memory plumbing: cudaMalloc'ed, zeroed buffer; 64-byte CUDA IPC handle out / in.
+ * These four allocate / synchronise and are for set-up only. */
+int fedb_symm_alloc(int64_t bytes, void** out);
+int fedb_symm_free(void* p);
+int fedb_ipc_get_handle(void* p, uint8_t* handle64);
+int fedb_ipc_open_handle(const uint8_t* handle64, void** out);
+int fedb_ipc_close_handle(void* p);
 
 /* One optimizer step of every group (the work of fedb_fwd_bwd followed by fedb_reduce_opt) for
  * callers that must not allocate device memory.  No counterpart in the reference.
