@@ -1,0 +1,86 @@
+"""Hyper-parameter grid as packed concurrent federations (H:68-132).
+
+The reference runs its 10 x 9 = 90 (hidden sizes x learning rate) federations one after
+another, each with every rank fitting an ``MLPClassifier`` for up to 400 epochs (303 s at np=4 on
+the survey box).  Here every grid point is one federation of the same engine: all 90 x clients
+local fits advance together through the same grouped launches, then one grouped aggregation and
+metric pass scores them all.  A local-epochs axis (BASELINE.json config 4) is optional.
+Selection rule as in H:114-119: first strictly greater pooled accuracy wins, in grid order.
+"""
+from __future__ import annotations
+
+from dataclasses import replace
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from ..models.spec import MLPSpec
+from . import logging as flog
+from .engine import FedEngine
+from .problem import FedProblem, TrainHyper
+
+# H:73-74, in the reference's iteration order
+HIDDEN_GRID = [(50,), (100,), (50, 50), (100, 50), (50, 100), (50, 200), (50, 400), (100, 400), (400, 200), (200, 400)]
+LR_GRID = [0.002, 0.005, 0.004, 0.008, 0.01, 0.02, 0.05, 0.1, 0.2]
+
+
+def build_grid(n_features: int, shards: Sequence[np.ndarray], hidden_grid=HIDDEN_GRID, lr_grid=LR_GRID,
+               max_iter_grid: Sequence[int] = (400,), seed: int = 42, init: str = "sklearn_exact") -> List[FedProblem]:
+    probs = []
+    for hl in hidden_grid:
+        for lr in lr_grid:
+            for mi in max_iter_grid:
+                probs.append(FedProblem.sklearn_like(n_features, shards, hidden=tuple(hl), lr=lr, max_iter=mi, seed=seed,
+                                                     init=init, name=f"hl={tuple(hl)},lr={lr},max_iter={mi}"))
+    return probs
+
+
+def run_grid(data, n_clients: int = 4, hidden_grid=HIDDEN_GRID, lr_grid=LR_GRID, max_iter_grid: Sequence[int] = (400,),
+             device: Optional[str] = None, log: Optional[flog.RunLog] = None, seed: int = 0, init: str = "sklearn_exact",
+             shards: Optional[Sequence[np.ndarray]] = None) -> Dict:
+    from ..data.partition import contiguous
+    shards = shards if shards is not None else contiguous(len(data.X_train), n_clients)
+    probs = build_grid(data.n_features, shards, hidden_grid, lr_grid, max_iter_grid, init=init)
+    results = []
+    # federations with different max_iter stop at different epochs; run one engine per max_iter value
+    for mi in max_iter_grid:
+        sub = [p for p in probs if p.hyper.max_iter == mi]
+        eng = FedEngine(sub, data.X_train, data.y_train, data.X_test, data.y_test, device=device, max_rounds=2, seed=seed)
+        eng.reset_fit_state()
+        eng.enqueue_round_begin()
+        n_iter = eng.fit_local(max_iter=mi)
+        eng.enqueue_eval_local()
+        eng.enqueue_aggregate()
+        h = eng.history()
+        test = eng.evaluate_global("test") if eng.n_test else [None] * len(sub)
+        for f, p in enumerate(sub):
+            gs = eng.group_of[f]
+            results.append({"hidden_layer_sizes": tuple(p.spec.dims[1:-1]), "learning_rate": p.hyper.lr, "max_iter": mi,
+                            "global": h["global"][f, 0], "local": h["local"][0][gs], "n_iter": n_iter[gs],
+                            "test_averaged_model": test[f], "weights": p.spec.to_coefs_intercepts(eng.global_slab(f)), "spec": p.spec})
+    best = None
+    for r in results:  # H:114: strictly greater, first wins
+        if log is not None:
+            log.lines(flog.tune_config_lines(r["hidden_layer_sizes"], r["learning_rate"], r["local"], r["global"]))
+            log.record(hidden=r["hidden_layer_sizes"], lr=r["learning_rate"], max_iter=r["max_iter"], global_metrics=r["global"],
+                       n_iter=r["n_iter"])
+        if best is None or r["global"][0] > best["global"][0]:
+            best = r
+    out = {"results": results, "best": best,
+           "best_params": {"hidden_layer_sizes": best["hidden_layer_sizes"], "learning_rate": best["learning_rate"]},
+           "best_metrics": {n: float(best["global"][i]) for i, n in enumerate(("accuracy", "precision", "recall", "f1"))}}
+    if len(max_iter_grid) > 1:
+        out["best_params"]["max_iter"] = best["max_iter"]
+    if log is not None:
+        coefs, inter = best["weights"]
+        log.lines(flog.tune_best_lines(out["best_params"], out["best_metrics"], list(coefs) + list(inter)))
+    return out
+
+
+def accuracy_table(results: List[Dict], hidden_grid=HIDDEN_GRID, lr_grid=LR_GRID) -> np.ndarray:
+    """[len(hidden_grid), len(sorted lr)] pooled-accuracy table in the layout of SURVEY.md §6.2."""
+    lrs = sorted(lr_grid)
+    t = np.full((len(hidden_grid), len(lrs)), np.nan)
+    for r in results:
+        t[hidden_grid.index(tuple(r["hidden_layer_sizes"])), lrs.index(r["learning_rate"])] = r["global"][0]
+    return t

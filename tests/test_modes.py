@@ -1,0 +1,93 @@
+"""sklearn-mode round policies, the packed hyper-parameter grid, the CLI and the reference-format
+logging — on the CPU path with small budgets (the GPU path runs the same Python)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from fedb200 import FedEngine, FedProblem, make_shards
+from fedb200.cli import main as cli_main
+from fedb200.fed import logging as flog
+from fedb200.fed.sklearn_mode import run_sklearn_rounds
+from fedb200.fed.tune import build_grid, run_grid
+from fedb200.models.checkpoint import load_checkpoint
+
+
+def _sk_engine(data, clients=2, n=600, max_iter=4, hidden=(16,)):
+    shards = make_shards("contiguous", n, clients)
+    prob = FedProblem.sklearn_like(14, shards, hidden=hidden, max_iter=max_iter)
+    return FedEngine([prob], data.X_train[:n], data.y_train[:n], data.X_test, data.y_test, device="cpu", max_rounds=4)
+
+
+def test_reference_faithful_rounds_are_identical(income_nomean):
+    """R5 of SURVEY §0: fit() re-initialises, so every round reproduces round 1."""
+    h = run_sklearn_rounds(_sk_engine(income_nomean), rounds=3, policy="reference_faithful")
+    assert np.array_equal(h["global"][0, 0], h["global"][0, 1]) and np.array_equal(h["global"][0, 1], h["global"][0, 2])
+    assert np.array_equal(h["n_iter"][0], h["n_iter"][2])
+
+
+def test_warm_start_improves_and_literal_policy_stalls(income_nomean):
+    hw = run_sklearn_rounds(_sk_engine(income_nomean, max_iter=40), rounds=3, policy="warm_start")
+    assert hw["global"][0, -1, 0] >= hw["global"][0, 0, 0] - 0.02
+    hl = run_sklearn_rounds(_sk_engine(income_nomean, max_iter=400, hidden=(8,)), rounds=2, policy="sklearn_literal")
+    # sklearn's warm_start keeps the no-improvement counter: once it has tripped, later fits stop at once
+    if hl["n_iter"][0].max() < 400:
+        assert hl["n_iter"][1].max() <= 2
+
+
+def test_sklearn_round_uses_pooled_unweighted(income_nomean):
+    eng = _sk_engine(income_nomean, clients=3, n=700)
+    h = run_sklearn_rounds(eng, rounds=1)
+    cm = eng.confusion()[:3]
+    from fedb200.fed.metrics import pooled
+    assert h["global"][0, 0, 0] == pytest.approx(pooled([c[:2, :2] for c in cm])["accuracy"], abs=1e-6)
+    assert list(eng.tb.groups["agg_num"]) == [1.0, 1.0, 1.0] and list(eng.tb.groups["agg_den"]) == [3.0, 3.0, 3.0]
+
+
+def test_grid_is_packed_and_picks_first_best(income_nomean):
+    class D:  # a 500-row view of the data
+        X_train, y_train = income_nomean.X_train[:500], income_nomean.y_train[:500]
+        X_test, y_test = income_nomean.X_test[:200], income_nomean.y_test[:200]
+        n_features = 14
+    assert len(build_grid(14, make_shards("contiguous", 500, 2))) == 90
+    out = run_grid(D, 2, hidden_grid=[(8,), (8, 8)], lr_grid=[0.004, 0.05], max_iter_grid=(3,), device="cpu", init="sklearn_glorot")
+    assert len(out["results"]) == 4
+    accs = [r["global"][0] for r in out["results"]]
+    assert out["best_metrics"]["accuracy"] == pytest.approx(max(accs))
+    assert out["results"][int(np.argmax(accs))]["hidden_layer_sizes"] == out["best_params"]["hidden_layer_sizes"]
+    coefs, inter = out["best"]["weights"]
+    assert coefs[0].shape[0] == 14 and inter[-1].shape == (1,)
+
+
+def test_log_formats_match_reference_strings():
+    loc = np.array([[0.5, 0.25, 0.125, 0.0625]])
+    lines = flog.custom_round_lines(3, loc, [0.83456, 0.8, 0.8, 0.8])
+    assert lines[0] == "\nRound 3:\n"
+    assert lines[1] == "  RANK 0 - Local Metrics (Round 3): [accuracy: 0.5000, precision: 0.2500, recall: 0.1250, f1: 0.0625]"
+    assert lines[2] == "  Global Metrics (Round 3): [accuracy: 0.8346, precision: 0.8000, recall: 0.8000, f1: 0.8000]"
+    assert flog.custom_stop_lines(10, 162)[0] == "Early stopping triggered: No significant change in metrics for 10 rounds."
+    s = flog.sklearn_round_lines(1, loc, [0.957, 0.9584, 0.957, 0.957])
+    assert "  Accuracy: 0.9570" in s and "-" * 50 in s
+
+
+def test_cli_custom_checkpoint_and_resume(tmp_path, capsys):
+    ck, jl = str(tmp_path / "g.npz"), str(tmp_path / "log.jsonl")
+    assert cli_main(["custom", "--clients", "2", "--rounds", "3", "--device", "cpu", "--checkpoint", ck, "--jsonl", jl,
+                     "--synthetic-rows", "600"]) == 0
+    out = capsys.readouterr().out
+    assert "Global Metrics (Round 3)" in out and "RANK 1 - Local Metrics (Round 1)" in out
+    spec, coefs, inter, meta, opt = load_checkpoint(ck)
+    assert spec.dims == (14, 50, 200, 2) and meta["round"] == 3 and set(opt) == {"m", "v", "step", "params"}
+    recs = [json.loads(l) for l in open(jl)]
+    assert len(recs) == 4 and recs[-1]["summary"]
+    assert cli_main(["custom", "--clients", "2", "--rounds", "1", "--device", "cpu", "--resume", ck, "--quiet",
+                     "--synthetic-rows", "600"]) == 0
+
+
+def test_cli_sklearn_and_tune_smoke(capsys):
+    assert cli_main(["sklearn-avg", "--clients", "2", "--rounds", "1", "--max-iter", "2", "--hidden", "8", "--device", "cpu",
+                     "--synthetic-rows", "500"]) == 0
+    assert "Final Global Weight Statistics:" in capsys.readouterr().out
+    assert cli_main(["tune", "--clients", "2", "--max-iter", "2", "--small", "--device", "cpu", "--quiet", "--synthetic-rows", "400"]) == 0
+    assert "Best" not in capsys.readouterr().err
