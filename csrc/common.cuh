@@ -153,29 +153,37 @@ __device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalar
 }
 
 
-// ---- metrics from confusion counts + early stop (K3/K5), shared by fedavg kernels ---------
+// ---- metrics from confusion counts + early stop (K3/K5), shared by the aggregation kernels ---------
+// Fully unrolled over FEDB_MAX_CLASSES so the per-class sums stay in registers (these run on the
+// critical path of every round, on a single warp).
 __device__ inline void metrics_from_conf(const int32_t* cm, int C, double out[4]) {
   double total = 0, tr = 0;
-  double sup[FEDB_MAX_CLASSES], prd[FEDB_MAX_CLASSES];
-  for (int c = 0; c < C; ++c) { sup[c] = 0; prd[c] = 0; }
-  for (int i = 0; i < C; ++i)
-    for (int j = 0; j < C; ++j) {
-      const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
-      total += x; sup[i] += x; prd[j] += x;
-      if (i == j) tr += x;
-    }
+  double sup[FEDB_MAX_CLASSES], prd[FEDB_MAX_CLASSES], dg[FEDB_MAX_CLASSES];
+#pragma unroll
+  for (int c = 0; c < FEDB_MAX_CLASSES; ++c) { sup[c] = 0; prd[c] = 0; dg[c] = 0; }
+#pragma unroll
+  for (int i = 0; i < FEDB_MAX_CLASSES; ++i)
+#pragma unroll
+    for (int j = 0; j < FEDB_MAX_CLASSES; ++j)
+      if (i < C && j < C) {
+        const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
+        total += x; sup[i] += x; prd[j] += x;
+        if (i == j) { tr += x; dg[i] = x; }
+      }
   out[0] = out[1] = out[2] = out[3] = 0.0;
   if (total == 0) return;
   out[0] = tr / total;
-  for (int c = 0; c < C; ++c) {
-    const double tp = (double)cm[c * FEDB_MAX_CLASSES + c];
-    const double w = sup[c] / total;
-    const double p = prd[c] > 0 ? tp / prd[c] : 0.0;
-    const double r = sup[c] > 0 ? tp / sup[c] : 0.0;
-    const double den = sup[c] + prd[c];
-    const double f = den > 0 ? 2.0 * tp / den : 0.0;
-    out[1] += p * w; out[2] += r * w; out[3] += f * w;
-  }
+#pragma unroll
+  for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
+    if (c < C) {
+      const double tp = dg[c];
+      const double w = sup[c] / total;
+      const double p = prd[c] > 0 ? tp / prd[c] : 0.0;
+      const double r = sup[c] > 0 ? tp / sup[c] : 0.0;
+      const double den = sup[c] + prd[c];
+      const double f = den > 0 ? 2.0 * tp / den : 0.0;
+      out[1] += p * w; out[2] += r * w; out[3] += f * w;
+    }
 }
 
 // C:181-192: anchor / patience early-stop rule on the four global metrics.
@@ -196,29 +204,61 @@ __device__ inline void early_stop_update(const FedbFed& F, FedbFedState& S, cons
   }
 }
 
-__device__ __noinline__ inline void round_metrics(const FedbGroup* groups, const FedbFed& F, FedbFedState& S, int f, int n_groups,
-                              const int32_t* conf, float* hist_local, float* hist_global) {
+// What fedb_round_begin does for one federation (C:130-142), callable from an aggregation kernel's tail.
+__device__ inline void begin_next_round(FedbFedState& S) {
+  if (S.stop_pending) S.stop = 1;
+  if (!S.stop) S.round += 1;
+}
+
+// One WARP turns a federation's confusion counts into the round's metrics: lane k handles clients
+// k, k+32, ... (per-client metrics -> hist_local), a fixed xor-tree adds them up (mean of local
+// metrics, C:169) or the pooled counts are scored (S:130-134); lane 0 then records the global
+// metrics and runs the early-stop rule.  `pool` = 64 ints of shared memory.  All 32 lanes must call.
+__device__ inline void round_metrics_warp(const FedbFed& F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
+                                          float* hist_local, float* hist_global, int* pool, bool begin_next = false) {
+  const int lane = threadIdx.x & 31;
   const int C = F.n_classes;
   const int r = S.round - 1;  // 0-based index of the round in progress
-  double glob[4] = {0, 0, 0, 0};
-  int32_t pooled[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
-  for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] = 0;
-  for (int k = 0; k < F.n_clients; ++k) {
+  const bool pooled = F.metric_mode == FEDB_METRIC_POOLED;
+  for (int i = lane; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += 32) pool[i] = 0;
+  __syncwarp();
+  double acc[4] = {0, 0, 0, 0};
+  for (int k = lane; k < F.n_clients; k += 32) {
     const int g = F.first_group + k;
     const int32_t* cm = conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
     double mloc[4];
     metrics_from_conf(cm, C, mloc);
     if (hist_local && r >= 0 && r < F.max_rounds)
-      for (int i = 0; i < 4; ++i) hist_local[((size_t)r * n_groups + g) * 4 + i] = (float)mloc[i];
-    for (int i = 0; i < 4; ++i) glob[i] += mloc[i];
-    for (int i = 0; i < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; ++i) pooled[i] += cm[i];
+      *reinterpret_cast<float4*>(hist_local + ((size_t)r * n_groups + g) * 4) =
+          make_float4((float)mloc[0], (float)mloc[1], (float)mloc[2], (float)mloc[3]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] += mloc[i];
+    if (pooled)
+      for (int i = 0; i < C; ++i)
+        for (int j = 0; j < C; ++j) atomicAdd(&pool[i * FEDB_MAX_CLASSES + j], cm[i * FEDB_MAX_CLASSES + j]);
   }
-  if (F.metric_mode == FEDB_METRIC_POOLED) metrics_from_conf(pooled, C, glob);
-  else for (int i = 0; i < 4; ++i) glob[i] /= (double)F.n_clients;
-  if (hist_global && r >= 0 && r < F.max_rounds)
-    for (int i = 0; i < 4; ++i) hist_global[((size_t)f * F.max_rounds + r) * 4 + i] = (float)glob[i];
-  early_stop_update(F, S, glob);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+  __syncwarp();
+  if (lane == 0) {
+    double glob[4];
+    if (pooled) metrics_from_conf(pool, C, glob);
+    else
+      for (int i = 0; i < 4; ++i) glob[i] = acc[i] / (double)F.n_clients;
+    if (hist_global && r >= 0 && r < F.max_rounds)
+      *reinterpret_cast<float4*>(hist_global + ((size_t)f * F.max_rounds + r) * 4) =
+          make_float4((float)glob[0], (float)glob[1], (float)glob[2], (float)glob[3]);
+    // work on a private copy: S lives in global memory and every dependent field access would be an
+    // L2 round trip on the round's critical path
+    FedbFedState st = S;
+    early_stop_update(F, st, glob);
+    st.done = st.round;
+    if (begin_next) begin_next_round(st);
+    S = st;
+  }
+  __syncwarp();
 }
-
 
 }  // namespace fedb

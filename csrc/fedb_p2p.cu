@@ -62,11 +62,16 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
   int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + par * conf_stride;
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
   const int gthreads = gridDim.x * blockDim.x, gtid = blockIdx.x * blockDim.x + tid;
+  // Stop flags as they stand for THIS round, taken before the grid barrier: block 0 raises them for
+  // the next round at the end of this very kernel (begin_next), which must not affect slower blocks.
+  __shared__ unsigned char s_stop[256];
+  for (int f = tid; f < R.n_feds; f += blockDim.x) s_stop[f] = R.fed_state[f].stop ? 1 : 0;
+  __syncthreads();
 
   // ---- A: local weighted partial sums -----------------------------------------------------------
   for (int f = 0; f < R.n_feds; ++f) {
     const FedbFed& F = R.feds[f];
-    if (R.fed_state[f].stop) continue;
+    if (s_stop[f]) continue;
     for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
       const int e = e4 * 4;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
   // ---- C: sum the partials of all ranks in rank order; write global + every resident client -------
   for (int f = 0; f < R.n_feds; ++f) {
     const FedbFed& F = R.feds[f];
-    if (R.fed_state[f].stop) continue;
+    if (s_stop[f]) continue;
     for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
       const int e = e4 * 4;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -135,10 +140,19 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
       R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
     }
     __syncthreads();
-    if (tid == 0)
+    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+    if (tid < 32)
       for (int f = 0; f < R.n_feds; ++f)
-        if (!R.fed_state[f].stop)
-          round_metrics(nullptr, R.feds_global[f], R.fed_state[f], f, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global);
+        if (!s_stop[f])
+          round_metrics_warp(R.feds_global[f], R.fed_state[f], f, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool,
+                             R.begin_next != 0);
+    __syncthreads();
+  }
+  if (blockIdx.x == 0 && R.begin_next) {   // next round's fedb_round_begin, fused (the counts above were already published)
+    if (tid == 0 && !R.do_metrics)
+      for (int f = 0; f < R.n_feds; ++f) begin_next_round(R.fed_state[f]);
+    int32_t* conf_rw = const_cast<int32_t*>(R.conf);
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += blockDim.x) conf_rw[i] = 0;
   }
   if (blockIdx.x == 0 && tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
 }
@@ -150,7 +164,7 @@ using namespace fedb;
 extern "C" int32_t fedb_p2p_rank_size(void) { return (int32_t)sizeof(FedbP2PRank); }
 
 extern "C" int fedb_fedavg_p2p(const FedbP2PRank* ranks_dev, int32_t n_ranks_here, int32_t blocks_x, void* stream) {
-  FEDB_REQUIRE(n_ranks_here >= 1 && blocks_x >= 1, "bad grid");
+  FEDB_REQUIRE(n_ranks_here >= 1 && blocks_x >= 1, "bad grid");  // (n_feds <= 256 is checked by the caller: parallel/p2p.py)
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(blocks_x, n_ranks_here);
   cfg.blockDim = dim3(P2P_THREADS);

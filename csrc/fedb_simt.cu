@@ -566,7 +566,8 @@ k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ job
 __global__ void __launch_bounds__(NTHREADS)
 k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds, FedbFedState* __restrict__ state,
          int n_groups, float* __restrict__ params, float* __restrict__ global, const int32_t* __restrict__ conf,
-         float* __restrict__ hist_local, float* __restrict__ hist_global, int write_back, int do_metrics) {
+         float* __restrict__ hist_local, float* __restrict__ hist_global, int write_back, int do_metrics, int begin_next,
+         int32_t* __restrict__ conf_rw) {
   const int f = blockIdx.y;
   const FedbFed& F = feds[f];
   if (state[f].stop) return;
@@ -588,8 +589,18 @@ k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds,
       for (int k = 0; k < F.n_clients; ++k)
         *reinterpret_cast<float4*>(params + groups[F.first_group + k].slab_off + e) = acc;
   }
-  if (do_metrics && blockIdx.x == 0 && threadIdx.x == 0)
-    round_metrics(groups, F, state[f], f, n_groups, conf, hist_local, hist_global);
+  if (blockIdx.x == 0) {
+    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+    if (threadIdx.x < 32) {
+      if (do_metrics) round_metrics_warp(F, state[f], f, n_groups, conf, hist_local, hist_global, pool, begin_next != 0);
+      else if (begin_next && threadIdx.x == 0) begin_next_round(state[f]);
+    }
+    if (begin_next) {  // clear this federation's confusion slots for the next round (after the metrics read them)
+      __syncthreads();
+      for (int i = threadIdx.x; i < F.n_clients * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += blockDim.x)
+        conf_rw[(size_t)F.first_group * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + i] = 0;
+    }
+  }
 }
 
 }  // namespace fedb
@@ -713,11 +724,15 @@ extern "C" int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const
 extern "C" int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
                            int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
                            float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
-                           void* stream) {
+                           int32_t begin_next, void* stream) {
   FEDB_REQUIRE(n_feds > 0 && max_slab > 0, "bad sizes");
   dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_feds);
+  // begin_next raises the stop flag at the end of block (0, f); with more than one block per federation a
+  // block scheduled late could see it one round early
+  FEDB_REQUIRE(!begin_next || grid.x == 1, "begin_next needs a single block per federation (slab <= 1024 floats)");
   k_fedavg<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups, feds, state, n_groups, params, global, conf, hist_local,
-                                                        hist_global, write_back, do_metrics);
+                                                        hist_global, write_back, do_metrics, begin_next,
+                                                        const_cast<int32_t*>(conf));
   FEDB_LAUNCH_OK();
   return FEDB_OK;
 }

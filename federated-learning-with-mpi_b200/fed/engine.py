@@ -63,6 +63,7 @@ class FedEngine:
         self._build_tables()
         self._alloc_state()
         self._graphs: Dict[str, object] = {}
+        self._primed = False
         self._select_precision()
         self.init_params()
 
@@ -82,7 +83,6 @@ class FedEngine:
                                  "in<=15, h1<=63, h2<=256, out<=8")
             self.precision_name = "bf16"
             self.tc_cluster = tc.tc_cluster_size(self.tb.groups)
-            self.kernel_names = ["k_round_begin", "k_local_round_tc", "k_fedavg"]
         elif req == "fp32":
             self.precision_name = "fp32"
         else:
@@ -112,7 +112,8 @@ class FedEngine:
                 if len(sh) == 0:
                     raise ValueError(f"client {k} of federation {f} has an empty shard (the reference would deadlock: S:91-93)")
                 rows_per_step = min(h.batch_size, len(sh)) if h.batch_size > 0 else len(sh)
-                max_tiles = (rows_per_step + TILE - 1) // TILE
+                # >= 8 records: the tensor-core kernel keeps one per CTA of its (<= 8-wide) cluster
+                max_tiles = max(8, (rows_per_step + TILE - 1) // TILE)
                 r = groups[g]
                 r["n_layers"] = s.n_layers
                 r["dims"][: len(s.dims)] = s.dims
@@ -199,6 +200,7 @@ class FedEngine:
         self.bs_stride = K.batch_stats_stride(self.tb.max_slab)
         self.batch_stats = z(G * self.n_batches * self.bs_stride, torch.float64)
         self.idx_epoch = self.idx.clone()
+        self.tail_count = z(1, torch.int32)
 
     def init_params(self) -> None:
         """(Re-)initialise every client's parameters and clear optimizer state (K4)."""
@@ -234,13 +236,42 @@ class FedEngine:
         K.evaluate(self.tb, self.local_jobs_np, self.local_jobs, self.local_tiles, self.n_local_tiles, self.params,
                    self.global_, self.X, self.y, self.idx, self.conf, self.fed_state)
 
-    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True) -> None:
+    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = False) -> None:
         K.fedavg(self.tb, self.fed_state, self.params, self.global_, self.conf, self.hist_local, self.hist_global,
-                 write_back, do_metrics)
+                 write_back, do_metrics, begin_next)
+
+    def _begin_is_fused(self) -> bool:
+        """True when the aggregation kernel also performs the next round's begin bookkeeping (the
+        single-launch tensor-core round; the cross-GPU kernel in DistFedEngine)."""
+        return self._fused_round_ok()
+
+    def prime(self) -> None:
+        """With a fused begin, the very first round_begin has to be run once, eagerly."""
+        if self._begin_is_fused() and not self._primed:
+            self.enqueue_round_begin()
+            self._primed = True
+
+    # one CTA aggregates every federation in the fused tail: worth it while that is a few microseconds
+    FUSED_TAIL_MAX_FLOATS = 1 << 20
+
+    def _fused_round_ok(self) -> bool:
+        return (self.precision_name == "bf16" and type(self).enqueue_aggregate is FedEngine.enqueue_aggregate
+                and self.params_total <= self.FUSED_TAIL_MAX_FLOATS and self.n_feds <= 256
+                and max(p.n_clients for p in self.problems) <= 32)
 
     def enqueue_round(self) -> None:
-        """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg."""
-        self.enqueue_round_begin()
+        """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg (+ the next
+        round's begin bookkeeping).  Requires :meth:`prime` once before the first round.  On the
+        tensor-core path with a small arena this is ONE launch (fedb_round_tc)."""
+        if self._fused_round_ok():
+            from ..ops import tc
+            E = max(p.hyper.local_epochs for p in self.problems)
+            tc.round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
+                        self.fed_state, self.loss, self.conf, self.scratch, E, self.global_, self.hist_local, self.hist_global,
+                        self.tail_count)
+            return
+        if not self._begin_is_fused():
+            self.enqueue_round_begin()
         self.enqueue_local_part()
         self.enqueue_aggregate()
 
@@ -253,7 +284,7 @@ class FedEngine:
         if self.precision_name == "bf16":
             from ..ops import tc
             tc.local_round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step,
-                              self.active, self.fed_state, self.loss, self.conf, 0, E, True)
+                              self.active, self.fed_state, self.loss, self.conf, self.scratch, 0, E, True)
         else:
             for _ in range(E):
                 for b in range(self.n_batches):
@@ -263,8 +294,10 @@ class FedEngine:
     @property
     def launches_per_round(self) -> int:
         E = max(p.hyper.local_epochs for p in self.problems)
+        if self._fused_round_ok():
+            return 1
         if self.precision_name == "bf16":
-            return 3
+            return 3 if not self._begin_is_fused() else 2
         return 1 + 2 * E * self.n_batches + 2
 
     def _graph(self, key: str, fn, unroll: int = 1):
@@ -288,8 +321,9 @@ class FedEngine:
         :meth:`history`.  On CUDA the round is replayed from a graph, ``unroll`` rounds per
         launch; the stop flags are polled once per replay."""
         st = self.fed_state_host()
-        done = int(st["round"].max()) if len(st) else 0
+        done = int(st["done"].max()) if len(st) else 0
         rounds = min(rounds, self.max_rounds - done)
+        self.prime()
         use_graph = (self.device.type == "cuda") if use_graph is None else use_graph
         if not use_graph:
             for _ in range(rounds):
@@ -371,10 +405,10 @@ class FedEngine:
     # ----------------------------------------------------------------------------- results
     def history(self) -> Dict[str, np.ndarray]:
         st = self.fed_state_host()
-        R = int(st["round"].max()) if len(st) else 0
+        R = int(st["done"].max()) if len(st) else 0
         hg = self.hist_global.cpu().numpy().reshape(self.n_feds, self.max_rounds, 4)[:, :R].astype(np.float64)
         hl = self.hist_local.cpu().numpy().reshape(self.max_rounds, self.n_groups, 4)[:R].astype(np.float64)
-        return {"global": hg, "local": hl, "rounds": st["round"].copy(), "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool),
+        return {"global": hg, "local": hl, "rounds": st["done"].copy(), "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool),
                 "last": st["last"].copy(), "metric_names": np.asarray(METRIC_NAMES)}
 
     def confusion(self) -> np.ndarray:
@@ -413,7 +447,7 @@ class FedEngine:
             n = len(gs) * P
             opt = {"m": self.m[o: o + n].view(len(gs), P), "v": self.v[o: o + n].view(len(gs), P),
                    "step": self.step[gs[0]: gs[0] + len(gs)], "params": self.params[o: o + n].view(len(gs), P)}
-        save_checkpoint(path, p.spec, self.global_slab(f), int(self.fed_state_host()[f]["round"]),
+        save_checkpoint(path, p.spec, self.global_slab(f), int(self.fed_state_host()[f]["done"]),
                         extras={"name": p.name}, opt_state=opt)
 
     def load_checkpoint(self, path: str, f: int = 0) -> Dict:
@@ -457,6 +491,7 @@ class FedEngine:
         state: stop flag + the four global metrics) back to the host.  Returns the
         ``FedbFedState`` records.  This mirrors what the reference does every round
         (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic."""
+        self.prime()
         self.X[: self.n_train].copy_(x_host, non_blocking=True)
         self.y[: self.n_train].copy_(y_host, non_blocking=True)
         if self.device.type == "cuda":
@@ -478,10 +513,19 @@ class FedEngine:
 
     # ------------------------------------------------------------------- bench conveniences
     precision_name = "fp32"
-    kernel_names = ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]
+
+    @property
+    def kernel_names(self) -> List[str]:
+        """Kernels launched per steady-state round (the first round additionally runs k_round_begin)."""
+        if self._fused_round_ok():
+            return ["k_local_round_tc[train+eval+fedavg+metrics]"]
+        if self.precision_name == "bf16":
+            return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]
+        return ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]
 
     def step_graph(self) -> None:
         """Enqueue exactly one round (graph replay on CUDA); no host synchronisation."""
+        self.prime()
         if self.device.type != "cuda":
             self.enqueue_round()
             return

@@ -167,7 +167,7 @@ FED_DTYPE = np.dtype([
     ("metric_mode", "i4"), ("patience", "i4"), ("atol", "f4"), ("rtol", "f4"), ("max_rounds", "i4"), ("pad_", "i4"),
 ], align=True)
 FEDSTATE_DTYPE = np.dtype([
-    ("stop", "i4"), ("stop_pending", "i4"), ("round", "i4"), ("count", "i4"), ("has_anchor", "i4"), ("pad_", "i4"),
+    ("stop", "i4"), ("stop_pending", "i4"), ("round", "i4"), ("count", "i4"), ("has_anchor", "i4"), ("done", "i4"),
     ("anchor", "f8", (4,)), ("last", "f8", (4,)),
 ], align=True)
 EVALJOB_DTYPE = np.dtype([
@@ -202,7 +202,7 @@ def _declare(l: ctypes.CDLL) -> None:
         "fedb_reduce_opt": [_P, _I32, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _I32, _P],
         "fedb_epoch_end": [_P, _I32, _P, _I32, _I32, _F64, _I32, _I32, _P, _P, _P, _P, _P, _P],
         "fedb_eval": [_P, _P, _P, _I32, _P, _P, _P, _I32, _P, _P, _P, _P, _I64, _P],
-        "fedb_fedavg": [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _P, _P, _I32, _I32, _P],
+        "fedb_fedavg": [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P],
     }
     for name, args in sigs.items():
         fn = getattr(l, name)
@@ -220,8 +220,11 @@ def _declare(l: ctypes.CDLL) -> None:
 OPTIONAL_SIGS = {
     "fedb_tc_probe": ([_P, _P, ctypes.POINTER(_I32), _P, _P], _I32),
     "fedb_tc_probe_args_size": ([], _I32),
-    "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
+    "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
     "fedb_tc_smem_bytes": ([], _I64),
+    "fedb_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P, _P], _I32),
+    "fedb_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P], _I32),
+    "fedb_local_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),
     "fedb_noalloc_scratch_floats": ([], _I64),
     "fedb_p2p_rank_size": ([], _I32),
     "fedb_fedavg_p2p": ([_P, _I32, _I32, _P], _I32),
@@ -238,7 +241,7 @@ P2PRANK_DTYPE = np.dtype([
     ("fed_state", "u8"), ("params", "u8"), ("global", "u8"), ("conf", "u8"), ("conf_all", "u8"), ("hist_local", "u8"),
     ("hist_global", "u8"), ("conf_src_rank", "u8"), ("conf_src_slot", "u8"), ("sym", "u8", (8,)),
     ("sym_partial_off", "i8"), ("sym_conf_off", "i8"), ("sym_flag_off", "i8"), ("seq", "u8"), ("bar", "u8"), ("err", "u8"),
-    ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"),
+    ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"), ("begin_next", "i4"), ("pad_", "i4"),
 ], align=True)
 
 

@@ -349,7 +349,8 @@ def _metrics(cm, C):
     return np.array([tp.sum() / total, (pr * w).sum(), (rc * w).sum(), (f1 * w).sum()])
 
 
-def fedavg(groups, feds, fed_state, max_slab, params, global_, conf, hist_local, hist_global, write_back, do_metrics):
+def fedavg(groups, feds, fed_state, max_slab, params, global_, conf, hist_local, hist_global, write_back, do_metrics,
+           begin_next=False):
     p, gl, cf = _np(params), _np(global_), _np(conf)
     hl, hg = _np(hist_local), _np(hist_global)
     st = _np(fed_state).view(FEDSTATE_DTYPE)
@@ -395,3 +396,11 @@ def fedavg(groups, feds, fed_state, max_slab, params, global_, conf, hist_local,
                     st[f]["anchor"] = glob
                     st[f]["has_anchor"] = 1
                     st[f]["count"] = int(F["patience"])
+            st[f]["done"] = st[f]["round"]
+        if begin_next:
+            if st[f]["stop_pending"]:
+                st[f]["stop"] = 1
+            if not st[f]["stop"]:
+                st[f]["round"] += 1
+            first, n = int(F["first_group"]), int(F["n_clients"])
+            cf.reshape(-1, MAX_CLASSES, MAX_CLASSES)[first: first + n] = 0

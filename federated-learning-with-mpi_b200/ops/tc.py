@@ -92,12 +92,26 @@ def tc_cluster_size(groups: np.ndarray) -> int:
     return int(min(8, max(1, (rows + TC_ROWS - 1) // TC_ROWS)))
 
 
-def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf,
-                   batch: int = 0, n_steps: int = 1, do_eval: bool = True) -> None:
+def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch,
+                   batch: int = 0, n_steps: int = 1, do_eval: bool = True, prof=None) -> None:
+    """``prof``: optional int64[32] device tensor receiving clock64 stamps of CTA 0 (debug)."""
     lib = nat.lib(required=True)
-    nat.check(lib.fedb_local_round_tc(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y),
-                                      nat.ptr(idx), nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active),
-                                      nat.ptr(fed_state), nat.ptr(loss_out), nat.ptr(conf), batch, n_steps, int(do_eval),
-                                      nat.cuda_stream()))
+    nat.check(lib.fedb_local_round_tc_prof(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y),
+                                           nat.ptr(idx), nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active),
+                                           nat.ptr(fed_state), nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), batch, n_steps,
+                                           int(do_eval), nat.ptr(prof), nat.cuda_stream()))
+    from . import kernels as K
+    K._count()
+
+
+def round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
+             global_, hist_local, hist_global, tail_count, prof=None) -> None:
+    """The whole round in one launch (see fedb_round_tc in include/fedb200.h)."""
+    lib = nat.lib(required=True)
+    nat.check(lib.fedb_round_tc_prof(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
+                                nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
+                                nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(tb.d_feds), tb.n_feds,
+                                nat.ptr(global_), nat.ptr(hist_local), nat.ptr(hist_global), conf.numel(), nat.ptr(tail_count),
+                                nat.ptr(prof), nat.cuda_stream()))
     from . import kernels as K
     K._count()

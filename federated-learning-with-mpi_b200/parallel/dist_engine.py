@@ -127,18 +127,25 @@ class DistFedEngine(FedEngine):
                                                 self.bar, self.err, g_total, timeout_s)
         self.rank_dev = K.upload_table(self.rank_record, d)
         self.p2p_blocks = p2p.blocks_for(self.tb.max_slab)
-        self.kernel_names = [k for k in self.kernel_names if k != "k_fedavg"] + ["k_fedavg_p2p"]
 
-    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True) -> None:
-        p2p.launch(self.rank_dev, 1, self.p2p_blocks)
+    def _begin_is_fused(self) -> bool:
+        return True   # k_fedavg_p2p ends with the next round's begin bookkeeping
+
+    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> None:
+        p2p.launch(self.rank_dev, 1, self.p2p_blocks)   # begin_next is baked into the rank record (always on)
+
+    @property
+    def kernel_names(self) -> List[str]:
+        local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
+        return local + ["k_fedavg_p2p"]
 
     def history(self) -> Dict[str, np.ndarray]:
         st = self.fed_state_host()
-        R = int(st["round"].max()) if len(st) else 0
+        R = int(st["done"].max()) if len(st) else 0
         hg = self.hist_global.cpu().numpy().reshape(self.n_feds, self.max_rounds, 4)[:, :R].astype(np.float64)
         hl = self.hist_local.cpu().numpy().reshape(self.max_rounds, self.n_groups_total, 4)[:R].astype(np.float64)
         from ..fed.metrics import METRIC_NAMES
-        return {"global": hg, "local": hl, "rounds": st["round"].copy(),
+        return {"global": hg, "local": hl, "rounds": st["done"].copy(),
                 "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool), "last": st["last"].copy(),
                 "metric_names": np.asarray(METRIC_NAMES)}
 
@@ -185,7 +192,7 @@ class EmulatedWorld:
 
     def enqueue_round(self) -> None:
         for r in self.ranks:
-            r.enqueue_round_begin()
+            r.prime()
             r.enqueue_local_part()
         p2p.launch(self.table_dev, self.world, self.blocks)
 

@@ -88,7 +88,9 @@ class SymmetricBuffer:
 def make_rank_record(eng, rank: int, world: int, lay: SymLayout, sym_ptrs: Sequence[int], feds_global: torch.Tensor,
                      conf_all: torch.Tensor, hist_local: torch.Tensor, hist_global: torch.Tensor, src_rank: torch.Tensor,
                      src_slot: torch.Tensor, seq: torch.Tensor, bar: torch.Tensor, err: torch.Tensor, n_groups_total: int,
-                     timeout_s: float = 5.0, write_back: bool = True, do_metrics: bool = True) -> np.ndarray:
+                     timeout_s: float = 5.0, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> np.ndarray:
+    if eng.n_feds > 256:
+        raise ValueError("the cross-GPU aggregation kernel handles at most 256 federations per launch")
     r = np.zeros(1, dtype=nat.P2PRANK_DTYPE)
     r["rank"], r["world"], r["n_feds"], r["n_groups_local"] = rank, world, eng.n_feds, eng.n_groups
     r["n_groups_total"], r["conf_slots"], r["global_total"] = n_groups_total, lay.conf_slots, lay.global_total
@@ -103,7 +105,7 @@ def make_rank_record(eng, rank: int, world: int, lay: SymLayout, sym_ptrs: Seque
     r["sym_partial_off"], r["sym_conf_off"], r["sym_flag_off"] = lay.partial_off, lay.conf_off, lay.flag_off
     r["seq"], r["bar"], r["err"] = seq.data_ptr(), bar.data_ptr(), err.data_ptr()
     r["timeout_cycles"] = int(timeout_s * 1.9e9)
-    r["write_back"], r["do_metrics"] = int(write_back), int(do_metrics)
+    r["write_back"], r["do_metrics"], r["begin_next"] = int(write_back), int(do_metrics), int(begin_next)
     return r
 
 

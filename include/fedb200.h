@@ -83,7 +83,7 @@ typedef struct FedbFedState {
   int32_t round;     /* rounds started so far */
   int32_t count;     /* C:124 termination_count */
   int32_t has_anchor;
-  int32_t pad_;
+  int32_t done;      /* rounds whose metrics have been recorded */
   double anchor[4];  /* C:125 prev_metric */
   double last[4];    /* last global metrics */
 } FedbFedState;
@@ -132,6 +132,7 @@ typedef struct FedbP2PRank {
   int32_t* err;                         /* set to FEDB_E_TIMEOUT when a peer never arrived */
   int64_t timeout_cycles;
   int32_t write_back, do_metrics;
+  int32_t begin_next, pad_;
 } FedbP2PRank;
 
 const char* fedb_last_error(void);
@@ -190,20 +191,33 @@ int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const FedbTile* 
  * (C:119-120); block 0 of each federation also turns the round's confusion counts into
  * accuracy / weighted precision / recall / F1 (C:85-90), appends them to the history and
  * runs the early-stop rule (C:181-192).  hist_local: [max_rounds][n_groups][4] floats,
- * hist_global: [n_feds][max_rounds][4].  write_back=0 leaves client slabs untouched. */
+ * hist_global: [n_feds][max_rounds][4].  write_back=0 leaves client slabs untouched.
+ * begin_next=1 additionally does the next round's fedb_round_begin work for the federation
+ * (stop promotion, round count, clearing its clients' confusion slots); only valid when one block
+ * covers a federation's slab (max_slab <= 1024 floats) — larger problems call fedb_round_begin. */
 int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
                 int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
                 float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
-                void* stream);
+                int32_t begin_next, void* stream);
 
 /* K2a/K3 on tcgen05: n_steps local optimizer steps (+ local evaluation into conf slot g) for every
  * group in one launch, one thread-block cluster per client (csrc/fedb_tc.cu; C:63-91).  Groups
- * must have 2 hidden ReLU layers with in <= 15, h1 <= 63, h2 <= 256, out <= 8. */
+ * must have 2 hidden ReLU layers with in <= 15, h1 <= 63, h2 <= 256, out <= 8.  scratch: the
+ * gradient-record arena of fedb_fwd_bwd; every group needs max_tiles >= cluster_size records. */
 int64_t fedb_tc_smem_bytes(void);
 int fedb_local_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X,
                         int32_t ldx, const int32_t* y, const int32_t* idx, float* params, float* m, float* v,
                         int32_t* step, const int32_t* active, const FedbFedState* fed_state, float* loss_out,
-                        int32_t* conf, int32_t batch, int32_t n_steps, int32_t do_eval, void* stream);
+                        int32_t* conf, float* scratch, int32_t batch, int32_t n_steps, int32_t do_eval, void* stream);
+
+/* The whole round in ONE launch for small single-GPU problems: fedb_local_round_tc's work, then the
+ * last cluster to finish performs fedb_fedavg(write_back=1, do_metrics=1, begin_next=1) for every
+ * federation.  conf_ints counters are cleared for the next round; tail_count: one zeroed uint32. */
+int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
+                  const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                  const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
+                  int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
+                  float* hist_global, int32_t conf_ints, uint32_t* tail_count, void* stream);
 
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop

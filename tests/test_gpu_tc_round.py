@@ -61,7 +61,7 @@ def test_gradients_match_emulation_and_fp32(income, rows, clients, hidden):
     from fedb200.ops import tc as tcops
     f32.enqueue_local_step(0)
     tcops.local_round_tc(tc.tb, tc.tc_cluster, tc.X, tc.y, tc.idx, tc.params, tc.m, tc.v, tc.step, tc.active, tc.fed_state,
-                         tc.loss, tc.conf, 0, 1, False)
+                         tc.loss, tc.conf, tc.scratch, 0, 1, False)
     torch.cuda.synchronize()
     g32, gtc = (before - f32.params).cpu(), (before - tc.params).cpu()
     spec = f32.problems[0].spec
@@ -92,7 +92,7 @@ def test_eval_counts_match_simt(income):
     K.round_begin(f32.tb, f32.fed_state, f32.conf)
     f32.enqueue_eval_local()
     tcops.local_round_tc(tc.tb, tc.tc_cluster, tc.X, tc.y, tc.idx, tc.params, tc.m, tc.v, tc.step, tc.active, tc.fed_state,
-                         tc.loss, tc.conf, 0, 0, True)
+                         tc.loss, tc.conf, tc.scratch, 0, 0, True)
     torch.cuda.synchronize()
     a, b = f32.confusion()[:3], tc.confusion()[:3]
     assert a.sum() == b.sum() == 3000 and np.abs(a - b).sum() <= 30  # bf16 logits flip a few near-ties

@@ -17,5 +17,5 @@ def test_two_gpu_bench_runs_and_learns():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     rec = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
-    assert rec["n_gpus"] == 2 and rec["value"] > 0 and "k_fedavg_p2p" in rec["kernels"]
+    assert rec["n_gpus"] == 2 and rec["value"] > 0 and any("k_fedavg_p2p" in k for k in rec["kernels"])
     assert rec["final_global_accuracy_train_shards"] > 0.8
