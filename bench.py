@@ -34,7 +34,8 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"],
+                    help="ours | reference (unmodified scripts) | nccl (stock torch + NCCL all_reduce baseline)")
     ap.add_argument("--clients-per-gpu", type=int, default=1)
     ap.add_argument("--precision", default=None, help="ours: fp32 (SIMT) | tf32 (tcgen05); default = best available")
     ap.add_argument("--no-flush", action="store_true", help="debug: skip the L2 flush between timed steps")
@@ -217,9 +218,61 @@ def run_reference(args):
         print(json.dumps(rec))
 
 
+# ----------------------------------------------------------------------------------------------
+def run_nccl(args):
+    """Stock-PyTorch (cuBLAS + NCCL all_reduce) FedAvg of the same model and config."""
+    import numpy as np
+    import torch
+    rank, local_rank, world = dist_env()
+    torch.cuda.set_device(local_rank)
+    sys.path.insert(0, os.path.join(ROOT, "baseline", "nccl_cublas"))
+    from fedavg_torch import TorchFedAvg
+    from fedb200 import prepare
+    from fedb200.utils.clocks import ClockSampler
+    if world > 1:
+        from fedb200.parallel.dist_engine import init_distributed
+        init_distributed()
+    data = prepare(with_mean=True)
+    cpg = args.clients_per_gpu
+    rows = [(np.arange(ROWS_PER_CLIENT) + c * ROWS_PER_CLIENT) % len(data.X_train) for c in range(rank * cpg, (rank + 1) * cpg)]
+    fed = TorchFedAvg(data.X_train, data.y_train, rows, world * cpg * ROWS_PER_CLIENT)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    K, W = args.steps, args.warmup
+    for _ in range(W):
+        fed.round()
+    barrier()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    with ClockSampler(local_rank) as clk:
+        for s, e in ev:
+            flush.zero_()
+            s.record()
+            fed.round()
+            e.record()
+        barrier()
+    ms = torch.tensor([sum(s.elapsed_time(e) for s, e in ev)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    ms = float(ms.item())
+    if rank == 0:
+        rec = base_record(args, world, "nccl_cublas_baseline")
+        samples = world * cpg * ROWS_PER_CLIENT
+        value = samples * K / (ms / 1e3)
+        rec["config"]["parallelism"] = f"{world} ranks, torch.nn + torch.optim + NCCL all_reduce FedAvg"
+        rec.update({"value": value, "ms_per_step": ms / K, "vs_baseline": value / BASELINE_SAMPLES_PER_SEC, "dtype": "fp32",
+                    "rounds_per_sec": K / (ms / 1e3), "gpu_launches": None, "clocks": clk.summary(),
+                    "final_global_accuracy_train_shards": float(fed.last_metrics[0])})
+        print(json.dumps(rec))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
-        run_reference(a)
-    else:
-        run_ours(a)
+    {"reference": run_reference, "nccl": run_nccl, "ours": run_ours}[a.impl](a)

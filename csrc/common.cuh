@@ -154,36 +154,51 @@ __device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalar
 
 
 // ---- metrics from confusion counts + early stop (K3/K5), shared by the aggregation kernels ---------
-// Fully unrolled over FEDB_MAX_CLASSES so the per-class sums stay in registers (these run on the
-// critical path of every round, on a single warp).
+// a / b to ~1e-14 relative: single-precision quotient plus one double-precision residual correction.
+// IEEE double division is a ~100-instruction dependent chain; a round's metrics need a dozen of them
+// on ONE warp on the critical path, which measured at ~4 us.
+__device__ __forceinline__ double fast_ddiv(double a, double b) {
+  const float rb = 1.0f / (float)b;
+  const double q0 = (double)((float)a * rb);
+  return fma(fma(-q0, b, a), (double)rb, q0);
+}
+
+// Binary problems (every model of the reference) take a short straight-line path; the general case
+// is a compact rolled loop.  Code size matters here: this runs once per round on one warp, and a
+// fully unrolled 8x8 version spent more time missing the instruction cache than computing.
 __device__ inline void metrics_from_conf(const int32_t* cm, int C, double out[4]) {
-  double total = 0, tr = 0;
-  double sup[FEDB_MAX_CLASSES], prd[FEDB_MAX_CLASSES], dg[FEDB_MAX_CLASSES];
-#pragma unroll
-  for (int c = 0; c < FEDB_MAX_CLASSES; ++c) { sup[c] = 0; prd[c] = 0; dg[c] = 0; }
-#pragma unroll
-  for (int i = 0; i < FEDB_MAX_CLASSES; ++i)
-#pragma unroll
-    for (int j = 0; j < FEDB_MAX_CLASSES; ++j)
-      if (i < C && j < C) {
-        const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
-        total += x; sup[i] += x; prd[j] += x;
-        if (i == j) { tr += x; dg[i] = x; }
-      }
   out[0] = out[1] = out[2] = out[3] = 0.0;
-  if (total == 0) return;
-  out[0] = tr / total;
-#pragma unroll
-  for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
-    if (c < C) {
-      const double tp = dg[c];
-      const double w = sup[c] / total;
-      const double p = prd[c] > 0 ? tp / prd[c] : 0.0;
-      const double r = sup[c] > 0 ? tp / sup[c] : 0.0;
-      const double den = sup[c] + prd[c];
-      const double f = den > 0 ? 2.0 * tp / den : 0.0;
-      out[1] += p * w; out[2] += r * w; out[3] += f * w;
+  if (C == 2) {
+    const double c00 = (double)cm[0], c01 = (double)cm[1], c10 = (double)cm[FEDB_MAX_CLASSES], c11 = (double)cm[FEDB_MAX_CLASSES + 1];
+    const double s0 = c00 + c01, s1 = c10 + c11, p0 = c00 + c10, p1 = c01 + c11, total = s0 + s1;
+    if (total == 0) return;
+    const double it = fast_ddiv(1.0, total), w0 = s0 * it, w1 = s1 * it;
+    out[0] = (c00 + c11) * it;
+    out[1] = (p0 > 0 ? fast_ddiv(c00, p0) : 0.0) * w0 + (p1 > 0 ? fast_ddiv(c11, p1) : 0.0) * w1;
+    out[2] = (s0 > 0 ? fast_ddiv(c00, s0) : 0.0) * w0 + (s1 > 0 ? fast_ddiv(c11, s1) : 0.0) * w1;
+    out[3] = (s0 + p0 > 0 ? fast_ddiv(2.0 * c00, s0 + p0) : 0.0) * w0 + (s1 + p1 > 0 ? fast_ddiv(2.0 * c11, s1 + p1) : 0.0) * w1;
+    return;
+  }
+  double total = 0, tr = 0;
+  for (int i = 0; i < C; ++i)
+    for (int j = 0; j < C; ++j) {
+      const double x = (double)cm[i * FEDB_MAX_CLASSES + j];
+      total += x;
+      if (i == j) tr += x;
     }
+  if (total == 0) return;
+  out[0] = fast_ddiv(tr, total);
+#pragma unroll 1
+  for (int c = 0; c < C; ++c) {
+    double sup = 0, prd = 0;
+    for (int j = 0; j < C; ++j) { sup += (double)cm[c * FEDB_MAX_CLASSES + j]; prd += (double)cm[j * FEDB_MAX_CLASSES + c]; }
+    const double tp = (double)cm[c * FEDB_MAX_CLASSES + c];
+    const double w = fast_ddiv(sup, total);
+    const double p = prd > 0 ? fast_ddiv(tp, prd) : 0.0;
+    const double r = sup > 0 ? fast_ddiv(tp, sup) : 0.0;
+    const double f = sup + prd > 0 ? fast_ddiv(2.0 * tp, sup + prd) : 0.0;
+    out[1] += p * w; out[2] += r * w; out[3] += f * w;
+  }
 }
 
 // C:181-192: anchor / patience early-stop rule on the four global metrics.
@@ -214,7 +229,8 @@ __device__ inline void begin_next_round(FedbFedState& S) {
 // k, k+32, ... (per-client metrics -> hist_local), a fixed xor-tree adds them up (mean of local
 // metrics, C:169) or the pooled counts are scored (S:130-134); lane 0 then records the global
 // metrics and runs the early-stop rule.  `pool` = 64 ints of shared memory.  All 32 lanes must call.
-__device__ inline void round_metrics_warp(const FedbFed& F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
+// (F is taken BY VALUE: through a pointer every field access may be re-fetched from L2 after each store)
+__device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
                                           float* hist_local, float* hist_global, int* pool, bool begin_next = false) {
   const int lane = threadIdx.x & 31;
   const int C = F.n_classes;
@@ -246,7 +262,7 @@ __device__ inline void round_metrics_warp(const FedbFed& F, FedbFedState& S, int
     double glob[4];
     if (pooled) metrics_from_conf(pool, C, glob);
     else
-      for (int i = 0; i < 4; ++i) glob[i] = acc[i] / (double)F.n_clients;
+      for (int i = 0; i < 4; ++i) glob[i] = fast_ddiv(acc[i], (double)F.n_clients);
     if (hist_global && r >= 0 && r < F.max_rounds)
       *reinterpret_cast<float4*>(hist_global + ((size_t)f * F.max_rounds + r) * 4) =
           make_float4((float)glob[0], (float)glob[1], (float)glob[2], (float)glob[3]);

@@ -755,6 +755,7 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
       }
     }
   }
+  if (a.prof && crank == 0 && tid == 0) a.prof[20] = clock64();
   if (crank == 0) {   // metrics read only the confusion counts: they overlap the averaging above
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32)
@@ -763,6 +764,7 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
         round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true);
       }
     __syncthreads();
+    if (a.prof && tid == 0) a.prof[21] = clock64();
     for (int i = tid; i < a.n_conf; i += TC_THREADS) a.conf[i] = 0;
   }
 }

@@ -51,4 +51,4 @@ if __name__ == "__main__":
                     1, e.global_, e.hist_local, e.hist_global, e.tail_count, prof)
         torch.cuda.synchronize()
     p = prof.cpu().numpy()
-    print("timeline (cycles from start):", {i: int(p[i] - p[0]) for i in range(20) if p[i]})
+    print("timeline (cycles from start):", {i: int(p[i] - p[0]) for i in range(24) if p[i]})
