@@ -78,22 +78,6 @@ struct TcArgs {
   unsigned int* tail_count;   // wraps to 0 by itself (atomicInc)
 };
 
-// step_scalars() in single precision (exp2f/log2f instead of double pow): evaluated by one thread
-// on the critical path of every step, where the double version costs ~3K cycles.  |rel err| < 1e-5.
-__device__ inline StepScalars step_scalars_fast(const FedbGroup& G, int t) {
-  StepScalars s;
-  float lr = G.lr;
-  if (G.lr_step_size > 0) lr *= exp2f((float)((t - 1) / G.lr_step_size) * log2f(G.lr_gamma));
-  if (G.opt == FEDB_OPT_SGD) {
-    s.lr_eff = lr; s.inv_sqrt_bc2 = 1.f;
-    return s;
-  }
-  const float bc1 = 1.f - exp2f((float)t * log2f(G.beta1)), bc2 = 1.f - exp2f((float)t * log2f(G.beta2));
-  if (G.opt == FEDB_OPT_ADAM_TORCH) { s.lr_eff = lr / bc1; s.inv_sqrt_bc2 = rsqrtf(bc2); }
-  else { s.lr_eff = lr * sqrtf(bc2) / bc1; s.inv_sqrt_bc2 = 1.f; }
-  return s;
-}
-
 struct Shape {
   int d0, h1, h2, C, N2, NP2, MT2;
   int ld0, ld1, ld2;

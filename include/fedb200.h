@@ -135,6 +135,36 @@ typedef struct FedbP2PRank {
   int32_t begin_next, pad_;
 } FedbP2PRank;
 
+/* Grouped tensor-core GEMM of the wide-MLP path (csrc/fedb_gemm.cu).  blockIdx.z = group (client);
+ * operand X of group g starts at X + g * x_group_stride (elements).  a_mn / b_mn: 0 = K-major source
+ * ([M or N][K], K contiguous), 1 = MN-major source ([K][M or N], M or N contiguous). */
+enum { FEDB_GEMM_FWD_BIAS_RELU = 0, FEDB_GEMM_DGRAD_MASK = 1, FEDB_GEMM_WGRAD_OPT = 2, FEDB_GEMM_STORE_F32 = 3 };
+typedef struct FedbGemm {
+  const void* A;                 /* bf16 */
+  const void* B;                 /* bf16 */
+  int64_t a_group_stride, b_group_stride;
+  int32_t lda, ldb;
+  int32_t M, N, K;
+  int32_t a_mn, b_mn;
+  int32_t epilogue;
+  const float* bias;             /* FWD: fp32 [N] per group */
+  int64_t bias_group_stride;
+  void* C;                       /* FWD / DGRAD: bf16 [M][ldc]; STORE_F32: fp32 */
+  int64_t c_group_stride;
+  int32_t ldc, ldact;
+  const void* act;               /* DGRAD: bf16 forward activation [M][ldact] whose sign gates the gradient */
+  int64_t act_group_stride;
+  float* W;                      /* WGRAD_OPT: fp32 master weights [M][ldw] (+ moments, bf16 shadow), updated in place */
+  float* Mom;
+  float* Vel;
+  void* Wsh;
+  int64_t w_group_stride;
+  int32_t ldw;
+  float l2_scale;                /* WGRAD_OPT: gradient += alpha * l2_scale * w (sklearn: 1 / n_batch) */
+  const FedbGroup* groups;       /* WGRAD_OPT: optimizer hyper-parameters per group */
+  const int32_t* step;           /* WGRAD_OPT: optimizer step count t per group (already incremented) */
+} FedbGemm;
+
 const char* fedb_last_error(void);
 int fedb_version(void);
 void fedb_struct_sizes(int32_t* out5); /* sizeof of the five structs above, for binding checks */
@@ -218,6 +248,11 @@ int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_siz
                   const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                   int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
                   float* hist_global, int32_t conf_ints, uint32_t* tail_count, void* stream);
+
+/* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
+ * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
+int32_t fedb_gemm_args_size(void);
+int fedb_gemm_tc(const FedbGemm* args_host, int32_t n_groups, void* stream);
 
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop

@@ -1,0 +1,76 @@
+"""Grouped tcgen05 GEMM (csrc/fedb_gemm.cu) vs torch, for the three operand-layout combinations a
+Linear layer needs and every epilogue."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+def _close(got, want, tol=1.5e-2):
+    err = (got.float() - want.float()).abs().max().item()
+    assert err <= tol * max(1.0, want.float().abs().max().item()), err
+
+
+@pytest.mark.parametrize("G,B,IN,OUT", [(2, 128, 64, 128), (3, 256, 192, 320), (1, 128, 16, 256), (2, 384, 4096, 128)])
+def test_forward_bias_relu(G, B, IN, OUT):
+    from fedb200.ops import gemm as gm
+    g = torch.Generator(device="cuda").manual_seed(0)
+    X = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
+    W = _bf(torch.randn(G, OUT, IN, device="cuda", generator=g) / IN ** 0.5)
+    b = torch.randn(G, OUT, device="cuda", generator=g)
+    Y = torch.empty(G, B, OUT, device="cuda", dtype=torch.bfloat16)
+    gm.gemm(G, B, OUT, IN, X, B * IN, IN, False, W, OUT * IN, IN, False, gm.FWD_BIAS_RELU, C=Y, c_stride=B * OUT, ldc=OUT,
+            bias=b, bias_stride=OUT)
+    torch.cuda.synchronize()
+    want = torch.relu(torch.einsum("gbi,goi->gbo", X.float(), W.float()) + b[:, None, :])
+    _close(Y, want)
+
+
+@pytest.mark.parametrize("G,B,IN,OUT", [(2, 128, 128, 64), (2, 256, 320, 192), (1, 128, 4096, 256)])
+def test_dgrad_mask(G, B, IN, OUT):
+    """dX = (dZ @ W) * (act > 0): A = dZ [B][OUT] K-major, B = W [OUT][IN] as an MN-major operand."""
+    from fedb200.ops import gemm as gm
+    g = torch.Generator(device="cuda").manual_seed(1)
+    dZ = _bf(torch.randn(G, B, OUT, device="cuda", generator=g))
+    W = _bf(torch.randn(G, OUT, IN, device="cuda", generator=g) / OUT ** 0.5)
+    act = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
+    dX = torch.empty(G, B, IN, device="cuda", dtype=torch.bfloat16)
+    gm.gemm(G, B, IN, OUT, dZ, B * OUT, OUT, False, W, OUT * IN, IN, True, gm.DGRAD_MASK, C=dX, c_stride=B * IN, ldc=IN,
+            act=act, act_stride=B * IN, ldact=IN)
+    torch.cuda.synchronize()
+    want = torch.einsum("gbo,goi->gbi", dZ.float(), W.float()) * (act.float() > 0)
+    _close(dX, want)
+
+
+@pytest.mark.parametrize("G,B,IN,OUT", [(2, 128, 64, 128), (2, 256, 192, 384), (1, 1024, 16, 128)])
+def test_wgrad_store_and_fused_sgd(G, B, IN, OUT):
+    """dW = dZ^T @ A with both operands MN-major; then the same GEMM with the optimizer in its epilogue."""
+    from fedb200.ops import gemm as gm
+    from fedb200.ops import _native as nat
+    g = torch.Generator(device="cuda").manual_seed(2)
+    dZ = _bf(torch.randn(G, B, OUT, device="cuda", generator=g))
+    A = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
+    dW = torch.empty(G, OUT, IN, device="cuda", dtype=torch.float32)
+    gm.gemm(G, OUT, IN, B, dZ, B * OUT, OUT, True, A, B * IN, IN, True, gm.STORE_F32, C=dW, c_stride=OUT * IN, ldc=IN)
+    torch.cuda.synchronize()
+    want = torch.einsum("gbo,gbi->goi", dZ.float(), A.float())
+    _close(dW, want, 5e-3)
+    # fused SGD(lr=0.5, momentum=0): W <- W - 0.5 * dW, bf16 shadow refreshed
+    groups = np.zeros(G, dtype=nat.GROUP_DTYPE)
+    groups["opt"], groups["lr"], groups["lr_gamma"] = nat.OPT_IDS["sgd"], 0.5, 1.0
+    d_groups = torch.from_numpy(groups.view(np.uint8).copy()).cuda()
+    step = torch.ones(G, dtype=torch.int32, device="cuda")
+    W = torch.randn(G, OUT, IN, device="cuda", generator=g)
+    W0 = W.clone()
+    Mo, Ve = torch.zeros_like(W), torch.zeros_like(W)
+    Wsh = torch.zeros(G, OUT, IN, device="cuda", dtype=torch.bfloat16)
+    gm.gemm(G, OUT, IN, B, dZ, B * OUT, OUT, True, A, B * IN, IN, True, gm.WGRAD_OPT, W=W, Mom=Mo, Vel=Ve, Wsh=Wsh,
+            w_stride=OUT * IN, ldw=IN, groups=d_groups, step=step)
+    torch.cuda.synchronize()
+    _close(W, W0 - 0.5 * want, 5e-3)
+    assert torch.equal(Wsh, W.to(torch.bfloat16))
