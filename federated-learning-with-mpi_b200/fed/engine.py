@@ -75,8 +75,16 @@ class FedEngine:
         full_batch = all(p.hyper.batch_size <= 0 and p.hyper.max_iter <= 0 for p in self.problems)
         ok = self.device.type == "cuda" and full_batch and tc.tc_eligible(self.tb.groups)
         req = self._precision_req
+        self.wide = None
         if req in (None, "auto"):
-            req = "bf16" if ok else "fp32"
+            req = "bf16" if ok else ("bf16_wide" if (self.tb.smem_bytes < 0 and self.device.type == "cuda") else "fp32")
+        if req == "bf16_wide":
+            from .wide import WideLocal
+            if self.device.type != "cuda":
+                raise ValueError("the wide (layer-wise tensor-core) path needs a CUDA device")
+            self.precision_name = "bf16_wide"
+            self._wide_pending = True
+            return
         if req in ("bf16", "tc", "tf32"):
             if not ok:
                 raise ValueError("the tensor-core path needs a CUDA device, full-batch steps and 3-layer ReLU MLPs with "
@@ -183,7 +191,7 @@ class FedEngine:
         z = lambda n, dt=torch.float32: torch.zeros(n, dtype=dt, device=d)
         self.params, self.m, self.v = z(self.params_total), z(self.params_total), z(self.params_total)
         self.global_ = z(self.global_total)
-        self.scratch = z(self.scratch_total)
+        self.scratch = z(self.scratch_total if self.tb.smem_bytes >= 0 else 32)   # (the wide path keeps no per-tile gradient records)
         self.step = z(G, torch.int32)
         self.active = torch.ones(G, dtype=torch.int32, device=d)
         self.loss = z(G)
@@ -201,6 +209,13 @@ class FedEngine:
         self.batch_stats = z(G * self.n_batches * self.bs_stride, torch.float64)
         self.idx_epoch = self.idx.clone()
         self.tail_count = z(1, torch.int32)
+
+    def _ensure_wide(self):
+        if getattr(self, "_wide_pending", False):
+            from .wide import WideLocal
+            self._wide_pending = False
+            self.wide = WideLocal(self)
+        return self.wide
 
     def init_params(self) -> None:
         """(Re-)initialise every client's parameters and clear optimizer state (K4)."""
@@ -222,6 +237,9 @@ class FedEngine:
         self.m.zero_()
         self.v.zero_()
         self.step.zero_()
+        if self.precision_name == "bf16_wide":
+            w = self._ensure_wide()
+            w.refresh_shadow()
 
     # ------------------------------------------------------------------------------ rounds
     def enqueue_local_step(self, batch: int = 0, idx: Optional[torch.Tensor] = None, stats: bool = False) -> None:
@@ -239,6 +257,8 @@ class FedEngine:
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = False) -> None:
         K.fedavg(self.tb, self.fed_state, self.params, self.global_, self.conf, self.hist_local, self.hist_global,
                  write_back, do_metrics, begin_next)
+        if self.precision_name == "bf16_wide" and write_back:
+            self.wide.refresh_shadow()   # the averaged fp32 weights replace every client's bf16 operands
 
     def _begin_is_fused(self) -> bool:
         """True when the aggregation kernel also performs the next round's begin bookkeeping (the
@@ -281,7 +301,11 @@ class FedEngine:
     def enqueue_local_part(self) -> None:
         """Everything a round does that involves only resident clients: E local steps + local eval."""
         E = max(p.hyper.local_epochs for p in self.problems)
-        if self.precision_name == "bf16":
+        if self.precision_name == "bf16_wide":
+            for _ in range(E):
+                self.wide.enqueue_step()
+            self.wide.enqueue_eval()
+        elif self.precision_name == "bf16":
             from ..ops import tc
             tc.local_round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step,
                               self.active, self.fed_state, self.loss, self.conf, self.scratch, 0, E, True)
@@ -296,6 +320,8 @@ class FedEngine:
         E = max(p.hyper.local_epochs for p in self.problems)
         if self._fused_round_ok():
             return 1
+        if self.precision_name == "bf16_wide":
+            return 1 + E * self.wide.launches_per_step + (self.wide.L - 1) + 1 + 2
         if self.precision_name == "bf16":
             return 3 if not self._begin_is_fused() else 2
         return 1 + 2 * E * self.n_batches + 2
@@ -427,6 +453,8 @@ class FedEngine:
         whole train set).  The reference broadcasts X_test/y_test and never uses them
         (C:245-246); this is the extension BASELINE.md's accuracy band was measured with."""
         from .metrics import metrics_from_confusion
+        if self.tb.smem_bytes < 0:
+            return self._evaluate_global_torch(which)
         jobs_np, d_jobs, tiles, n_tiles = self._global_jobs[which]
         base = self.n_groups if which == "test" else self.n_groups + self.n_feds
         C2 = nat.MAX_CLASSES ** 2
@@ -435,6 +463,24 @@ class FedEngine:
                    self.conf, None)
         cm = self.confusion()
         return [metrics_from_confusion(cm[base + f][: p.spec.n_classes, : p.spec.n_classes]) for f, p in enumerate(self.problems)]
+
+    def _evaluate_global_torch(self, which: str) -> List[Dict[str, float]]:
+        """Held-out evaluation for models too wide for the SIMT eval kernel: a plain fp32 torch forward
+        of the global slab (reporting only — not part of any round)."""
+        from .metrics import confusion_matrix, metrics_from_confusion
+        lo, n = (self.n_train, self.n_test) if which == "test" else (0, self.n_train)
+        X, y = self.X[lo: lo + n], self.y[lo: lo + n]
+        out = []
+        for f, p in enumerate(self.problems):
+            s, slab = p.spec, self.global_slab(f)
+            a = X[:, : s.dims[0]]
+            for l in range(s.n_layers):
+                a = a @ s.weight_view(slab, l).T + s.bias_view(slab, l)
+                if l + 1 < s.n_layers:
+                    a = torch.relu(a)
+            pred = a.argmax(1) if s.head == "softmax_ce" else (a[:, 0] > 0).long()
+            out.append(metrics_from_confusion(confusion_matrix(y.cpu().numpy(), pred.cpu().numpy(), s.n_classes)))
+        return out
 
     def save_checkpoint(self, path: str, f: int = 0, resume: bool = False) -> None:
         from ..models.checkpoint import save_checkpoint
@@ -519,6 +565,9 @@ class FedEngine:
         """Kernels launched per steady-state round (the first round additionally runs k_round_begin)."""
         if self._fused_round_ok():
             return ["k_local_round_tc[train+eval+fedavg+metrics]"]
+        if self.precision_name == "bf16_wide":
+            return ["k_round_begin", "k_gemm_tc[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
+                    "k_fedavg", "k_wide_shadow"]
         if self.precision_name == "bf16":
             return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]
         return ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]

@@ -226,6 +226,11 @@ OPTIONAL_SIGS = {
     "fedb_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P], _I32),
     "fedb_local_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),
     "fedb_noalloc_scratch_floats": ([], _I64),
+    "fedb_wide_gather_x": ([_P, _I32, _P, _I32, _P, _P, _I32, _I32, _P], _I32),
+    "fedb_wide_shadow": ([_P, _P, _I64, _P], _I32),
+    "fedb_wide_head_fwd": ([_P, _I32, _P, _P, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _I32, _P], _I32),
+    "fedb_wide_head_bwd": ([_P, _I32, _P, _P, _P, _P, _P, _I32, _I32, _P, _P, _P, _P, _P, _P, _P], _I32),
+    "fedb_wide_bias_opt": ([_P, _I32, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P, _P], _I32),
     "fedb_gemm_args_size": ([], _I32),
     "fedb_gemm_tc": ([_P, _I32, _P], _I32),
     "fedb_p2p_rank_size": ([], _I32),

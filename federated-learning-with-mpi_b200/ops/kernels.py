@@ -51,7 +51,11 @@ class DeviceTables:
         max_slab = int(groups["slab_size"].max())
         smem = 0
         for g in groups:
-            smem = max(smem, simt_smem_bytes(g["dims"], int(g["n_layers"])))
+            try:
+                smem = max(smem, simt_smem_bytes(g["dims"], int(g["n_layers"])))
+            except ValueError:
+                smem = -1   # too wide for the whole-network SIMT kernels: only the layer-wise (wide) path can run it
+                break
         d_groups = torch.from_numpy(groups.view(np.uint8).copy()).to(device)
         d_feds = torch.from_numpy(feds.view(np.uint8).copy()).to(device)
         return DeviceTables(groups, feds, d_groups, d_feds, max_slab, smem)

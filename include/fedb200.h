@@ -254,6 +254,20 @@ int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_siz
 int32_t fedb_gemm_args_size(void);
 int fedb_gemm_tc(const FedbGemm* args_host, int32_t n_groups, void* stream);
 
+/* Wide-MLP path, the kernels around fedb_gemm_tc (csrc/fedb_wide.cu).  A* / dZ are bf16 [G][B][d]
+ * activation buffers (B rows per client, padded shards must be equal-sized); dz is fp32 [G][B][8]. */
+int fedb_wide_gather_x(const FedbGroup* groups, int32_t n_groups, const float* X, int32_t ldx, const int32_t* idx,
+                       void* A0, int32_t B, int32_t ld0, void* stream);
+int fedb_wide_shadow(const float* src, void* dst, int64_t n_floats, void* stream);
+int fedb_wide_head_fwd(const FedbGroup* groups, int32_t n_groups, const float* params, const void* A, int32_t B, int32_t d,
+                       const int32_t* y, const int32_t* idx, float* dz, float* loss_rows, int32_t* conf, int32_t* step,
+                       const FedbFedState* fed_state, int32_t eval_mode, void* stream);
+int fedb_wide_head_bwd(const FedbGroup* groups, int32_t n_groups, float* params, float* m, float* v, void* shadow,
+                       const void* A, int32_t B, int32_t d, const float* dz, const float* loss_rows, void* dZ,
+                       const int32_t* step, const FedbFedState* fed_state, float* loss_out, void* stream);
+int fedb_wide_bias_opt(const FedbGroup* groups, int32_t n_groups, float* params, float* m, float* v, const void* dZ,
+                       int32_t B, int32_t d, int32_t layer, const int32_t* step, const FedbFedState* fed_state, void* stream);
+
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop
  * (csrc/fedb_p2p.cu; C:101-120, C:165-192).  ranks_dev[0..n_ranks_here): one entry in real
