@@ -34,7 +34,7 @@ namespace cg = cooperative_groups;
 namespace fedb {
 namespace {
 
-constexpr int TC_THREADS = 128;
+constexpr int TC_THREADS = 256;   // two threads per data row (see local_round_body)
 constexpr int TC_ROWS = 128;
 constexpr int PANEL = 128 * 128;  // bytes of a [128][64] bf16 panel
 // shared-memory map (bytes from the 1024-aligned base)
@@ -48,9 +48,11 @@ constexpr int SM_W2 = SM_W1 + 64 * 128;       // [256][64] bf16
 constexpr int SM_W3 = SM_W2 + 256 * 128;      // fp32 [8][256]
 constexpr int SM_B3 = SM_W3 + 8 * 256 * 4;    // fp32 [8], then scalars
 constexpr int SM_END = SM_B3 + 256;
+constexpr int SM_SLOTS = SM_END;               // [CS][per] float4 partial-gradient slices + CS loss floats (never overlaps live panels)
+constexpr int SLOTS_MAX_BYTES = 227 * 1024 - 4096 - SM_SLOTS;   // what is left of the SM's shared memory
 constexpr int SM_STAGE = SM_H1;               // fp32 gradient staging overlays H1..Z once the MMAs are done
 // TMEM columns
-constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 320, TM_DW1 = 448, TM_DW3 = 464;
+constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 320, TM_DW1 = 448, TM_DW3 = 464, TM_ZX = 496;   // ZX: 2 x 8 logit-exchange columns
 
 struct TcArgs {
   const FedbGroup* groups;
@@ -132,40 +134,33 @@ __device__ void convert_weights(uint8_t* sm, const float* L, const SlabLayout& l
   __syncthreads();
 }
 
-// One data row per thread: global -> registers (issued early so the latency overlaps other work)
+// Two threads per data row: half h moves columns 8h..8h+7 (global -> registers, issued early so the
+// latency overlaps other work; then registers -> X panel as bf16, column 15 = 1 on valid rows).
 struct RowRegs {
-  float4 q[4];
+  float4 q[2];
   int label;
 };
-__device__ __forceinline__ RowRegs fetch_row(const TcArgs& a, int64_t pos, bool valid) {
+__device__ __forceinline__ RowRegs fetch_row(const TcArgs& a, int64_t pos, bool valid, int half) {
   RowRegs r;
   r.label = 0;
+  r.q[0] = r.q[1] = make_float4(0.f, 0.f, 0.f, 0.f);
   if (valid) {
     const int row = __ldg(a.idx + pos);
-    const float4* src = reinterpret_cast<const float4*>(a.X + (size_t)row * a.ldx);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) r.q[q] = __ldg(src + q);
+    const float4* src = reinterpret_cast<const float4*>(a.X + (size_t)row * a.ldx) + 2 * half;
+    r.q[0] = __ldg(src);
+    r.q[1] = __ldg(src + 1);
     r.label = __ldg(a.y + row);
-  } else {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) r.q[q] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   return r;
 }
-// registers -> X panel (bf16; column 15 = 1 on valid rows). Returns the label.
-__device__ __forceinline__ int store_row(uint8_t* sm, const RowRegs& r, bool valid, const Shape& s) {
-  const int t = threadIdx.x;
-  float f[16];
+__device__ __forceinline__ int store_row(uint8_t* sm, const RowRegs& r, bool valid, const Shape& s, int row, int half) {
+  float f[8] = {r.q[0].x, r.q[0].y, r.q[0].z, r.q[0].w, r.q[1].x, r.q[1].y, r.q[1].z, r.q[1].w};
 #pragma unroll
-  for (int q = 0; q < 4; ++q) { f[4 * q] = r.q[q].x; f[4 * q + 1] = r.q[q].y; f[4 * q + 2] = r.q[q].z; f[4 * q + 3] = r.q[q].w; }
-#pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (i >= s.d0) f[i] = 0.f;
-  f[15] = valid ? 1.f : 0.f;
-#pragma unroll
-  for (int c = 0; c < 2; ++c)
-    st16(sm + SM_X + tc::panel_off(t, 8 * c), tc::pack_bf16(f[8 * c], f[8 * c + 1]), tc::pack_bf16(f[8 * c + 2], f[8 * c + 3]),
-         tc::pack_bf16(f[8 * c + 4], f[8 * c + 5]), tc::pack_bf16(f[8 * c + 6], f[8 * c + 7]));
+  for (int i = 0; i < 8; ++i)
+    if (8 * half + i >= s.d0) f[i] = 0.f;
+  if (half == 1) f[7] = valid ? 1.f : 0.f;
+  st16(sm + SM_X + tc::panel_off(row, 8 * half), tc::pack_bf16(f[0], f[1]), tc::pack_bf16(f[2], f[3]), tc::pack_bf16(f[4], f[5]),
+       tc::pack_bf16(f[6], f[7]));
   return r.label;
 }
 
@@ -228,6 +223,9 @@ struct Issuer {
 
 }  // namespace
 
+// Row <-> thread mapping: 256 threads, two per data row.  Thread t serves row (t & 127) — TMEM lane
+// (t & 127), reachable from warps w and w + 4 alike — and the column half (t >> 7) of every epilogue,
+// so each scheduler has two warps to interleave and every epilogue takes half as long.
 __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_raw) {
   __shared__ uint64_t bar, wbar;
   __shared__ uint32_t tmem_slot;
@@ -265,11 +263,17 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
   s.ld0 = ru4(s.d0); s.ld1 = ru4(s.h1); s.ld2 = ru4(s.h2);
   const SlabLayout lay = slab_layout(G.dims, 3);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & 127, half = tid >> 7;
   const int step0 = a.step[g];
   float* Pg = a.params + G.slab_off;
+  // gradient exchange geometry: CTA o owns float4 indices [o*per, (o+1)*per) of the slab
+  const int n4 = lay.end >> 2, per = (n4 + CS - 1) / CS;
+  const uint32_t inv_per = 0xFFFFFFFFu / (uint32_t)per + 1u;   // e4 / per == __umulhi(e4, inv_per) for e4 < 2^16
+  const int lo = q * per, hi = min(n4, lo + per);
 
-  if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
   float* landing = reinterpret_cast<float*>(sm + SM_STAGE);   // fp32 slab landing zone (idle panel area)
+  float4* slots = reinterpret_cast<float4*>(sm + SM_SLOTS);   // [CS][per] partial-gradient slices sent by every CTA
+  if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
   if (tid == 0) {
     tc::mbar_init(&bar, 1);
     tc::mbar_init(&wbar, 1);
@@ -281,17 +285,33 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);  // this thread's TMEM lane
+  const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);  // this thread's TMEM lane
   const Issuer mma{tc::make_desc(sm_u, 0, 1024), tc::make_desc(sm_u, PANEL, 1024), tmem};
   uint32_t ph = 0, wph = 0;
   float* W3s = reinterpret_cast<float*>(sm + SM_W3);
   float* b3s = reinterpret_cast<float*>(sm + SM_B3);
   const float inv_n = 1.f / (float)nb;
+  // peers' slot arrays / landing zones over distributed shared memory
+  float4* peer_slots[8];
+  float4* peer_land[8];
+#pragma unroll
+  for (int rk = 0; rk < 8; ++rk) {
+    peer_slots[rk] = cluster.map_shared_rank(slots, rk < CS ? rk : 0);
+    peer_land[rk] = reinterpret_cast<float4*>(cluster.map_shared_rank(landing, rk < CS ? rk : 0));
+  }
+  // one gradient float4 (slab index e4) -> the owner CTA's slot for this CTA
+  auto send_grad = [&](int e4, const float4 v) {
+    const int o = (int)__umulhi((uint32_t)e4, inv_per);
+    float4* dst = peer_slots[0];
+#pragma unroll
+    for (int rk = 1; rk < 8; ++rk) dst = (o == rk) ? peer_slots[rk] : dst;
+    dst[q * per + (e4 - o * per)] = v;
+  };
 
 #define STAMP(i) do { if (a.prof && blockIdx.x == 0 && tid == 0) a.prof[i] = clock64(); } while (0)
   STAMP(0);
   // first tile's row: issue its loads before the weight conversion so both latencies overlap
-  RowRegs rr = fetch_row(a, G.idx_off + b0 + q * TC_ROWS + tid, q < ntiles && q * TC_ROWS + tid < nb);
+  RowRegs rr = fetch_row(a, G.idx_off + b0 + q * TC_ROWS + row, q < ntiles && q * TC_ROWS + row < nb, half);
   tc::mbar_wait(&wbar, wph); wph ^= 1;
   convert_weights(sm, landing, lay, s);
   STAMP(1);
@@ -308,6 +328,9 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
     tc::tc_fence_after();                \
   } while (0)
 
+  // split of the layer-2 columns between the two halves (in 16-column chunks)
+  const int nch2 = s.N2 >> 4, ch_lo = half ? (nch2 + 1) >> 1 : 0, ch_hi = half ? nch2 : (nch2 + 1) >> 1;
+
   for (int st = 0; st < a.n_steps; ++st) {
     float loss_acc = 0.f, db3_acc[FEDB_MAX_CLASSES];
 #pragma unroll
@@ -316,30 +339,31 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
 
     for (int tile = q; tile < ntiles; tile += CS, ++my_tiles) {
       const bool acc = my_tiles > 0;
-      const int r = tile * TC_ROWS + tid;
+      const int r = tile * TC_ROWS + row;
       const bool valid = r < nb;
-      if (my_tiles > 0 || st > 0) rr = fetch_row(a, G.idx_off + b0 + r, valid);
-      const int label = store_row(sm, rr, valid, s);
+      if (my_tiles > 0 || st > 0) rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+      const int label = store_row(sm, rr, valid, s, row, half);
       handoff();
       STAMP(2);
       // ---- layer 1 -----------------------------------------------------------------------
       FEDB_MMA_PHASE(mma.fwd1(s));
       STAMP(3);
-      uint64_t mask1 = 0;
+      uint32_t mask1 = 0;   // ReLU mask of this half's 32 columns of H1
       {
         float v[16];
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c0 = 32 * half + 16 * cc;
           tc::tmem_ld16(tl + TM_D1 + c0, v);
           tc::tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            if (v[i] > 0.f) mask1 |= 1ull << (c0 + i); else v[i] = 0.f;
+            if (v[i] > 0.f) mask1 |= 1u << (16 * cc + i); else v[i] = 0.f;
           }
-          if (c0 == 48) { v[15] = valid ? 1.f : 0.f; mask1 &= ~(1ull << 63); }
+          if (c0 == 48) { v[15] = valid ? 1.f : 0.f; mask1 &= ~(1u << 31); }
 #pragma unroll
           for (int h = 0; h < 2; ++h)
-            st16(sm + SM_H1 + tc::panel_off(tid, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
+            st16(sm + SM_H1 + tc::panel_off(row, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
                  tc::pack_bf16(v[8 * h + 2], v[8 * h + 3]), tc::pack_bf16(v[8 * h + 4], v[8 * h + 5]),
                  tc::pack_bf16(v[8 * h + 6], v[8 * h + 7]));
         }
@@ -351,8 +375,9 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       STAMP(5);
       float z[FEDB_MAX_CLASSES], dz3[FEDB_MAX_CLASSES];
 #pragma unroll
-      for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = k < s.C ? b3s[k] : 0.f;
-      for (int c0 = 0; c0 < s.N2; c0 += 16) {
+      for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = 0.f;
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
+        const int c0 = ch << 4;
         float v[16];
         tc::tmem_ld16(tl + TM_D2 + c0, v);
         tc::tmem_ld_wait();
@@ -367,9 +392,22 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
         uint8_t* pz = sm + SM_Z + (c0 >> 6) * PANEL;
 #pragma unroll
         for (int h = 0; h < 2; ++h)
-          st16(pz + tc::panel_off(tid, (c0 & 63) + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
+          st16(pz + tc::panel_off(row, (c0 & 63) + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
                tc::pack_bf16(v[8 * h + 2], v[8 * h + 3]), tc::pack_bf16(v[8 * h + 4], v[8 * h + 5]),
                tc::pack_bf16(v[8 * h + 6], v[8 * h + 7]));
+      }
+      // the two halves swap their partial logits through 16 spare TMEM columns of the row's lane
+      tc::tmem_st8(tl + TM_ZX + 8 * half, z);
+      tc::tmem_st_wait();
+      tc::tc_fence_before();
+      __syncthreads();
+      tc::tc_fence_after();
+      {
+        float zo[8];
+        tc::tmem_ld8(tl + TM_ZX + 8 * (half ^ 1), zo);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = (half ? zo[k] + z[k] : z[k] + zo[k]) + (k < s.C ? b3s[k] : 0.f);
       }
       {
         float loss = 0.f;
@@ -398,19 +436,23 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
             dz3[0] = (p - yt) * inv_n;
           }
         }
-        loss_acc += loss;
+        if (half == 0) {   // one thread per row books the loss / db3 and publishes dZ3
+          loss_acc += loss;
 #pragma unroll
-        for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] += dz3[k];
-        st16(sm + SM_DZ3 + tc::panel_off(tid, 0), tc::pack_bf16(dz3[0], dz3[1]), tc::pack_bf16(dz3[2], dz3[3]),
-             tc::pack_bf16(dz3[4], dz3[5]), tc::pack_bf16(dz3[6], dz3[7]));
-        st16(sm + SM_DZ3 + tc::panel_off(tid, 8), 0, 0, 0, 0);
+          for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] += dz3[k];
+          st16(sm + SM_DZ3 + tc::panel_off(row, 0), tc::pack_bf16(dz3[0], dz3[1]), tc::pack_bf16(dz3[2], dz3[3]),
+               tc::pack_bf16(dz3[4], dz3[5]), tc::pack_bf16(dz3[6], dz3[7]));
+        } else {
+          st16(sm + SM_DZ3 + tc::panel_off(row, 8), 0, 0, 0, 0);
+        }
       }
       handoff();
       STAMP(6);
       // ---- head weight gradient (needs H2), then dZ2 overwrites H2 --------------------------
       FEDB_MMA_PHASE(mma.wgrad3(s, acc));
       STAMP(7);
-      for (int c0 = 0; c0 < s.N2; c0 += 16) {
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
+        const int c0 = ch << 4;
         float v[16], d[16];
         tc::tmem_ld16(tl + TM_D2 + c0, v);
         tc::tmem_ld_wait();
@@ -427,7 +469,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
         uint8_t* pz = sm + SM_Z + (c0 >> 6) * PANEL;
 #pragma unroll
         for (int h = 0; h < 2; ++h)
-          st16(pz + tc::panel_off(tid, (c0 & 63) + 8 * h), tc::pack_bf16(d[8 * h], d[8 * h + 1]),
+          st16(pz + tc::panel_off(row, (c0 & 63) + 8 * h), tc::pack_bf16(d[8 * h], d[8 * h + 1]),
                tc::pack_bf16(d[8 * h + 2], d[8 * h + 3]), tc::pack_bf16(d[8 * h + 4], d[8 * h + 5]),
                tc::pack_bf16(d[8 * h + 6], d[8 * h + 7]));
       }
@@ -439,14 +481,15 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       {
         float v[16];
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c0 = 32 * half + 16 * cc;
           tc::tmem_ld16(tl + TM_D1 + c0, v);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = ((mask1 >> (c0 + i)) & 1ull) ? v[i] : 0.f;
+          for (int i = 0; i < 16; ++i) v[i] = ((mask1 >> (16 * cc + i)) & 1u) ? v[i] : 0.f;
 #pragma unroll
           for (int h = 0; h < 2; ++h)
-            st16(sm + SM_DZ1 + tc::panel_off(tid, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
+            st16(sm + SM_DZ1 + tc::panel_off(row, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
                  tc::pack_bf16(v[8 * h + 2], v[8 * h + 3]), tc::pack_bf16(v[8 * h + 4], v[8 * h + 5]),
                  tc::pack_bf16(v[8 * h + 6], v[8 * h + 7]));
         }
@@ -458,84 +501,108 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       STAMP(11);
     }  // tiles
 
-    // ---- spill this CTA's gradients (fp32, slab layout) straight from TMEM to its record in the global
-    // scratch (L2-resident; the cluster reduction reads it back from there — measured 3x faster than
-    // reducing through distributed shared memory for this size).  Every slab position below lay.end is
-    // written (padding explicitly as 0).
-    float* rec = a.scratch + G.scratch_off + (size_t)q * (G.slab_size + FEDB_LOSS_SLOTS);
-    if (my_tiles == 0) {
-      for (int i = tid; i < (lay.total >> 2); i += TC_THREADS) reinterpret_cast<float4*>(rec)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    } else {
+    // ---- send this CTA's partial gradients, slice by slice, straight from TMEM into the owning CTA's
+    // shared memory (distributed shared memory stores): a reduce-scatter with no trip through L2.
+    // Every slab position below lay.end is sent (padding explicitly as 0).
+    {
+      const bool have = my_tiles > 0;
       float v[16];
       for (int mt = 0; mt < s.MT2; ++mt) {
-        const int j = 128 * mt + tid;
+        const int j = 128 * mt + row;
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
-          tc::tmem_ld16(tl + TM_DW2 + 64 * mt + c0, v);
-          tc::tmem_ld_wait();
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c0 = 32 * half + 16 * cc;
+          if (have) { tc::tmem_ld16(tl + TM_DW2 + 64 * mt + c0, v); tc::tmem_ld_wait(); }
+          else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+          }
           if (j < s.h2) {
 #pragma unroll
             for (int i4 = 0; i4 < 4; ++i4) {
               const int col = c0 + 4 * i4;
               if (col < s.ld1)
-                *reinterpret_cast<float4*>(rec + lay.w_off[1] + j * s.ld1 + col) =
-                    make_float4(col < s.h1 ? v[4 * i4] : 0.f, col + 1 < s.h1 ? v[4 * i4 + 1] : 0.f, col + 2 < s.h1 ? v[4 * i4 + 2] : 0.f,
-                                col + 3 < s.h1 ? v[4 * i4 + 3] : 0.f);
+                send_grad((lay.w_off[1] + j * s.ld1 + col) >> 2,
+                          make_float4(col < s.h1 ? v[4 * i4] : 0.f, col + 1 < s.h1 ? v[4 * i4 + 1] : 0.f,
+                                      col + 2 < s.h1 ? v[4 * i4 + 2] : 0.f, col + 3 < s.h1 ? v[4 * i4 + 3] : 0.f));
             }
-            if (c0 == 48) rec[lay.b_off[1] + j] = v[15];
-          } else if (j < ru4(s.h2)) {
-            if (c0 == 0) rec[lay.b_off[1] + j] = 0.f;
+          }
+          // bias gradients sit in column 63: one float each, gathered four rows at a time by the lane that
+          // owns the aligned group (warp shuffle keeps it a single float4 store)
+          if (c0 == 48) {
+            const float b0v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 0), b1v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 1);
+            const float b2v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 2), b3v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 3);
+            if ((lane & 3) == 0 && j < ru4(s.h2))
+              send_grad((lay.b_off[1] + j) >> 2, make_float4(j < s.h2 ? b0v : 0.f, j + 1 < s.h2 ? b1v : 0.f, j + 2 < s.h2 ? b2v : 0.f,
+                                                             j + 3 < s.h2 ? b3v : 0.f));
           }
         }
-        tc::tmem_ld16(tl + TM_DW3 + 16 * mt, v);
-        tc::tmem_ld_wait();
+        if (half == 0) {   // head weights: dW3[k][j] for this thread's j, four neighbouring j per store
+          if (have) { tc::tmem_ld16(tl + TM_DW3 + 16 * mt, v); tc::tmem_ld_wait(); }
 #pragma unroll
-        for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-          if (k < s.C && j < s.ld2) rec[lay.w_off[2] + k * s.ld2 + j] = j < s.h2 ? v[k] : 0.f;
-      }
-      tc::tmem_ld16(tl + TM_DW1, v);
-      tc::tmem_ld_wait();
-      if (tid < s.h1) {
-#pragma unroll
-        for (int i4 = 0; i4 < 4; ++i4) {
-          const int col = 4 * i4;
-          if (col < s.ld0)
-            *reinterpret_cast<float4*>(rec + lay.w_off[0] + tid * s.ld0 + col) =
-                make_float4(col < s.d0 ? v[col] : 0.f, col + 1 < s.d0 ? v[col + 1] : 0.f, col + 2 < s.d0 ? v[col + 2] : 0.f,
-                            col + 3 < s.d0 ? v[col + 3] : 0.f);
+          for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
+            if (k < s.C) {
+              const float x0 = __shfl_sync(0xffffffffu, v[k], (lane & ~3) + 0), x1 = __shfl_sync(0xffffffffu, v[k], (lane & ~3) + 1);
+              const float x2 = __shfl_sync(0xffffffffu, v[k], (lane & ~3) + 2), x3 = __shfl_sync(0xffffffffu, v[k], (lane & ~3) + 3);
+              if ((lane & 3) == 0 && j < s.ld2)
+                send_grad((lay.w_off[2] + k * s.ld2 + j) >> 2, make_float4(j < s.h2 ? x0 : 0.f, j + 1 < s.h2 ? x1 : 0.f,
+                                                                           j + 2 < s.h2 ? x2 : 0.f, j + 3 < s.h2 ? x3 : 0.f));
+            }
         }
-        rec[lay.b_off[0] + tid] = v[15];
-      } else if (tid < ru4(s.h1)) {
-        rec[lay.b_off[0] + tid] = 0.f;
       }
-      if (tid >= s.C && tid < ru4(s.C)) rec[lay.b_off[2] + tid] = 0.f;
+      if (half == 0) {     // layer 1: dW1[row][0..15] (+ db1 in column 15)
+        if (have) { tc::tmem_ld16(tl + TM_DW1, v); tc::tmem_ld_wait(); }
+        else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+        if (row < s.h1) {
+#pragma unroll
+          for (int i4 = 0; i4 < 4; ++i4) {
+            const int col = 4 * i4;
+            if (col < s.ld0)
+              send_grad((lay.w_off[0] + row * s.ld0 + col) >> 2,
+                        make_float4(col < s.d0 ? v[col] : 0.f, col + 1 < s.d0 ? v[col + 1] : 0.f, col + 2 < s.d0 ? v[col + 2] : 0.f,
+                                    col + 3 < s.d0 ? v[col + 3] : 0.f));
+          }
+        }
+        const float b0v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 0), b1v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 1);
+        const float b2v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 2), b3v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 3);
+        if ((lane & 3) == 0 && row < ru4(s.h1))
+          send_grad((lay.b_off[0] + row) >> 2, make_float4(row < s.h1 ? b0v : 0.f, row + 1 < s.h1 ? b1v : 0.f,
+                                                           row + 2 < s.h1 ? b2v : 0.f, row + 3 < s.h1 ? b3v : 0.f));
+      }
     }
     STAMP(12);
-    // loss and db3: warp shuffle, then the 4 warps in a fixed order
+    // loss and db3: warp shuffle, then the 4 row-warps in a fixed order; sent like any other gradient
     {
       float vals[9];
       vals[0] = loss_acc;
 #pragma unroll
       for (int k = 0; k < 8; ++k) vals[k + 1] = db3_acc[k];
+      if (half == 0) {
 #pragma unroll
-      for (int i = 0; i < 9; ++i) {
-        float x = vals[i];
+        for (int i = 0; i < 9; ++i) {
+          float x = vals[i];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-        if (lane == 0) red_f[warp][i] = x;
+          for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+          if (lane == 0) red_f[warp][i] = x;
+        }
       }
       __syncthreads();
-      if (tid < 9) {
-        const float x = red_f[0][tid] + red_f[1][tid] + red_f[2][tid] + red_f[3][tid];
-        if (tid == 0) rec[G.slab_size] = x;                             // loss sum of this CTA's rows
-        else if (tid - 1 < s.C) rec[lay.b_off[2] + tid - 1] = x;        // db3
+      if (tid == 0) {
+        float t[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) t[i] = red_f[0][i] + red_f[1][i] + red_f[2][i] + red_f[3][i];
+        send_grad(lay.b_off[2] >> 2, make_float4(0 < s.C ? t[1] : 0.f, 1 < s.C ? t[2] : 0.f, 2 < s.C ? t[3] : 0.f, 3 < s.C ? t[4] : 0.f));
+        if (s.C > 4) send_grad((lay.b_off[2] >> 2) + 1, make_float4(t[5], 5 < s.C ? t[6] : 0.f, 6 < s.C ? t[7] : 0.f, 7 < s.C ? t[8] : 0.f));
+        // loss partial: slot n4 of rank 0's extra row (index per*CS + q)
+        reinterpret_cast<float*>(peer_slots[0] + CS * per)[q] = t[0];
+        sc_s = step_scalars_fast(G, step0 + st + 1);
       }
     }
-    if (tid == 0) sc_s = step_scalars_fast(G, step0 + st + 1);
     // my slice of the slab and its moments do not depend on the peers: fetch them before the barrier
-    constexpr int PF = 3;
-    const int n4 = lay.end >> 2, per = (n4 + CS - 1) / CS;
-    const int lo = q * per, hi = min(n4, lo + per);
+    constexpr int PF = 2;
     const bool use_v = a.v && G.opt != FEDB_OPT_SGD;
     float4 w_pf[PF], m_pf[PF], v_pf[PF];
 #pragma unroll
@@ -549,38 +616,31 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       }
     }
     tc::tc_fence_before();
-    __threadfence();
-    cluster.sync();
+    cluster.sync();     // every partial slice has landed in its owner's shared memory
     STAMP(13);
 
-    // ---- cluster reduction over DSMEM (fixed rank order) + optimizer on my slice ----------------
+    // ---- owner: fixed-order sum of the CS partials (local shared memory), optimizer, then all-gather of
+    // the updated fp32 slice into every CTA's landing zone (distributed shared memory stores) -------------
     {
       const StepScalars sc = sc_s;
-      const float* rec0 = a.scratch + G.scratch_off;
-      const size_t rstride = (size_t)(G.slab_size + FEDB_LOSS_SLOTS);
       int it = 0;
       for (int e4 = lo + tid; e4 < hi; e4 += TC_THREADS, ++it) {
-        const int e = e4 * 4;
-        float4 pr[8];   // every load of this element group is issued before the first use
+        const int e = e4 * 4, i = e4 - lo;
+        float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int rk = 0; rk < 8; ++rk)
-          if (rk < CS) pr[rk] = __ldcg(reinterpret_cast<const float4*>(rec0 + rk * rstride + e));
+          if (rk < CS) { const float4 p = slots[rk * per + i]; gsum.x += p.x; gsum.y += p.y; gsum.z += p.z; gsum.w += p.w; }
         float4 w, mm, vv;
         if (it < PF) {
-          // (static indexing keeps the prefetch arrays in registers)
-          w = it == 0 ? w_pf[0] : (it == 1 ? w_pf[1] : w_pf[2]);
-          mm = it == 0 ? m_pf[0] : (it == 1 ? m_pf[1] : m_pf[2]);
-          vv = it == 0 ? v_pf[0] : (it == 1 ? v_pf[1] : v_pf[2]);
+          w = it == 0 ? w_pf[0] : w_pf[1];
+          mm = it == 0 ? m_pf[0] : m_pf[1];
+          vv = it == 0 ? v_pf[0] : v_pf[1];
         } else {
           w = *reinterpret_cast<float4*>(Pg + e);
           mm = vv = make_float4(0.f, 0.f, 0.f, 0.f);
           if (a.m) mm = *reinterpret_cast<float4*>(a.m + G.slab_off + e);
           if (use_v) vv = *reinterpret_cast<float4*>(a.v + G.slab_off + e);
         }
-        float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int rk = 0; rk < 8; ++rk)
-          if (rk < CS) { gsum.x += pr[rk].x; gsum.y += pr[rk].y; gsum.z += pr[rk].z; gsum.w += pr[rk].w; }
         const bool is_w = (e < lay.b_off[0]) || (e >= lay.w_off[1] && e < lay.b_off[1]) || (e >= lay.w_off[2] && e < lay.b_off[2]);
         if (is_w && G.alpha != 0.f) {
           const float al = G.alpha * inv_n;
@@ -591,25 +651,23 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
         w.y = opt_update(G, sc, w.y, gsum.y, mm.y, vv.y);
         w.z = opt_update(G, sc, w.z, gsum.z, mm.z, vv.z);
         w.w = opt_update(G, sc, w.w, gsum.w, mm.w, vv.w);
-        *reinterpret_cast<float4*>(Pg + e) = w;
+#pragma unroll
+        for (int rk = 0; rk < 8; ++rk)
+          if (rk < CS) peer_land[rk][e4] = w;
+        *reinterpret_cast<float4*>(Pg + e) = w;          // master copy (off the critical path)
         if (a.m) *reinterpret_cast<float4*>(a.m + G.slab_off + e) = mm;
         if (use_v) *reinterpret_cast<float4*>(a.v + G.slab_off + e) = vv;
       }
-      if (q == 0 && warp == 3 && a.loss_out) {   // 8 lanes fetch the 8 partial losses at once; fixed-order sum
-        float x = lane < CS ? __ldcg(rec0 + lane * rstride + G.slab_size) : 0.f;
+      if (q == 0 && tid == 32 && a.loss_out) {
+        const float* lp = reinterpret_cast<const float*>(slots + CS * per);
         float ls = 0.f;
-#pragma unroll
-        for (int rk = 0; rk < 8; ++rk) ls += __shfl_sync(0xffffffffu, x, rk);
-        if (lane == 0) a.loss_out[g] = ls * inv_n;
+        for (int rk = 0; rk < CS; ++rk) ls += lp[rk];
+        a.loss_out[g] = ls * inv_n;
       }
     }
     STAMP(14);
-    __threadfence();
-    asm volatile("fence.proxy.async;" ::: "memory");   // my slice must be visible to the peers' bulk copies
-    cluster.sync();   // all slices written; all records consumed
+    cluster.sync();   // every CTA holds the complete updated slab in its landing zone
     STAMP(15);
-    if (tid == 0) bulk_load_begin(reinterpret_cast<uint8_t*>(landing), Pg, (uint32_t)lay.end * 4u, &wbar);
-    tc::mbar_wait(&wbar, wph); wph ^= 1;
     convert_weights(sm, landing, lay, s);
     STAMP(16);
   }  // steps
@@ -619,21 +677,22 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
     if (tid < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES) cnt[tid] = 0;
     __syncthreads();
     for (int tile = q; tile < ntiles; tile += CS) {
-      const int r = tile * TC_ROWS + tid;
+      const int r = tile * TC_ROWS + row;
       const bool valid = r < nb;
       int label;
       if (ntiles <= CS && a.n_steps > 0) {
         label = rr.label;   // single tile per CTA: the X panel from the training step is still in place
       } else {
-        rr = fetch_row(a, G.idx_off + b0 + r, valid);
-        label = store_row(sm, rr, valid, s);
+        rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+        label = store_row(sm, rr, valid, s, row, half);
       }
       handoff();
       FEDB_MMA_PHASE(mma.fwd1(s));
       {
         float v[16];
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c0 = 32 * half + 16 * cc;
           tc::tmem_ld16(tl + TM_D1 + c0, v);
           tc::tmem_ld_wait();
 #pragma unroll
@@ -641,7 +700,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
           if (c0 == 48) v[15] = valid ? 1.f : 0.f;
 #pragma unroll
           for (int h = 0; h < 2; ++h)
-            st16(sm + SM_H1 + tc::panel_off(tid, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
+            st16(sm + SM_H1 + tc::panel_off(row, c0 + 8 * h), tc::pack_bf16(v[8 * h], v[8 * h + 1]),
                  tc::pack_bf16(v[8 * h + 2], v[8 * h + 3]), tc::pack_bf16(v[8 * h + 4], v[8 * h + 5]),
                  tc::pack_bf16(v[8 * h + 6], v[8 * h + 7]));
         }
@@ -650,8 +709,9 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       FEDB_MMA_PHASE(mma.fwd2(s));
       float z[FEDB_MAX_CLASSES];
 #pragma unroll
-      for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = k < s.C ? b3s[k] : 0.f;
-      for (int c0 = 0; c0 < s.N2; c0 += 16) {
+      for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = 0.f;
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
+        const int c0 = ch << 4;
         float v[16];
         tc::tmem_ld16(tl + TM_D2 + c0, v);
         tc::tmem_ld_wait();
@@ -662,16 +722,28 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
             for (int i = 0; i < 16; ++i) z[k] = fmaf(fmaxf(v[i], 0.f), W3s[k * 256 + c0 + i], z[k]);
           }
       }
-      int pred = 0;
-      if (G.head == FEDB_HEAD_SOFTMAX_CE) {
-        float best = z[0];
+      tc::tmem_st8(tl + TM_ZX + 8 * half, z);
+      tc::tmem_st_wait();
+      tc::tc_fence_before();
+      __syncthreads();
+      tc::tc_fence_after();
+      if (half == 0) {
+        float zo[8];
+        tc::tmem_ld8(tl + TM_ZX + 8, zo);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int k = 1; k < FEDB_MAX_CLASSES; ++k)
-          if (k < s.C && z[k] > best) { best = z[k]; pred = k; }
-      } else {
-        pred = z[0] > 0.f ? 1 : 0;
+        for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = z[k] + zo[k] + (k < s.C ? b3s[k] : 0.f);
+        int pred = 0;
+        if (G.head == FEDB_HEAD_SOFTMAX_CE) {
+          float best = z[0];
+#pragma unroll
+          for (int k = 1; k < FEDB_MAX_CLASSES; ++k)
+            if (k < s.C && z[k] > best) { best = z[k]; pred = k; }
+        } else {
+          pred = z[0] > 0.f ? 1 : 0;
+        }
+        if (valid && label >= 0 && label < FEDB_MAX_CLASSES) atomicAdd(&cnt[label * FEDB_MAX_CLASSES + pred], 1);
       }
-      if (valid && label >= 0 && label < FEDB_MAX_CLASSES) atomicAdd(&cnt[label * FEDB_MAX_CLASSES + pred], 1);
     }
     tc::tmem_ld_wait();
     __syncthreads();
@@ -697,8 +769,11 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
   const int tid = threadIdx.x;
   __shared__ long long t_off[TAIL_MAX_CLIENTS];
   __shared__ float t_num[TAIL_MAX_CLIENTS], t_den[TAIL_MAX_CLIENTS];
-  const int nthr = csize * TC_THREADS, gt = crank * TC_THREADS + tid;
-  for (int f = 0; f < a.n_feds; ++f) {
+  // the last CTA of the cluster scores the round (metrics need only the confusion counts) while the
+  // others average; with a single CTA it does both
+  const int mrank = csize - 1, workers = csize > 1 ? csize - 1 : 1;
+  const int nthr = workers * TC_THREADS, gt = crank * TC_THREADS + tid;
+  for (int f = 0; f < a.n_feds && (csize == 1 || crank != mrank); ++f) {
     if (s_stop[f]) continue;
     const FedbFed F = a.feds[f];
     __syncthreads();
@@ -740,7 +815,7 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
     }
   }
   if (a.prof && crank == 0 && tid == 0) a.prof[20] = clock64();
-  if (crank == 0) {   // metrics read only the confusion counts: they overlap the averaging above
+  if (crank == mrank) {
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32)
       for (int f = 0; f < a.n_feds; ++f) {
@@ -768,24 +843,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_local_round_tc(TcArgs a) {
   for (int f = threadIdx.x; f < a.n_feds; f += TC_THREADS) s_stop[f] = a.fed_state_rw[f].stop ? 1 : 0;
   __threadfence();
   cluster.sync();
-  if (crank == 0 && threadIdx.x == 0) {
-    const unsigned int n_clusters = gridDim.x / CS;
-    const unsigned int last = (atomicInc(a.tail_count, n_clusters - 1) == n_clusters - 1) ? 1u : 0u;
-    for (int r = 0; r < CS; ++r) *cluster.map_shared_rank(&s_last, r) = last;
+  const unsigned int n_clusters = gridDim.x / CS;
+  if (n_clusters > 1) {
+    if (crank == 0 && threadIdx.x == 0) {
+      const unsigned int last = (atomicInc(a.tail_count, n_clusters - 1) == n_clusters - 1) ? 1u : 0u;
+      for (int r = 0; r < CS; ++r) *cluster.map_shared_rank(&s_last, r) = last;
+    }
+    cluster.sync();
+    if (!s_last) return;
+    __threadfence();
   }
-  cluster.sync();
   if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[18] = clock64();
-  if (!s_last) return;
-  __threadfence();
   round_tail(a, crank, CS, s_stop);
-  if (a.prof && crank == 0 && threadIdx.x == 0) a.prof[19] = clock64();
+  if (a.prof && crank == CS - 1 && threadIdx.x == 0) a.prof[19] = clock64();
 }
 
 }  // namespace fedb
 
 using namespace fedb;
 
-extern "C" int64_t fedb_tc_smem_bytes(void) { return SM_END + 1024; }
+extern "C" int64_t fedb_tc_smem_bytes(void) { return SM_SLOTS + SLOTS_MAX_BYTES + 1024; }
+// largest slab (floats) whose gradient slices fit the per-CTA exchange area
+extern "C" int32_t fedb_tc_max_slab(void) { return (SLOTS_MAX_BYTES - 64) / 4 - 32; }
 
 extern "C" int fedb_round_tc_prof(const FedbGroup*, int32_t, int32_t, const float*, int32_t, const int32_t*, const int32_t*, float*, float*,
                                   float*, int32_t*, const int32_t*, FedbFedState*, float*, int32_t*, float*, int32_t, const FedbFed*,
@@ -794,9 +873,8 @@ extern "C" int fedb_round_tc_prof(const FedbGroup*, int32_t, int32_t, const floa
 static int launch_tc(TcArgs a, int32_t n_groups, int32_t cluster_size, void* stream) {
   FEDB_REQUIRE(n_groups > 0 && cluster_size >= 1 && cluster_size <= 8, "bad grid");
   FEDB_REQUIRE(a.ldx >= 16 && a.ldx % 4 == 0, "feature rows must be padded to >= 16 floats");
-  FEDB_REQUIRE(a.scratch != nullptr, "scratch (gradient records) is required");
   static bool attr_set = false;
-  const int smem = SM_END + 1024;
+  const int smem = SM_SLOTS + SLOTS_MAX_BYTES + 1024;
   if (!attr_set) {
     FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_local_round_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;

@@ -222,6 +222,7 @@ OPTIONAL_SIGS = {
     "fedb_tc_probe_args_size": ([], _I32),
     "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
     "fedb_tc_smem_bytes": ([], _I64),
+    "fedb_tc_max_slab": ([], _I32),
     "fedb_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P, _P], _I32),
     "fedb_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P], _I32),
     "fedb_local_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),

@@ -68,6 +68,7 @@ def probe(a_img: torch.Tensor, b_img: torch.Tensor, N: int, a_steps: Sequence[in
 
 # ---- fused tensor-core local round (csrc/fedb_tc.cu) -----------------------------------------
 TC_ROWS = 128
+TC_MAX_SLAB = 11920   # floats; fedb_tc_max_slab(): the gradient slices of all 8 CTAs must fit one CTA's exchange area
 
 
 def tc_eligible(groups: np.ndarray) -> bool:
@@ -79,7 +80,7 @@ def tc_eligible(groups: np.ndarray) -> bool:
             return False
         if not (d[0] <= 15 and d[1] <= 63 and d[2] <= 256 and d[3] <= 8):
             return False
-        if int(g["slab_size"]) > 24000:
+        if int(g["slab_size"]) > TC_MAX_SLAB:
             return False
     return True
 
