@@ -27,6 +27,7 @@
 #include <cooperative_groups.h>
 
 #include "common.cuh"
+#include "p2p_common.cuh"
 #include "tc_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -78,6 +79,8 @@ struct TcArgs {
   float* hist_local;
   float* hist_global;
   unsigned int* tail_count;   // wraps to 0 by itself (atomicInc)
+  // ---- fused cross-GPU aggregation (tail_mode 2): one federation, one resident client per rank ----
+  const FedbP2PRank* p2p;
 };
 
 struct Shape {
@@ -271,6 +274,13 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
   const uint32_t inv_per = 0xFFFFFFFFu / (uint32_t)per + 1u;   // e4 / per == __umulhi(e4, inv_per) for e4 < 2^16
   const int lo = q * per, hi = min(n4, lo + per);
 
+  // fused cross-GPU aggregation: where this rank publishes its weighted slab for the current round
+  uint64_t p2p_seq = 0;
+  float* p2p_partial = nullptr;
+  if (a.tail_mode == 2) {
+    p2p_seq = *reinterpret_cast<volatile uint64_t*>(a.p2p->seq);
+    p2p_partial = reinterpret_cast<float*>(a.p2p->sym[a.p2p->rank] + a.p2p->sym_partial_off) + (p2p_seq & 1) * a.p2p->global_total;
+  }
   float* landing = reinterpret_cast<float*>(sm + SM_STAGE);   // fp32 slab landing zone (idle panel area)
   float4* slots = reinterpret_cast<float4*>(sm + SM_SLOTS);   // [CS][per] partial-gradient slices sent by every CTA
   if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
@@ -654,6 +664,10 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
 #pragma unroll
         for (int rk = 0; rk < 8; ++rk)
           if (rk < CS) peer_land[rk][e4] = w;
+        if (p2p_partial && st == a.n_steps - 1)          // this rank's FedAvg term, (w * n_k) / N, for the peers to fetch (C:110-115)
+          reinterpret_cast<float4*>(p2p_partial)[e4] =
+              make_float4(__fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den), __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den),
+                          __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den), __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den));
         *reinterpret_cast<float4*>(Pg + e) = w;          // master copy (off the critical path)
         if (a.m) *reinterpret_cast<float4*>(a.m + G.slab_off + e) = mm;
         if (use_v) *reinterpret_cast<float4*>(a.v + G.slab_off + e) = vv;
@@ -666,7 +680,14 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       }
     }
     STAMP(14);
+    if (p2p_partial && st == a.n_steps - 1) __threadfence_system();   // my slice of the partial is visible to the peers
     cluster.sync();   // every CTA holds the complete updated slab in its landing zone
+    if (p2p_partial && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
+      // arrival flag A ("my partial is complete") into every peer's buffer; the local evaluation below
+      // overlaps its flight over NVLink and the peers' own progress
+      uint64_t* pf = reinterpret_cast<uint64_t*>(a.p2p->sym[tid] + a.p2p->sym_flag_off);
+      st_release_sys_u64(pf + a.p2p->rank, p2p_seq + 1);
+    }
     STAMP(15);
     convert_weights(sm, landing, lay, s);
     STAMP(16);
@@ -828,10 +849,90 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
   }
 }
 
+// Cross-GPU FedAvg fused into the round kernel (one federation, one resident client per rank): the
+// protocol of k_fedavg_p2p (csrc/fedb_p2p.cu) executed by the client's own cluster.  The partial
+// (w * n_k) / N was published by the optimizer phase and flag A raised BEFORE the local evaluation, so
+// the NVLink latency hides behind it; here the confusion counts follow (flag B), every CTA but the last
+// sums the R partials in rank order with peer loads and writes the global model + the client's slab,
+// and the last CTA scores the round from all ranks' counts and does the next round's bookkeeping.
+__device__ void p2p_tail(const TcArgs& a) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x;
+  __shared__ FedbP2PRank R;
+  for (int i = tid; i < (int)(sizeof(FedbP2PRank) / 4); i += TC_THREADS)
+    reinterpret_cast<int32_t*>(&R)[i] = reinterpret_cast<const int32_t*>(a.p2p)[i];
+  __shared__ int s_timeout;
+  if (tid == 0) s_timeout = 0;
+  __syncthreads();
+  const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
+  const int par = (int)(seq & 1);
+  const bool stopped = R.fed_state[0].stop != 0;   // as it stands for THIS round
+  __threadfence();
+  cluster.sync();                                   // all CTAs: evaluation counts are in a.conf; seq / stop have been read
+  if (stopped) return;
+  const long long t0 = clock64();
+  const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
+  if (crank == 0) {   // publish this rank's confusion counts, then flag B
+    int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + par * conf_stride;
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) my_confx[i] = __ldcg(a.conf + i);
+    __threadfence_system();
+    __syncthreads();
+    if (tid < R.world) st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 8 + R.rank, seq + 1);
+  }
+  const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
+  if (CS == 1 || crank != mrank) {   // ---- aggregation: wait for every peer's partial (flag A), sum in rank order
+    if (tid < R.world)
+      while (ld_acquire_sys_u64(my_flags + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+    __syncthreads();
+    const FedbFed F = R.feds[0];
+    const FedbGroup* G = R.groups + F.first_group;
+    float4* slab = reinterpret_cast<float4*>(R.params + G->slab_off);
+    float4* glob = reinterpret_cast<float4*>(R.global + F.global_off);
+    const int n4 = F.slab_size >> 2;
+    for (int e4 = crank * TC_THREADS + tid; e4 < n4; e4 += workers * TC_THREADS) {
+      float4 pr[8];
+#pragma unroll
+      for (int qq = 0; qq < 8; ++qq)
+        if (qq < R.world)
+          pr[qq] = ld_relaxed_sys_f4(reinterpret_cast<const float*>(R.sym[qq] + R.sym_partial_off) + (int64_t)par * R.global_total + F.global_off + 4 * e4);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int qq = 0; qq < 8; ++qq)
+        if (qq < R.world) { acc.x += pr[qq].x; acc.y += pr[qq].y; acc.z += pr[qq].z; acc.w += pr[qq].w; }
+      glob[e4] = acc;
+      if (R.write_back) slab[e4] = acc;
+    }
+  }
+  if (crank == mrank) {              // ---- metrics from every rank's counts (flag B), early stop, next round's begin
+    if (tid < R.world)
+      while (ld_acquire_sys_u64(my_flags + 8 + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+    __syncthreads();
+    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) {
+      const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
+      const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[qq] + R.sym_conf_off) + par * conf_stride;
+      R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
+    }
+    __syncthreads();
+    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+    if (tid < 32 && R.do_metrics)
+      round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true);
+    __syncthreads();
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) a.conf[i] = 0;
+    if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
+  }
+  __syncthreads();
+  if (s_timeout && tid == 0) *R.err = FEDB_E_TIMEOUT;
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1) k_local_round_tc(TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   local_round_body(a, smem_raw);
   if (a.tail_mode == 0) return;
+  if (a.tail_mode == 2) { p2p_tail(a); return; }
   // Every cluster — including those that had nothing to do — checks in once all of its CTAs are
   // done; the cluster that observes the last check-in runs the tail.  No grid-wide barrier and no
   // co-residency assumption: the other clusters have simply finished.
@@ -930,6 +1031,21 @@ extern "C" int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t 
                              float* hist_global, int32_t conf_ints, uint32_t* tail_count, void* stream) {
   return fedb_round_tc_prof(groups, n_groups, cluster_size, X, ldx, y, idx, params, m, v, step, active, fed_state, loss_out, conf,
                             scratch, n_steps, feds, n_feds, global, hist_local, hist_global, conf_ints, tail_count, nullptr, stream);
+}
+
+// The whole round of a multi-GPU federation with ONE resident client per rank in one launch per rank:
+// local steps + (partial published, flag raised) + local evaluation + cross-GPU aggregation over NVLink
+// peer memory + metrics + early stop (see p2p_tail).  rank_dev: this rank's FedbP2PRank record.
+extern "C" int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
+                                 const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
+                                 FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
+                                 const FedbP2PRank* rank_dev, void* stream) {
+  FEDB_REQUIRE(rank_dev != nullptr, "rank record required");
+  TcArgs a{};
+  a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
+  a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
+  a.n_steps = n_steps; a.do_eval = 1; a.prof = nullptr; a.tail_mode = 2; a.n_groups = 1; a.n_feds = 1; a.p2p = rank_dev;
+  return launch_tc(a, 1, cluster_size, stream);
 }
 
 extern "C" int fedb_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,

@@ -116,3 +116,14 @@ def round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_s
                                 nat.ptr(prof), nat.cuda_stream()))
     from . import kernels as K
     K._count()
+
+
+def round_tc_p2p(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
+                 rank_dev) -> None:
+    """Multi-GPU round in one launch per rank (one federation, one resident client): fedb_round_tc_p2p."""
+    lib = nat.lib(required=True)
+    nat.check(lib.fedb_round_tc_p2p(nat.ptr(tb.d_groups), cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
+                                    nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
+                                    nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(rank_dev), nat.cuda_stream()))
+    from . import kernels as K
+    K._count()

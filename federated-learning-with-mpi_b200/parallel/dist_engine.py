@@ -131,11 +131,34 @@ class DistFedEngine(FedEngine):
     def _begin_is_fused(self) -> bool:
         return True   # k_fedavg_p2p ends with the next round's begin bookkeeping
 
+    def _fused_p2p_ok(self) -> bool:
+        """One federation with exactly one resident client on the tensor-core path: the whole multi-GPU
+        round is ONE launch per rank (aggregation inside the round kernel, fedb_round_tc_p2p)."""
+        return (self.precision_name == "bf16" and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
+                and os.environ.get("FEDB200_NO_FUSED_P2P") is None)
+
+    def enqueue_round(self) -> None:
+        if self._fused_p2p_ok():
+            from ..ops import tc
+            E = max(p.hyper.local_epochs for p in self.problems)
+            tc.round_tc_p2p(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
+                            self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev)
+            return
+        super().enqueue_round()
+
+    @property
+    def launches_per_round(self) -> int:
+        if self._fused_p2p_ok():
+            return 1
+        return FedEngine.launches_per_round.fget(self)
+
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> None:
         p2p.launch(self.rank_dev, 1, self.p2p_blocks)   # begin_next is baked into the rank record (always on)
 
     @property
     def kernel_names(self) -> List[str]:
+        if self._fused_p2p_ok():
+            return ["k_local_round_tc[train+eval+p2p-fedavg+metrics]"]
         local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
         return local + ["k_fedavg_p2p"]
 

@@ -268,6 +268,15 @@ int fedb_wide_head_bwd(const FedbGroup* groups, int32_t n_groups, float* params,
 int fedb_wide_bias_opt(const FedbGroup* groups, int32_t n_groups, float* params, float* m, float* v, const void* dZ,
                        int32_t B, int32_t d, int32_t layer, const int32_t* step, const FedbFedState* fed_state, void* stream);
 
+/* K2a + K3 + K1b in ONE launch per rank: a multi-GPU federation with one resident client per rank (the
+ * reference's own topology, C:36) — local steps, local evaluation, cross-GPU FedAvg over NVLink peer
+ * memory, write-back, metrics, early stop.  rank_dev: this rank's FedbP2PRank (same record and symmetric
+ * buffer as fedb_fedavg_p2p; flags[8..15] of the buffer carry the second arrival flag). */
+int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
+                      const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
+                      FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
+                      const FedbP2PRank* rank_dev, void* stream);
+
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop
  * (csrc/fedb_p2p.cu; C:101-120, C:165-192).  ranks_dev[0..n_ranks_here): one entry in real

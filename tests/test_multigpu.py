@@ -11,11 +11,21 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
 
-def test_two_gpu_bench_runs_and_learns():
+def _bench(port, env_extra=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", "29541", os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "60", "--warmup", "5"]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+           "--master-port", str(port), os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "60", "--warmup", "5"]
+    env = dict(os.environ, **(env_extra or {}))
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0, out.stderr[-2000:]
-    rec = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
-    assert rec["n_gpus"] == 2 and rec["value"] > 0 and any("k_fedavg_p2p" in k for k in rec["kernels"])
-    assert rec["final_global_accuracy_train_shards"] > 0.8
+    return json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+
+
+def test_two_gpu_bench_fused_and_standalone_aggregation_agree():
+    fused = _bench(29541)
+    assert fused["n_gpus"] == 2 and fused["value"] > 0 and any("p2p-fedavg" in k for k in fused["kernels"])
+    assert fused["final_global_accuracy_train_shards"] > 0.8
+    # the stand-alone aggregation kernel performs the same arithmetic in the same order: identical trajectory
+    sep = _bench(29542, {"FEDB200_NO_FUSED_P2P": "1"})
+    assert any("k_fedavg_p2p" in k for k in sep["kernels"])
+    assert sep["final_global_accuracy_train_shards"] == fused["final_global_accuracy_train_shards"]
+    assert sep["rounds_run"] == fused["rounds_run"]
