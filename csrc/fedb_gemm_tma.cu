@@ -1,0 +1,234 @@
+// K2d, main variant: the grouped GEMM of fedb_gemm.cu with the canonical Blackwell structure —
+// operands fetched by TMA (cp.async.bulk.tensor, 3-D tensor maps: K x rows x client, hardware 128B
+// swizzle straight into the UMMA panel layout), a warp-specialised CTA (warp 0 = TMA producer,
+// warp 1 = tcgen05.mma issuer + TMEM owner, warps 2-5 = epilogue), a full/empty mbarrier ring, and an
+// epilogue that stages the fp32 accumulator tile through shared memory so that every global access of
+// the fused bias/ReLU, ReLU-mask and optimizer epilogues is a fully coalesced 512-byte row segment.
+// Same arguments, shapes and epilogues as fedb_gemm_tc (include/fedb200.h: FedbGemm).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace fedb {
+namespace {
+
+constexpr int T_THREADS = 192;
+constexpr int BM = 128, BN = 128, BK = 64;
+constexpr int STAGES = 3;                                  // 96 KB: two CTAs per SM overlap epilogue and main loop
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TILE_LD = BN + 4;                            // fp32 staging row stride (floats): 16-byte aligned, bank-shifted
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+               "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(tc::smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(T_THREADS) k_gemm_tma(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                        FedbGemm p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ StepScalars sc_s;
+  __shared__ FedbGroup Gs;
+  const uint32_t raw = tc::smem_u32(smem_raw);
+  const uint32_t sm = (raw + 1023u) & ~1023u;
+  uint8_t* smp = smem_raw + (sm - raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = blockIdx.z, m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int n_cnt = min(BN, p.N - n0);
+  const int KT = (p.K + BK - 1) / BK;
+
+  if (p.epilogue == FEDB_GEMM_WGRAD_OPT && tid < (int)(sizeof(FedbGroup) / 4))
+    reinterpret_cast<int32_t*>(&Gs)[tid] = reinterpret_cast<const int32_t*>(p.groups + g)[tid];
+  if (warp == 1) tc::tmem_alloc<128>(&tmem_slot);
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    tc::mbar_init(&done_bar, 1);
+    tc::fence_mbar_init();
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (p.epilogue == FEDB_GEMM_WGRAD_OPT && tid == 64) sc_s = step_scalars_fast(Gs, p.step[g]);
+
+  if (warp == 0) {
+    // ===== TMA producer (one lane) =====
+    if (lane == 0) {
+      for (int kt = 0; kt < KT; ++kt) {
+        const int s = kt % STAGES, k0 = kt * BK;
+        if (kt >= STAGES) tc::mbar_wait(&empty_bar[s], ((kt / STAGES) - 1) & 1);
+        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        const uint32_t a_dst = sm + s * STAGE_BYTES, b_dst = a_dst + A_BYTES;
+        if (!p.a_mn) tma_load_3d(a_dst, &tmA, k0, m0, g, &full_bar[s]);                       // box {64 k, 128 rows}
+        else { tma_load_3d(a_dst, &tmA, m0, k0, g, &full_bar[s]); tma_load_3d(a_dst + BK * 128, &tmA, m0 + 64, k0, g, &full_bar[s]); }
+        if (!p.b_mn) tma_load_3d(b_dst, &tmB, k0, n0, g, &full_bar[s]);
+        else { tma_load_3d(b_dst, &tmB, n0, k0, g, &full_bar[s]); tma_load_3d(b_dst + BK * 128, &tmB, n0 + 64, k0, g, &full_bar[s]); }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one lane) =====
+    if (lane == 0) {
+      const uint32_t idesc = tc::make_idesc_bf16(BM, n_cnt, p.a_mn != 0, p.b_mn != 0);
+      for (int kt = 0; kt < KT; ++kt) {
+        const int s = kt % STAGES;
+        tc::mbar_wait(&full_bar[s], (kt / STAGES) & 1);
+        tc::tc_fence_after();
+        const int k_cnt = min(BK, p.K - kt * BK);
+        const uint32_t a_base = sm + s * STAGE_BYTES, b_base = a_base + A_BYTES;
+        for (int k = 0; k < (k_cnt >> 4); ++k) {
+          const uint64_t ad = p.a_mn ? tc::make_desc(a_base + 2048 * k, BK * 128, 1024) : tc::make_desc(a_base + 32 * k, 0, 1024);
+          const uint64_t bd = p.b_mn ? tc::make_desc(b_base + 2048 * k, BK * 128, 1024) : tc::make_desc(b_base + 32 * k, 0, 1024);
+          tc::mma_bf16(tmem, ad, bd, idesc, (kt | k) != 0);
+        }
+        tc::mma_commit(&empty_bar[s]);
+        if (kt == KT - 1) tc::mma_commit(&done_bar);
+      }
+    }
+  }
+  // ===== epilogue =====
+  // (1) warps 2..5: accumulator rows -> fp32 staging tile in shared memory (the operand ring is idle by then)
+  float* tile = reinterpret_cast<float*>(smp);
+  if (warp >= 2) {
+    tc::mbar_wait(&done_bar, 0);
+    tc::tc_fence_after();
+    const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+    const int r = quad * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(quad * 32) << 16);
+    for (int c0 = 0; c0 < n_cnt; c0 += 16) {
+      float v[16];
+      tc::tmem_ld16(tl + c0, v);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4)
+        *reinterpret_cast<float4*>(tile + r * TILE_LD + c0 + 4 * q4) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  // (2) all 6 warps: one warp per row at a time, lane = 4 consecutive columns -> coalesced global traffic
+  const int nq = n_cnt >> 2;                         // float4 groups per row (<= 32)
+  if (p.epilogue == FEDB_GEMM_WGRAD_OPT) {
+    const StepScalars sc = sc_s;
+    const bool use_v = p.Vel && Gs.opt != FEDB_OPT_SGD;
+    const float l2 = Gs.alpha * p.l2_scale;
+    for (int r = warp; r < BM; r += T_THREADS / 32) {
+      if (lane < nq) {
+        const size_t off = (size_t)g * p.w_group_stride + (size_t)(m0 + r) * p.ldw + n0 + 4 * lane;
+        const float4 gr = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+        float4 w = *reinterpret_cast<const float4*>(p.W + off);
+        float4 mm = p.Mom ? *reinterpret_cast<const float4*>(p.Mom + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 vv = use_v ? *reinterpret_cast<const float4*>(p.Vel + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+        w.x = opt_update(Gs, sc, w.x, fmaf(l2, w.x, gr.x), mm.x, vv.x);
+        w.y = opt_update(Gs, sc, w.y, fmaf(l2, w.y, gr.y), mm.y, vv.y);
+        w.z = opt_update(Gs, sc, w.z, fmaf(l2, w.z, gr.z), mm.z, vv.z);
+        w.w = opt_update(Gs, sc, w.w, fmaf(l2, w.w, gr.w), mm.w, vv.w);
+        *reinterpret_cast<float4*>(p.W + off) = w;
+        if (p.Mom) *reinterpret_cast<float4*>(p.Mom + off) = mm;
+        if (use_v) *reinterpret_cast<float4*>(p.Vel + off) = vv;
+        if (p.Wsh) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.Wsh) + off) = make_uint2(tc::pack_bf16(w.x, w.y), tc::pack_bf16(w.z, w.w));
+      }
+    }
+  } else if (p.epilogue == FEDB_GEMM_STORE_F32) {
+    for (int r = warp; r < BM; r += T_THREADS / 32)
+      if (lane < nq)
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)g * p.c_group_stride + (size_t)(m0 + r) * p.ldc + n0 + 4 * lane) =
+            *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+  } else {
+    const float4 bias4 = (p.epilogue == FEDB_GEMM_FWD_BIAS_RELU && p.bias && lane < nq)
+                             ? *reinterpret_cast<const float4*>(p.bias + (size_t)g * p.bias_group_stride + n0 + 4 * lane)
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = warp; r < BM; r += T_THREADS / 32) {
+      if (lane < nq) {
+        float4 v = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+        if (p.epilogue == FEDB_GEMM_FWD_BIAS_RELU) {
+          v.x = fmaxf(v.x + bias4.x, 0.f); v.y = fmaxf(v.y + bias4.y, 0.f); v.z = fmaxf(v.z + bias4.z, 0.f); v.w = fmaxf(v.w + bias4.w, 0.f);
+        } else {
+          const uint2 a = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.act) + (size_t)g * p.act_group_stride +
+                                                          (size_t)(m0 + r) * p.ldact + n0 + 4 * lane);
+          const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(&a);
+          v.x = __bfloat162float(ab[0]) > 0.f ? v.x : 0.f; v.y = __bfloat162float(ab[1]) > 0.f ? v.y : 0.f;
+          v.z = __bfloat162float(ab[2]) > 0.f ? v.z : 0.f; v.w = __bfloat162float(ab[3]) > 0.f ? v.w : 0.f;
+        }
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)g * p.c_group_stride + (size_t)(m0 + r) * p.ldc + n0 + 4 * lane) =
+            make_uint2(tc::pack_bf16(v.x, v.y), tc::pack_bf16(v.z, v.w));
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<128>(tmem);
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 3-D bf16 tensor map {inner, rows, groups}; box {64, box_rows, 1}; 128-byte swizzle.
+static int make_map(CUtensorMap* m, const void* base, int64_t inner, int64_t rows, int64_t groups, int64_t ld, int64_t group_stride,
+                    int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return set_err(FEDB_E_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)groups};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)(groups > 1 ? group_stride : ld * rows) * 2};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled failed with CUresult %d (inner %lld rows %lld ld %lld)", (int)r, (long long)inner,
+             (long long)rows, (long long)ld);
+    return FEDB_E_CUDA;
+  }
+  return FEDB_OK;
+}
+
+extern "C" int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream) {
+  const FedbGemm& p = *args_host;
+  FEDB_REQUIRE(n_groups > 0 && p.M > 0 && p.N > 0 && p.K > 0, "bad GEMM sizes");
+  FEDB_REQUIRE(p.M % 128 == 0 && p.N % 16 == 0 && p.K % 16 == 0, "GEMM needs M % 128 == 0, N % 16 == 0, K % 16 == 0");
+  FEDB_REQUIRE(p.lda % 8 == 0 && p.ldb % 8 == 0 && p.a_group_stride % 8 == 0 && p.b_group_stride % 8 == 0,
+               "operand leading dimensions / group strides must be multiples of 8 elements (16 bytes)");
+  FEDB_REQUIRE(((uintptr_t)p.A % 16) == 0 && ((uintptr_t)p.B % 16) == 0, "operands must be 16-byte aligned");
+  alignas(64) CUtensorMap tmA, tmB;
+  // K-major source [MN rows][K]: inner = K, box rows = 128 (MN).  MN-major source [K rows][MN]: inner = MN, box rows = 64 (K).
+  if (int rc = p.a_mn ? make_map(&tmA, p.A, p.M, p.K, n_groups, p.lda, p.a_group_stride, 64)
+                      : make_map(&tmA, p.A, p.K, p.M, n_groups, p.lda, p.a_group_stride, 128)) return rc;
+  if (int rc = p.b_mn ? make_map(&tmB, p.B, p.N, p.K, n_groups, p.ldb, p.b_group_stride, 64)
+                      : make_map(&tmB, p.B, p.K, p.N, n_groups, p.ldb, p.b_group_stride, 128)) return rc;
+  static bool attr_set = false;
+  const int tile_bytes = BM * TILE_LD * 4;
+  const int smem = (STAGES * STAGE_BYTES > tile_bytes ? STAGES * STAGE_BYTES : tile_bytes) + 1024;
+  if (!attr_set) {
+    FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_gemm_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  dim3 grid((p.N + BN - 1) / BN, p.M / BM, n_groups);
+  k_gemm_tma<<<grid, T_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, p);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}

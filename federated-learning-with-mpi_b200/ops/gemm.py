@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import numpy as np
@@ -38,5 +39,6 @@ def gemm(n_groups: int, M: int, N: int, K_: int, A, a_stride: int, lda: int, a_m
     a["act"], a["act_group_stride"], a["ldact"] = _p(act), act_stride, ldact
     a["W"], a["Mom"], a["Vel"], a["Wsh"], a["w_group_stride"], a["ldw"], a["l2_scale"] = _p(W), _p(Mom), _p(Vel), _p(Wsh), w_stride, ldw, l2_scale
     a["groups"], a["step"] = _p(groups), _p(step)
-    nat.check(lib.fedb_gemm_tc(a.ctypes.data, n_groups, nat.cuda_stream()))
+    fn = lib.fedb_gemm_tc if os.environ.get("FEDB200_GEMM", "tma") == "cpasync" else lib.fedb_gemm_tma
+    nat.check(fn(a.ctypes.data, n_groups, nat.cuda_stream()))
     K._count()

@@ -252,7 +252,9 @@ int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_siz
 /* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
  * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
 int32_t fedb_gemm_args_size(void);
-int fedb_gemm_tc(const FedbGemm* args_host, int32_t n_groups, void* stream);
+int fedb_gemm_tc(const FedbGemm* args_host, int32_t n_groups, void* stream);   /* cp.async-fed variant (fallback) */
+/* Main variant: TMA-fed (3-D tensor maps encoded per call), warp-specialised, coalesced epilogues. */
+int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream);
 
 /* Wide-MLP path, the kernels around fedb_gemm_tc (csrc/fedb_wide.cu).  A* / dZ are bf16 [G][B][d]
  * activation buffers (B rows per client, padded shards must be equal-sized); dz is fp32 [G][B][8]. */

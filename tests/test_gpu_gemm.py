@@ -7,6 +7,12 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["tma", "cpasync"], autouse=True)
+def _variant(request, monkeypatch):
+    """Every case runs on both the TMA-fed main kernel and the cp.async fallback."""
+    monkeypatch.setenv("FEDB200_GEMM", request.param)
+
+
 def _bf(x):
     return x.to(torch.bfloat16)
 
