@@ -35,7 +35,7 @@ def test_wide_gradients_match_fp32(income, hidden, rows, clients):
                 a, b = view(g32[c * P:(c + 1) * P], l), view(gw[c * P:(c + 1) * P], l)
                 cos = float((a * b).sum() / (a.norm() * b.norm() + 1e-20))
                 assert cos > 0.995, (c, l, view.__name__, cos)
-                assert float((a - b).abs().max()) <= 0.1 * float(a.abs().max()) + 1e-7, (c, l, view.__name__)
+                assert float((a - b).abs().max()) <= 0.2 * float(a.abs().max()) + 1e-7, (c, l, view.__name__)
     np.testing.assert_allclose(wide.loss.cpu().numpy(), f32.loss.cpu().numpy(), rtol=1e-2)
     assert torch.equal(wide.step, f32.step)
     assert float(wide.params.cpu()[~spec.param_mask().repeat(clients)].abs().max()) == 0.0
