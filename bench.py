@@ -36,10 +36,17 @@ def parse():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"],
                     help="ours | reference (unmodified scripts) | nccl (stock torch + NCCL all_reduce baseline)")
-    ap.add_argument("--clients-per-gpu", type=int, default=1)
+    ap.add_argument("--clients-per-gpu", type=int, default=None, help="default: 1 (income) / 128 (wide)")
+    ap.add_argument("--config", default="income", choices=["income", "wide"],
+                    help="income = BASELINE config 3 (the headline; default); wide = BASELINE config 5 (4 x 4096 hidden, "
+                         "synthetic income-shaped non-IID data, 1024 rows per client, SGD) — ours only")
+    ap.add_argument("--width", type=int, default=4096)
     ap.add_argument("--precision", default=None, help="ours: fp32 (SIMT) | tf32 (tcgen05); default = best available")
     ap.add_argument("--no-flush", action="store_true", help="debug: skip the L2 flush between timed steps")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.clients_per_gpu is None:
+        a.clients_per_gpu = 128 if a.config == "wide" else 1
+    return a
 
 
 def dist_env():
@@ -47,6 +54,19 @@ def dist_env():
 
 
 def base_record(args, world, impl):
+    if args.config == "wide":
+        rows = 1024
+        return {
+            "metric": "fedavg_client_samples_per_sec", "unit": "client-samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "data": "synthetic income-shaped rows (label-skewed clients), random-init weights", "impl": impl,
+            "config": {"model": f"mlp-14-{args.width}x4-2 softmax-CE, SGD(lr=0.05), 1 full-batch local step/round, local eval + "
+                                "weighted P/R/F1, sample-weighted FedAvg (BASELINE config 5)",
+                       "clients": world * args.clients_per_gpu, "clients_per_gpu": args.clients_per_gpu, "rows_per_client": rows,
+                       "global_batch": world * args.clients_per_gpu * rows, "seq_len": None,
+                       "parallelism": f"federated-dp{world} (one process per GPU)",
+                       "l2": "working set (weights of all clients) far larger than L2; no flush"},
+        }
     return {
         "metric": "fedavg_client_samples_per_sec", "unit": "client-samples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "data": "bundled income CSV (real rows), random-init weights",
@@ -66,28 +86,42 @@ def run_ours(args):
     import torch
     rank, local_rank, world = dist_env()
     torch.cuda.set_device(local_rank)
-    from fedb200 import FedProblem, prepare
+    from fedb200 import FedProblem, TrainHyper, prepare, synthetic_income_like
     from fedb200.utils.clocks import ClockSampler
-    data = prepare(with_mean=True)
+    rec0 = base_record(args, world, "ours")
     cpg = args.clients_per_gpu
     n_clients = world * cpg
-    # client c owns rows [c*1000, (c+1)*1000) of the (already shuffled) train split, wrapping if needed
-    rows = [(np.arange(ROWS_PER_CLIENT) + c * ROWS_PER_CLIENT) % len(data.X_train) for c in range(n_clients)]
+    extra = {}
+    if args.config == "wide":
+        rows_per_client = 1024
+        data = synthetic_income_like(40000, seed=1)
+        rng = np.random.default_rng(0)
+        pos, neg = np.flatnonzero(data.y_train == 1), np.flatnonzero(data.y_train == 0)
+        rows = []
+        for c in range(n_clients):          # label-skewed (non-IID) clients: class mix ~ Beta(0.5, 0.5)
+            k = int(rows_per_client * rng.beta(0.5, 0.5))
+            rows.append(np.concatenate([rng.choice(pos, k), rng.choice(neg, rows_per_client - k)]))
+        extra = dict(hidden=(args.width,) * 4, hyper=TrainHyper(opt="sgd", lr=0.05, lr_step_size=0), shared_init=True)
+    else:
+        rows_per_client = ROWS_PER_CLIENT
+        data = prepare(with_mean=True)
+        # client c owns rows [c*1000, (c+1)*1000) of the (already shuffled) train split, wrapping if needed
+        rows = [(np.arange(ROWS_PER_CLIENT) + c * ROWS_PER_CLIENT) % len(data.X_train) for c in range(n_clients)]
     if world > 1:
         from fedb200.parallel.dist_engine import DistFedEngine, init_distributed
         init_distributed()
         eng = DistFedEngine.custom_income(data, rows, rank, world, max_rounds=3 * args.steps + args.warmup + 32,
-                                          precision=args.precision)
+                                          precision=args.precision, **extra)
     else:
         from fedb200.parallel.dist_engine import make_local_engine
-        eng = make_local_engine(data, rows, max_rounds=3 * args.steps + args.warmup + 32, precision=args.precision)
+        eng = make_local_engine(data, rows, max_rounds=3 * args.steps + args.warmup + 32, precision=args.precision, **extra)
 
     def barrier():
         if world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
-    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    flush = None if (args.no_flush or args.config == "wide") else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     K, W = args.steps, args.warmup
     # ---- device-timed rounds ------------------------------------------------------------------
     for _ in range(W):
@@ -130,13 +164,14 @@ def run_ours(args):
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms_flushed, ms_warm, ms_e2e = (float(x) for x in t.cpu())
-    samples = n_clients * ROWS_PER_CLIENT
-    rec = base_record(args, world, "ours")
+    samples = n_clients * rows_per_client
+    rec = rec0
     value = samples * K / (ms_flushed / 1e3)
     h2d, d2h = eng.e2e_bytes()
     hist = eng.history()
     rec.update({
-        "value": value, "ms_per_step": ms_flushed / K, "vs_baseline": value / BASELINE_SAMPLES_PER_SEC,
+        "value": value, "ms_per_step": ms_flushed / K,
+        "vs_baseline": (value / BASELINE_SAMPLES_PER_SEC) if args.config == "income" else None,
         "dtype": eng.precision_name, "rounds_per_sec": K / (ms_flushed / 1e3),
         "vs_baseline_rounds_per_sec": (K / (ms_flushed / 1e3)) / BASELINE_ROUNDS_PER_SEC,
         "warm_no_flush": {"ms_per_step": ms_warm / K, "client_samples_per_sec": samples * K / (ms_warm / 1e3),

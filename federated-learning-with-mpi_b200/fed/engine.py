@@ -24,6 +24,7 @@ from ..models import init as minit
 from ..models.spec import MLPSpec
 from ..ops import _native as nat
 from ..ops import kernels as K
+from ..utils import trace
 from .metrics import METRIC_NAMES
 from .problem import FedProblem
 
@@ -292,8 +293,10 @@ class FedEngine:
             return
         if not self._begin_is_fused():
             self.enqueue_round_begin()
-        self.enqueue_local_part()
-        self.enqueue_aggregate()
+        with trace.span("fedb200.local_train_eval"):
+            self.enqueue_local_part()
+        with trace.span("fedb200.aggregate"):
+            self.enqueue_aggregate()
 
     def enqueue_round_begin(self) -> None:
         K.round_begin(self.tb, self.fed_state, self.conf)
@@ -566,7 +569,7 @@ class FedEngine:
         if self._fused_round_ok():
             return ["k_local_round_tc[train+eval+fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
-            return ["k_round_begin", "k_gemm_tc[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
+            return ["k_round_begin", "k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
                     "k_fedavg", "k_wide_shadow"]
         if self.precision_name == "bf16":
             return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]

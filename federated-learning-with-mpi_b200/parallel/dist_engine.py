@@ -41,9 +41,12 @@ def _compact(data, rows: Sequence[np.ndarray]):
 
 
 def make_local_engine(data, rows: Sequence[np.ndarray], max_rounds: int = 300, precision: Optional[str] = None,
-                      patience: int = 0, device: Optional[str] = None) -> FedEngine:
+                      patience: int = 0, device: Optional[str] = None, hidden=(50, 200), hyper=None,
+                      shared_init: bool = False) -> FedEngine:
     X, y, shards = _compact(data, rows)
-    prob = FedProblem.custom(data.n_features, data.n_classes, shards, patience=patience)
+    kw = {} if hyper is None else {"hyper": hyper}
+    prob = FedProblem.custom(data.n_features, data.n_classes, shards, hidden=tuple(hidden), patience=patience,
+                             init_per_client=not shared_init, **kw)
     return FedEngine([prob], X, y, data.X_test, data.y_test, device=device, max_rounds=max_rounds, precision=precision)
 
 
@@ -154,11 +157,15 @@ class DistFedEngine(FedEngine):
 
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> None:
         p2p.launch(self.rank_dev, 1, self.p2p_blocks)   # begin_next is baked into the rank record (always on)
+        if self.precision_name == "bf16_wide":
+            self.wide.refresh_shadow()                  # averaged fp32 weights -> bf16 GEMM operands
 
     @property
     def kernel_names(self) -> List[str]:
         if self._fused_p2p_ok():
             return ["k_local_round_tc[train+eval+p2p-fedavg+metrics]"]
+        if self.precision_name == "bf16_wide":
+            return ["k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt", "k_fedavg_p2p", "k_wide_shadow"]
         local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
         return local + ["k_fedavg_p2p"]
 
@@ -184,9 +191,12 @@ class DistFedEngine(FedEngine):
 
     @staticmethod
     def custom_income(data, rows: Sequence[np.ndarray], rank: int, world: int, max_rounds: int = 300,
-                      precision: Optional[str] = None, patience: int = 0) -> "DistFedEngine":
+                      precision: Optional[str] = None, patience: int = 0, hidden=(50, 200), hyper=None,
+                      shared_init: bool = False) -> "DistFedEngine":
         """The benchmark federation: one custom-MLP federation whose client c owns ``rows[c]``."""
-        prob = FedProblem.custom(data.n_features, data.n_classes, [np.asarray(r, dtype=np.int32) for r in rows], patience=patience)
+        kw = {} if hyper is None else {"hyper": hyper}
+        prob = FedProblem.custom(data.n_features, data.n_classes, [np.asarray(r, dtype=np.int32) for r in rows], hidden=tuple(hidden),
+                                 patience=patience, init_per_client=not shared_init, **kw)
         return DistFedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
                              max_rounds=max_rounds, precision=precision)
 
