@@ -97,10 +97,13 @@ def cmd_custom(args) -> int:
                              atol=args.tolerance, weighting=args.weighting, init_seed=args.seed, init_per_client=not args.shared_init)
     world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
     if world > 1:
-        from .parallel.dist_engine import DistFedEngine, init_distributed
-        init_distributed()
-        eng = DistFedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
-                            max_rounds=args.rounds, seed=args.seed, precision=args.precision)
+        import torch
+        from .parallel.dist_engine import DistFedEngine, GlooFedEngine, init_distributed
+        on_gpu = torch.cuda.is_available() and args.device != "cpu"
+        init_distributed("nccl" if on_gpu else "gloo")
+        Engine = DistFedEngine if on_gpu else GlooFedEngine       # NVLink kernels / CPU plumbing (BASELINE config 1)
+        eng = Engine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
+                     max_rounds=args.rounds, seed=args.seed, precision=args.precision)
     else:
         eng = FedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, device=args.device, max_rounds=args.rounds,
                         seed=args.seed, precision=args.precision)

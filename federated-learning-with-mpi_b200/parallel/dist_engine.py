@@ -236,3 +236,88 @@ class EmulatedWorld:
         for r in self.ranks:
             r.check_errors()
         return [r.history() for r in self.ranks]
+
+
+class GlooFedEngine(FedEngine):
+    """CPU multi-process federation (BASELINE config 1: "mpirun -np 3 ... on CPU, plumbing, no GPU"): every
+    process hosts its share of the clients on the fp32 host path and the aggregation is a gloo
+    ``all_reduce`` of the locally weighted slabs plus an ``all_gather`` of the confusion counts.  Same
+    placement, arithmetic order per rank, metrics and early-stop rule as :class:`DistFedEngine`; this is the
+    no-GPU stand-in for its NVLink kernel, not a hot path."""
+
+    def __init__(self, problems: Sequence[FedProblem], X_train, y_train, X_test=None, y_test=None, rank: int = 0, world: int = 1,
+                 max_rounds: int = 300, seed: int = 0, **_):
+        import torch.distributed as dist
+        self.rank, self.world = rank, world
+        self.global_problems = list(problems)
+        local = []
+        for p in problems:
+            mine = place_clients(p.n_clients, world)[rank]
+            if len(mine) == 0:
+                raise ValueError("fewer clients than ranks")
+            total = float(sum(len(s) for s in p.shards)) if p.weighting == "samples" else float(p.n_clients)
+            local.append(_replace(p, shards=[p.shards[k] for k in mine], total_weight=total, client_offset=mine[0]))
+        super().__init__(local, X_train, y_train, X_test, y_test, device="cpu", max_rounds=max_rounds, seed=seed)
+        self.n_groups_total = sum(p.n_clients for p in problems)
+        self._owner = [[q for q in range(world) for _ in place_clients(p.n_clients, world)[q]] for p in problems]
+        self.hist_local = torch.zeros(self.max_rounds * self.n_groups_total * 4)
+        self._dist = dist
+        self._group = dist.new_group(backend="gloo") if dist.get_backend() != "gloo" else None
+
+    def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = False) -> None:
+        from ..fed.metrics import EarlyStop, mean_of_local, pooled
+        from ..ops import reference as ref
+        dist, st = self._dist, self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
+        # local weighted partial sums with the single-process kernel (no write-back, no metrics) ...
+        ref.fedavg(self.tb.groups, self.tb.feds, self.fed_state, self.tb.max_slab, self.params, self.global_, self.conf,
+                   None, None, False, False)
+        # ... summed over ranks (gloo sums in rank order for small tensors; results are identical on all ranks)
+        dist.all_reduce(self.global_, group=self._group)
+        confs = [torch.zeros_like(self.conf[: self.n_groups * p2p.C2]) for _ in range(self.world)]
+        dist.all_gather(confs, self.conf[: self.n_groups * p2p.C2].contiguous(), group=self._group)
+        g_base = 0
+        for f, p in enumerate(self.global_problems):
+            if st[f]["stop"]:
+                g_base += p.n_clients
+                continue
+            P, C = p.spec.slab_size, p.spec.n_classes
+            if write_back:
+                for gi in self.group_of[f]:
+                    o = int(self.tb.groups[gi]["slab_off"])
+                    self.params[o: o + P] = self.global_slab(f)
+            if do_metrics:
+                # confusion matrices of ALL clients of the federation, in global client order
+                cms, seen = [], {q: 0 for q in range(self.world)}
+                base = {q: sum(len(place_clients(pp.n_clients, self.world)[q]) for pp in self.global_problems[:f]) for q in range(self.world)}
+                for q in self._owner[f]:
+                    cm = confs[q].view(-1, nat.MAX_CLASSES, nat.MAX_CLASSES)[base[q] + seen[q]].numpy()[:C, :C]
+                    seen[q] += 1
+                    cms.append(cm)
+                r = int(st[f]["round"]) - 1
+                from ..fed.metrics import metrics_from_confusion
+                loc = np.array([[metrics_from_confusion(c)[k] for k in ("accuracy", "precision", "recall", "f1")] for c in cms])
+                glob = pooled(cms) if p.metric_mode == "pooled" else mean_of_local(cms)
+                gv = np.array([glob[k] for k in ("accuracy", "precision", "recall", "f1")])
+                if 0 <= r < self.max_rounds:
+                    self.hist_local.view(self.max_rounds, self.n_groups_total, 4)[r, g_base: g_base + p.n_clients] = torch.from_numpy(loc).float()
+                    self.hist_global.view(self.n_feds, self.max_rounds, 4)[f, r] = torch.from_numpy(gv).float()
+                st[f]["last"] = gv
+                if p.patience > 0:
+                    close = bool(st[f]["has_anchor"]) and bool(np.all(np.abs(gv - st[f]["anchor"]) <= p.atol + p.rtol * np.abs(st[f]["anchor"])))
+                    if close:
+                        st[f]["count"] -= 1
+                        if st[f]["count"] == 0:
+                            st[f]["stop_pending"] = 1
+                    else:
+                        st[f]["anchor"], st[f]["has_anchor"], st[f]["count"] = gv, 1, p.patience
+                st[f]["done"] = st[f]["round"]
+            g_base += p.n_clients
+
+    def history(self) -> Dict[str, np.ndarray]:
+        st = self.fed_state_host()
+        R = int(st["done"].max()) if len(st) else 0
+        from ..fed.metrics import METRIC_NAMES
+        return {"global": self.hist_global.numpy().reshape(self.n_feds, self.max_rounds, 4)[:, :R].astype(np.float64),
+                "local": self.hist_local.numpy().reshape(self.max_rounds, self.n_groups_total, 4)[:R].astype(np.float64),
+                "rounds": st["done"].copy(), "stopped": st["stop"].astype(bool) | st["stop_pending"].astype(bool),
+                "last": st["last"].copy(), "metric_names": np.asarray(METRIC_NAMES)}

@@ -1,0 +1,43 @@
+"""Multi-process paths on CPU (gloo, world_size 2/3): the CPU-plumbing federation of BASELINE config 1
+and the reference arm of bench.py (unmodified reference script over the mpi4py stand-in)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _torchrun(nproc, port, args, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
+           "--master-port", str(port)] + args
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="1")
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=ROOT)
+
+
+def test_three_rank_cpu_federation_matches_single_process(tmp_path):
+    from fedb200.cli import main as cli_main
+    single, multi = str(tmp_path / "s.jsonl"), str(tmp_path / "m.jsonl")
+    common = ["custom", "--clients", "3", "--rounds", "4", "--device", "cpu", "--quiet", "--partition", "contiguous", "--synthetic-rows", "900"]
+    assert cli_main(common + ["--jsonl", single]) == 0
+    out = _torchrun(3, 29631, ["-m", "fedb200"] + common + ["--jsonl", multi])
+    assert out.returncode == 0, out.stderr[-2000:]
+    a = [json.loads(l) for l in open(single)][:4]
+    b = [json.loads(l) for l in open(multi)][:4]
+    for ra, rb in zip(a, b):
+        np.testing.assert_allclose(ra["global_metrics"], rb["global_metrics"], atol=1e-6)
+        np.testing.assert_allclose(ra["local_metrics"], rb["local_metrics"], atol=1e-6)
+
+
+def test_reference_arm_runs_unmodified_script_on_two_ranks():
+    if not os.path.exists(os.path.join(ROOT, "baseline", "_ref", "FL_CustomMLPCLassifierImplementation_Multiple_Rounds.py")) \
+            and not os.path.exists("/root/reference"):
+        import pytest
+        pytest.skip("reference scripts not available")
+    out = _torchrun(2, 29632, ["bench.py", "--impl", "reference", "--gpus", "2", "--steps", "4", "--warmup", "1"])
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert rec["impl"] == "reference" and rec["n_gpus"] == 2 and rec["value"] > 0
+    assert 0.4 < rec["final_global_accuracy_train_shards"] <= 1.0
