@@ -121,22 +121,39 @@ __global__ void __launch_bounds__(T_THREADS) k_gemm_tma(const __grid_constant__ 
   if (p.epilogue == FEDB_GEMM_WGRAD_OPT) {
     const StepScalars sc = sc_s;
     const bool use_v = p.Vel && Gs.opt != FEDB_OPT_SGD;
+    const bool use_m = p.Mom && !(Gs.opt == FEDB_OPT_SGD && Gs.momentum == 0.f);   // plain SGD keeps no state: skip its traffic
     const float l2 = Gs.alpha * p.l2_scale;
-    for (int r = warp; r < BM; r += T_THREADS / 32) {
+    constexpr int NW = T_THREADS / 32, UR = 4;       // 4 rows per warp in flight: the epilogue is bound by optimizer-state traffic
+    for (int r0 = warp; r0 < BM; r0 += NW * UR) {
+      size_t off[UR];
+      float4 w[UR], mm[UR], vv[UR];
       if (lane < nq) {
-        const size_t off = (size_t)g * p.w_group_stride + (size_t)(m0 + r) * p.ldw + n0 + 4 * lane;
-        const float4 gr = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
-        float4 w = *reinterpret_cast<const float4*>(p.W + off);
-        float4 mm = p.Mom ? *reinterpret_cast<const float4*>(p.Mom + off) : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 vv = use_v ? *reinterpret_cast<const float4*>(p.Vel + off) : make_float4(0.f, 0.f, 0.f, 0.f);
-        w.x = opt_update(Gs, sc, w.x, fmaf(l2, w.x, gr.x), mm.x, vv.x);
-        w.y = opt_update(Gs, sc, w.y, fmaf(l2, w.y, gr.y), mm.y, vv.y);
-        w.z = opt_update(Gs, sc, w.z, fmaf(l2, w.z, gr.z), mm.z, vv.z);
-        w.w = opt_update(Gs, sc, w.w, fmaf(l2, w.w, gr.w), mm.w, vv.w);
-        *reinterpret_cast<float4*>(p.W + off) = w;
-        if (p.Mom) *reinterpret_cast<float4*>(p.Mom + off) = mm;
-        if (use_v) *reinterpret_cast<float4*>(p.Vel + off) = vv;
-        if (p.Wsh) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.Wsh) + off) = make_uint2(tc::pack_bf16(w.x, w.y), tc::pack_bf16(w.z, w.w));
+#pragma unroll
+        for (int u = 0; u < UR; ++u) {
+          const int r = r0 + u * NW;
+          off[u] = (size_t)g * p.w_group_stride + (size_t)(m0 + r) * p.ldw + n0 + 4 * lane;
+          if (r < BM) {
+            w[u] = *reinterpret_cast<const float4*>(p.W + off[u]);
+            mm[u] = use_m ? *reinterpret_cast<const float4*>(p.Mom + off[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            vv[u] = use_v ? *reinterpret_cast<const float4*>(p.Vel + off[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UR; ++u) {
+          const int r = r0 + u * NW;
+          if (r < BM) {
+            const float4 gr = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+            float4 x = w[u];
+            x.x = opt_update(Gs, sc, x.x, fmaf(l2, x.x, gr.x), mm[u].x, vv[u].x);
+            x.y = opt_update(Gs, sc, x.y, fmaf(l2, x.y, gr.y), mm[u].y, vv[u].y);
+            x.z = opt_update(Gs, sc, x.z, fmaf(l2, x.z, gr.z), mm[u].z, vv[u].z);
+            x.w = opt_update(Gs, sc, x.w, fmaf(l2, x.w, gr.w), mm[u].w, vv[u].w);
+            *reinterpret_cast<float4*>(p.W + off[u]) = x;
+            if (use_m) *reinterpret_cast<float4*>(p.Mom + off[u]) = mm[u];
+            if (use_v) *reinterpret_cast<float4*>(p.Vel + off[u]) = vv[u];
+            if (p.Wsh) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.Wsh) + off[u]) = make_uint2(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w));
+          }
+        }
       }
     }
   } else if (p.epilogue == FEDB_GEMM_STORE_F32) {

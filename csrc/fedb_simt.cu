@@ -12,6 +12,7 @@
 //   k_fedavg      C:101-120, S:108-122, H:24-46 (aggregation) + C:165-192 (global metrics,
 //                 early stop)
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 namespace fedb {
 
@@ -567,7 +568,7 @@ __global__ void __launch_bounds__(NTHREADS)
 k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds, FedbFedState* __restrict__ state,
          int n_groups, float* __restrict__ params, float* __restrict__ global, const int32_t* __restrict__ conf,
          float* __restrict__ hist_local, float* __restrict__ hist_global, int write_back, int do_metrics, int begin_next,
-         int32_t* __restrict__ conf_rw) {
+         int32_t* __restrict__ conf_rw, uint16_t* __restrict__ shadow) {
   const int f = blockIdx.y;
   const FedbFed& F = feds[f];
   if (state[f].stop) return;
@@ -585,9 +586,15 @@ k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds,
       acc.w += __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den);
     }
     *reinterpret_cast<float4*>(global + F.global_off + e) = acc;
-    if (write_back)
+    if (write_back) {
       for (int k = 0; k < F.n_clients; ++k)
         *reinterpret_cast<float4*>(params + groups[F.first_group + k].slab_off + e) = acc;
+      if (shadow) {   // wide path: the bf16 GEMM operands of every client follow the averaged weights in the same pass
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
+        const uint2 pk = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+        for (int k = 0; k < F.n_clients; ++k) *reinterpret_cast<uint2*>(shadow + groups[F.first_group + k].slab_off + e) = pk;
+      }
+    }
   }
   if (blockIdx.x == 0) {
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
@@ -724,7 +731,7 @@ extern "C" int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const
 extern "C" int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
                            int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
                            float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
-                           int32_t begin_next, void* stream) {
+                           int32_t begin_next, void* shadow_bf16, void* stream) {
   FEDB_REQUIRE(n_feds > 0 && max_slab > 0, "bad sizes");
   dim3 grid((max_slab / 4 + NTHREADS - 1) / NTHREADS, n_feds);
   // begin_next raises the stop flag at the end of block (0, f); with more than one block per federation a
@@ -732,7 +739,7 @@ extern "C" int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFed
   FEDB_REQUIRE(!begin_next || grid.x == 1, "begin_next needs a single block per federation (slab <= 1024 floats)");
   k_fedavg<<<grid, NTHREADS, 0, (cudaStream_t)stream>>>(groups, feds, state, n_groups, params, global, conf, hist_local,
                                                         hist_global, write_back, do_metrics, begin_next,
-                                                        const_cast<int32_t*>(conf));
+                                                        const_cast<int32_t*>(conf), (uint16_t*)shadow_bf16);
   FEDB_LAUNCH_OK();
   return FEDB_OK;
 }

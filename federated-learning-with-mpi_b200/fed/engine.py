@@ -256,10 +256,10 @@ class FedEngine:
                    self.global_, self.X, self.y, self.idx, self.conf, self.fed_state)
 
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = False) -> None:
+        # wide path: the averaged fp32 weights replace every client's bf16 GEMM operands in the same pass
+        shadow = self.wide.shadow if (self.precision_name == "bf16_wide" and write_back and self.wide is not None) else None
         K.fedavg(self.tb, self.fed_state, self.params, self.global_, self.conf, self.hist_local, self.hist_global,
-                 write_back, do_metrics, begin_next)
-        if self.precision_name == "bf16_wide" and write_back:
-            self.wide.refresh_shadow()   # the averaged fp32 weights replace every client's bf16 operands
+                 write_back, do_metrics, begin_next, shadow)
 
     def _begin_is_fused(self) -> bool:
         """True when the aggregation kernel also performs the next round's begin bookkeeping (the
@@ -324,7 +324,7 @@ class FedEngine:
         if self._fused_round_ok():
             return 1
         if self.precision_name == "bf16_wide":
-            return 1 + E * self.wide.launches_per_step + (self.wide.L - 1) + 1 + 2
+            return 1 + E * self.wide.launches_per_step + (self.wide.L - 1) + 1 + 1
         if self.precision_name == "bf16":
             return 3 if not self._begin_is_fused() else 2
         return 1 + 2 * E * self.n_batches + 2
@@ -570,7 +570,7 @@ class FedEngine:
             return ["k_local_round_tc[train+eval+fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
             return ["k_round_begin", "k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
-                    "k_fedavg", "k_wide_shadow"]
+                    "k_fedavg[+bf16 shadow]"]
         if self.precision_name == "bf16":
             return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]
         return ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]

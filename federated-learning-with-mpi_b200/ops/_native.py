@@ -202,7 +202,7 @@ def _declare(l: ctypes.CDLL) -> None:
         "fedb_reduce_opt": [_P, _I32, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _I32, _P],
         "fedb_epoch_end": [_P, _I32, _P, _I32, _I32, _F64, _I32, _I32, _P, _P, _P, _P, _P, _P],
         "fedb_eval": [_P, _P, _P, _I32, _P, _P, _P, _I32, _P, _P, _P, _P, _I64, _P],
-        "fedb_fedavg": [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P],
+        "fedb_fedavg": [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P],
     }
     for name, args in sigs.items():
         fn = getattr(l, name)

@@ -172,11 +172,12 @@ def evaluate(tb: DeviceTables, jobs_np: np.ndarray, d_jobs, tiles, n_tiles: int,
 
 
 def fedavg(tb: DeviceTables, fed_state, params, global_, conf, hist_local, hist_global, write_back: bool = True,
-           do_metrics: bool = True, begin_next: bool = False) -> None:
+           do_metrics: bool = True, begin_next: bool = False, shadow=None) -> None:
     if _cuda(params):
         nat.check(_L().fedb_fedavg(nat.ptr(tb.d_groups), nat.ptr(tb.d_feds), nat.ptr(fed_state), tb.n_feds, tb.n_groups,
                                    tb.max_slab, nat.ptr(params), nat.ptr(global_), nat.ptr(conf), nat.ptr(hist_local),
-                                   nat.ptr(hist_global), int(write_back), int(do_metrics), int(begin_next), nat.cuda_stream()))
+                                   nat.ptr(hist_global), int(write_back), int(do_metrics), int(begin_next), nat.ptr(shadow),
+                                   nat.cuda_stream()))
         _count()
     else:
         ref.fedavg(tb.groups, tb.feds, fed_state, tb.max_slab, params, global_, conf, hist_local, hist_global,

@@ -224,11 +224,12 @@ int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const FedbTile* 
  * hist_global: [n_feds][max_rounds][4].  write_back=0 leaves client slabs untouched.
  * begin_next=1 additionally does the next round's fedb_round_begin work for the federation
  * (stop promotion, round count, clearing its clients' confusion slots); only valid when one block
- * covers a federation's slab (max_slab <= 1024 floats) — larger problems call fedb_round_begin. */
+ * covers a federation's slab (max_slab <= 1024 floats) — larger problems call fedb_round_begin.
+ * shadow_bf16 (optional): bf16 arena with the params layout that receives the averaged weights too. */
 int fedb_fedavg(const FedbGroup* groups, const FedbFed* feds, FedbFedState* state, int32_t n_feds,
                 int32_t n_groups, int32_t max_slab, float* params, float* global, const int32_t* conf,
                 float* hist_local, float* hist_global, int32_t write_back, int32_t do_metrics,
-                int32_t begin_next, void* stream);
+                int32_t begin_next, void* shadow_bf16, void* stream);
 
 /* K2a/K3 on tcgen05: n_steps local optimizer steps (+ local evaluation into conf slot g) for every
  * group in one launch, one thread-block cluster per client (csrc/fedb_tc.cu; C:63-91).  Groups
