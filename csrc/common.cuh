@@ -247,7 +247,8 @@ __device__ inline void begin_next_round(FedbFedState& S) {
 // metrics and runs the early-stop rule.  `pool` = 64 ints of shared memory.  All 32 lanes must call.
 // (F is taken BY VALUE: through a pointer every field access may be re-fetched from L2 after each store)
 __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
-                                          float* hist_local, float* hist_global, int* pool, bool begin_next = false) {
+                                          float* hist_local, float* hist_global, int* pool, bool begin_next = false,
+                                          FedbFedState* host_mirror = nullptr) {
   const int lane = threadIdx.x & 31;
   const int C = F.n_classes;
   const int r = S.round - 1;  // 0-based index of the round in progress
@@ -289,6 +290,7 @@ __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int 
     st.done = st.round;
     if (begin_next) begin_next_round(st);
     S = st;
+    if (host_mirror) *host_mirror = st;   // mapped pinned host memory: the round's result reaches the host without a memcpy node
   }
   __syncwarp();
 }

@@ -81,6 +81,7 @@ struct TcArgs {
   unsigned int* tail_count;   // wraps to 0 by itself (atomicInc)
   // ---- fused cross-GPU aggregation (tail_mode 2): one federation, one resident client per rank ----
   const FedbP2PRank* p2p;
+  FedbFedState* state_mirror;   // optional: mapped pinned host copy of the federation state, written by the tail
 };
 
 struct Shape {
@@ -841,7 +842,8 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
     if (tid < 32)
       for (int f = 0; f < a.n_feds; ++f) {
         if (s_stop[f]) continue;
-        round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true);
+        round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true,
+                           a.state_mirror ? a.state_mirror + f : nullptr);
       }
     __syncthreads();
     if (a.prof && tid == 0) a.prof[21] = clock64();
@@ -919,7 +921,8 @@ __device__ void p2p_tail(const TcArgs& a) {
     __syncthreads();
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32 && R.do_metrics)
-      round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true);
+      round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true,
+                         a.state_mirror);
     __syncthreads();
     for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) a.conf[i] = 0;
     if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
@@ -969,7 +972,7 @@ extern "C" int32_t fedb_tc_max_slab(void) { return (SLOTS_MAX_BYTES - 64) / 4 - 
 
 extern "C" int fedb_round_tc_prof(const FedbGroup*, int32_t, int32_t, const float*, int32_t, const int32_t*, const int32_t*, float*, float*,
                                   float*, int32_t*, const int32_t*, FedbFedState*, float*, int32_t*, float*, int32_t, const FedbFed*,
-                                  int32_t, float*, float*, float*, int32_t, uint32_t*, long long*, void*);
+                                  int32_t, float*, float*, float*, int32_t, uint32_t*, FedbFedState*, long long*, void*);
 
 static int launch_tc(TcArgs a, int32_t n_groups, int32_t cluster_size, void* stream) {
   FEDB_REQUIRE(n_groups > 0 && cluster_size >= 1 && cluster_size <= 8, "bad grid");
@@ -1028,9 +1031,10 @@ extern "C" int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t 
                              const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                              const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                              int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
-                             float* hist_global, int32_t conf_ints, uint32_t* tail_count, void* stream) {
+                             float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror, void* stream) {
   return fedb_round_tc_prof(groups, n_groups, cluster_size, X, ldx, y, idx, params, m, v, step, active, fed_state, loss_out, conf,
-                            scratch, n_steps, feds, n_feds, global, hist_local, hist_global, conf_ints, tail_count, nullptr, stream);
+                            scratch, n_steps, feds, n_feds, global, hist_local, hist_global, conf_ints, tail_count, state_mirror, nullptr,
+                            stream);
 }
 
 // The whole round of a multi-GPU federation with ONE resident client per rank in one launch per rank:
@@ -1039,12 +1043,13 @@ extern "C" int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t 
 extern "C" int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
                                  const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
                                  FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
-                                 const FedbP2PRank* rank_dev, void* stream) {
+                                 const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream) {
   FEDB_REQUIRE(rank_dev != nullptr, "rank record required");
   TcArgs a{};
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
   a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
   a.n_steps = n_steps; a.do_eval = 1; a.prof = nullptr; a.tail_mode = 2; a.n_groups = 1; a.n_feds = 1; a.p2p = rank_dev;
+  a.state_mirror = state_mirror;
   return launch_tc(a, 1, cluster_size, stream);
 }
 
@@ -1052,7 +1057,8 @@ extern "C" int fedb_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int
                                   const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                                   const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                                   int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
-                                  float* hist_global, int32_t conf_ints, uint32_t* tail_count, long long* prof, void* stream) {
+                                  float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror,
+                                  long long* prof, void* stream) {
   FEDB_REQUIRE(feds && fed_state && global && tail_count && n_feds > 0, "bad tail arguments");
   TcArgs a{};
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
@@ -1060,5 +1066,6 @@ extern "C" int fedb_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int
   a.n_steps = n_steps; a.do_eval = 1; a.prof = prof;
   a.tail_mode = 1; a.n_groups = n_groups; a.n_feds = n_feds; a.n_conf = conf_ints; a.feds = feds; a.fed_state_rw = fed_state;
   a.global = global; a.hist_local = hist_local; a.hist_global = hist_global; a.tail_count = tail_count;
+  a.state_mirror = state_mirror;
   return launch_tc(a, n_groups, cluster_size, stream);
 }

@@ -210,6 +210,8 @@ class FedEngine:
         self.batch_stats = z(G * self.n_batches * self.bs_stride, torch.float64)
         self.idx_epoch = self.idx.clone()
         self.tail_count = z(1, torch.int32)
+        # mapped pinned host copy of the federation state: the fused round kernels store their result there too
+        self._state_pinned = torch.zeros(self.fed_state.numel(), dtype=torch.uint8).pin_memory() if d.type == "cuda" else None
 
     def _ensure_wide(self):
         if getattr(self, "_wide_pending", False):
@@ -289,7 +291,7 @@ class FedEngine:
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
                         self.fed_state, self.loss, self.conf, self.scratch, E, self.global_, self.hist_local, self.hist_global,
-                        self.tail_count)
+                        self.tail_count, state_mirror=self._state_pinned)
             return
         if not self._begin_is_fused():
             self.enqueue_round_begin()
@@ -539,23 +541,38 @@ class FedEngine:
         inputs from (pinned) host memory, run the round, read the round's result (federation
         state: stop flag + the four global metrics) back to the host.  Returns the
         ``FedbFedState`` records.  This mirrors what the reference does every round
-        (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic."""
+        (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic.
+        On CUDA the two uploads, the round and the read-back are ONE graph launch (captured per
+        pair of host buffers), followed by one stream synchronisation."""
         self.prime()
-        self.X[: self.n_train].copy_(x_host, non_blocking=True)
-        self.y[: self.n_train].copy_(y_host, non_blocking=True)
-        if self.device.type == "cuda":
-            if "roundx1" not in self._graphs:
+        if self.device.type != "cuda":
+            self.X[: self.n_train].copy_(x_host)
+            self.y[: self.n_train].copy_(y_host)
+            self.enqueue_round()
+            return self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
+        key = f"e2e:{x_host.data_ptr()}:{y_host.data_ptr()}"
+        mirrored = self._result_is_mirrored()   # the round kernel itself writes the result into mapped host memory
+
+        def body():
+            self.X[: self.n_train].copy_(x_host, non_blocking=True)
+            self.y[: self.n_train].copy_(y_host, non_blocking=True)
+            self.enqueue_round()
+            if not mirrored:
+                self._state_pinned.copy_(self.fed_state, non_blocking=True)
+
+        if x_host.is_pinned() and y_host.is_pinned():
+            if key + "x1" not in self._graphs:
                 snap = self._snapshot()
-                self._graph("round", self.enqueue_round, 1)
+                self._graph(key, body, 1)
                 self._restore(snap)
-            self._graphs["roundx1"].replay()
-            if not hasattr(self, "_state_pinned"):
-                self._state_pinned = torch.empty(self.fed_state.numel(), dtype=torch.uint8).pin_memory()
-            self._state_pinned.copy_(self.fed_state, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            return self._state_pinned.numpy().view(nat.FEDSTATE_DTYPE)
-        self.enqueue_round()
-        return self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
+            self._graphs[key + "x1"].replay()
+        else:
+            body()
+        torch.cuda.current_stream().synchronize()
+        return self._state_pinned.numpy().view(nat.FEDSTATE_DTYPE)
+
+    def _result_is_mirrored(self) -> bool:
+        return self._fused_round_ok()
 
     def e2e_bytes(self):
         return self.n_train * self.ldx * 4 + self.n_train * 4, int(self.fed_state.numel())

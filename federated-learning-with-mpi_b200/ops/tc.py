@@ -106,24 +106,25 @@ def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active,
 
 
 def round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
-             global_, hist_local, hist_global, tail_count, prof=None) -> None:
+             global_, hist_local, hist_global, tail_count, prof=None, state_mirror=None) -> None:
     """The whole round in one launch (see fedb_round_tc in include/fedb200.h)."""
     lib = nat.lib(required=True)
     nat.check(lib.fedb_round_tc_prof(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
                                 nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
                                 nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(tb.d_feds), tb.n_feds,
                                 nat.ptr(global_), nat.ptr(hist_local), nat.ptr(hist_global), conf.numel(), nat.ptr(tail_count),
-                                nat.ptr(prof), nat.cuda_stream()))
+                                nat.ptr(state_mirror), nat.ptr(prof), nat.cuda_stream()))
     from . import kernels as K
     K._count()
 
 
 def round_tc_p2p(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
-                 rank_dev) -> None:
+                 rank_dev, state_mirror=None) -> None:
     """Multi-GPU round in one launch per rank (one federation, one resident client): fedb_round_tc_p2p."""
     lib = nat.lib(required=True)
     nat.check(lib.fedb_round_tc_p2p(nat.ptr(tb.d_groups), cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
                                     nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
-                                    nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(rank_dev), nat.cuda_stream()))
+                                    nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(rank_dev), nat.ptr(state_mirror),
+                                    nat.cuda_stream()))
     from . import kernels as K
     K._count()

@@ -140,12 +140,15 @@ class DistFedEngine(FedEngine):
         return (self.precision_name == "bf16" and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
                 and os.environ.get("FEDB200_NO_FUSED_P2P") is None)
 
+    def _result_is_mirrored(self) -> bool:
+        return self._fused_p2p_ok()
+
     def enqueue_round(self) -> None:
         if self._fused_p2p_ok():
             from ..ops import tc
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc_p2p(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
-                            self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev)
+                            self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, state_mirror=self._state_pinned)
             return
         super().enqueue_round()
 

@@ -243,12 +243,15 @@ int fedb_local_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t clust
 
 /* The whole round in ONE launch for small single-GPU problems: fedb_local_round_tc's work, then the
  * last cluster to finish performs fedb_fedavg(write_back=1, do_metrics=1, begin_next=1) for every
- * federation.  conf_ints counters are cleared for the next round; tail_count: one zeroed uint32. */
+ * federation.  conf_ints counters are cleared for the next round; tail_count: one zeroed uint32.
+ * state_mirror (optional): mapped pinned HOST memory, n_feds records; the tail stores the updated
+ * federation state there as well, so a host that syncs on the stream reads the round's result
+ * without a device-to-host memcpy. */
 int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
                   const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                   const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                   int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
-                  float* hist_global, int32_t conf_ints, uint32_t* tail_count, void* stream);
+                  float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror, void* stream);
 
 /* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
  * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
@@ -278,7 +281,7 @@ int fedb_wide_bias_opt(const FedbGroup* groups, int32_t n_groups, float* params,
 int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
                       const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
                       FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
-                      const FedbP2PRank* rank_dev, void* stream);
+                      const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream);
 
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop
