@@ -138,6 +138,25 @@ __device__ void convert_weights(uint8_t* sm, const float* L, const SlabLayout& l
   __syncthreads();
 }
 
+// The small part of convert_weights: W1 (+ b1 in column 15) and b2 (column 63 of W2) from the fp32 landing
+// zone.  W2 itself and the head arrive already converted (publish_weights in the round body).
+__device__ void convert_small(uint8_t* sm, const float* L, const SlabLayout& lay, const Shape& s) {
+  const int tid = threadIdx.x;
+  {
+    const int q = tid & 3, nq = s.ld0 >> 2;
+    for (int j = tid >> 2; j < s.h1; j += TC_THREADS / 4) {
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (q < nq) w = *reinterpret_cast<const float4*>(L + lay.w_off[0] + j * s.ld0 + 4 * q);
+      if (q == 3) w.w = L[lay.b_off[0] + j];
+      *reinterpret_cast<uint2*>(sm + SM_W1 + tc::panel_off(j, 4 * q)) = make_uint2(tc::pack_bf16(w.x, w.y), tc::pack_bf16(w.z, w.w));
+    }
+  }
+  for (int j = tid; j < s.h2; j += TC_THREADS)
+    *reinterpret_cast<__nv_bfloat16*>(sm + SM_W2 + tc::panel_off(j, 63)) = __float2bfloat16_rn(L[lay.b_off[1] + j]);
+  tc::fence_async_smem();
+  __syncthreads();
+}
+
 // Two threads per data row: half h moves columns 8h..8h+7 (global -> registers, issued early so the
 // latency overlaps other work; then registers -> X panel as bf16, column 15 = 1 on valid rows).
 struct RowRegs {
@@ -304,12 +323,41 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
   const float inv_n = 1.f / (float)nb;
   // peers' slot arrays / landing zones over distributed shared memory
   float4* peer_slots[8];
-  float4* peer_land[8];
+  uint8_t* peer_sm[8];   // every CTA's operand area: updated weights are stored straight into the peers' bf16 panels
 #pragma unroll
   for (int rk = 0; rk < 8; ++rk) {
     peer_slots[rk] = cluster.map_shared_rank(slots, rk < CS ? rk : 0);
-    peer_land[rk] = reinterpret_cast<float4*>(cluster.map_shared_rank(landing, rk < CS ? rk : 0));
+    peer_sm[rk] = cluster.map_shared_rank(sm, rk < CS ? rk : 0);
   }
+  // One updated float4 of the slab (element index e) -> the operand image of every CTA of the cluster:
+  // bf16 into the swizzled W1 / W2 panels (biases into their spare K column), fp32 into the head arrays.
+  // This is the all-gather of the new weights AND their conversion in one step.
+  auto publish_weights = [&](int e, const float4 w) {
+    // W2 (88 % of the slab): 4 columns of one row = 8 contiguous bytes of the swizzled panel
+    if (e >= lay.w_off[1] && e < lay.b_off[1]) {
+      const int r = e - lay.w_off[1];
+      const int j = r / s.ld1, i = r - j * s.ld1;
+      const int off = SM_W2 + (int)tc::panel_off(j, i);
+      const uint2 pk = make_uint2(tc::pack_bf16(w.x, w.y), tc::pack_bf16(w.z, w.w));
+#pragma unroll
+      for (int rk = 0; rk < 8; ++rk)
+        if (rk < CS) *reinterpret_cast<uint2*>(peer_sm[rk] + off) = pk;
+      return;
+    }
+    int off;
+    if (e >= lay.w_off[2] && e < lay.b_off[2]) {          // W3 [C][ld2] -> fp32 [C][256]
+      const int r = e - lay.w_off[2];
+      const int k = r / s.ld2, c = r - k * s.ld2;
+      off = SM_W3 + (k * 256 + c) * 4;
+    } else if (e >= lay.b_off[2]) {                       // b3
+      off = SM_B3 + (e - lay.b_off[2]) * 4;
+    } else {                                              // W1, b1, b2: fp32 into the landing zone, converted locally (convert_small)
+      off = SM_STAGE + e * 4;
+    }
+#pragma unroll
+    for (int rk = 0; rk < 8; ++rk)
+      if (rk < CS) *reinterpret_cast<float4*>(peer_sm[rk] + off) = w;
+  };
   // one gradient float4 (slab index e4) -> the owner CTA's slot for this CTA
   auto send_grad = [&](int e4, const float4 v) {
     const int o = (int)__umulhi((uint32_t)e4, inv_per);
@@ -630,8 +678,8 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
     cluster.sync();     // every partial slice has landed in its owner's shared memory
     STAMP(13);
 
-    // ---- owner: fixed-order sum of the CS partials (local shared memory), optimizer, then all-gather of
-    // the updated fp32 slice into every CTA's landing zone (distributed shared memory stores) -------------
+    // ---- owner: fixed-order sum of the CS partials (local shared memory), optimizer, then all-gather +
+    // bf16 conversion of the updated slice into every CTA's operand panels (distributed shared memory) ------
     {
       const StepScalars sc = sc_s;
       int it = 0;
@@ -662,9 +710,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
         w.y = opt_update(G, sc, w.y, gsum.y, mm.y, vv.y);
         w.z = opt_update(G, sc, w.z, gsum.z, mm.z, vv.z);
         w.w = opt_update(G, sc, w.w, gsum.w, mm.w, vv.w);
-#pragma unroll
-        for (int rk = 0; rk < 8; ++rk)
-          if (rk < CS) peer_land[rk][e4] = w;
+        publish_weights(e, w);
         if (p2p_partial && st == a.n_steps - 1)          // this rank's FedAvg term, (w * n_k) / N, for the peers to fetch (C:110-115)
           reinterpret_cast<float4*>(p2p_partial)[e4] =
               make_float4(__fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den), __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den),
@@ -682,7 +728,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
     }
     STAMP(14);
     if (p2p_partial && st == a.n_steps - 1) __threadfence_system();   // my slice of the partial is visible to the peers
-    cluster.sync();   // every CTA holds the complete updated slab in its landing zone
+    cluster.sync();   // every CTA holds the complete updated operand image (bf16 panels + fp32 head)
     if (p2p_partial && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
       // arrival flag A ("my partial is complete") into every peer's buffer; the local evaluation below
       // overlaps its flight over NVLink and the peers' own progress
@@ -690,7 +736,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       st_release_sys_u64(pf + a.p2p->rank, p2p_seq + 1);
     }
     STAMP(15);
-    convert_weights(sm, landing, lay, s);
+    convert_small(sm, landing, lay, s);   // W1 / b1 / b2 from the landing zone (+ proxy fence and block barrier)
     STAMP(16);
   }  // steps
 
