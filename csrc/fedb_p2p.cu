@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
   const int par = (int)(seq & 1);
   const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
   float* my_partial = reinterpret_cast<float*>(R.sym[R.rank] + R.sym_partial_off) + (int64_t)par * R.global_total;
-  int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + par * conf_stride;
+  int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + R.rank) * conf_stride;   // area (parity, source rank)
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
   const int gthreads = gridDim.x * blockDim.x, gtid = blockIdx.x * blockDim.x + tid;
   // Stop flags as they stand for THIS round, taken before the grid barrier: block 0 raises them for
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
     for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += blockDim.x) {
       const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
       const int q = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
-      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[q] + R.sym_conf_off) + par * conf_stride;
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[q] + R.sym_conf_off) + (par * 8 + q) * conf_stride;
       R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
     }
     __syncthreads();

@@ -727,11 +727,13 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       }
     }
     STAMP(14);
-    if (p2p_partial && st == a.n_steps - 1) __threadfence_system();   // my slice of the partial is visible to the peers
     cluster.sync();   // every CTA holds the complete updated operand image (bf16 panels + fp32 head)
     if (p2p_partial && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
       // arrival flag A ("my partial is complete") into every peer's buffer; the local evaluation below
-      // overlaps its flight over NVLink and the peers' own progress
+      // overlaps its flight over NVLink and the peers' own progress.  The cluster barrier ordered every
+      // CTA's partial stores before this thread; the system-scope fence + release store make them
+      // visible to whoever acquires the flag (cumulativity) — no per-thread system fence needed.
+      __threadfence_system();
       uint64_t* pf = reinterpret_cast<uint64_t*>(a.p2p->sym[tid] + a.p2p->sym_flag_off);
       st_release_sys_u64(pf + a.p2p->rank, p2p_seq + 1);
     }
@@ -921,12 +923,17 @@ __device__ void p2p_tail(const TcArgs& a) {
   const long long t0 = clock64();
   const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
-  if (crank == 0) {   // publish this rank's confusion counts, then flag B
-    int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + par * conf_stride;
-    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) my_confx[i] = __ldcg(a.conf + i);
-    __threadfence_system();
+  if (crank == 0) {   // PUSH this rank's confusion counts into every peer's area (parity, my rank), then flag B
+    const int nconf = R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+    for (int i = tid; i < nconf * R.world; i += TC_THREADS) {
+      const int qq = i / nconf, w = i - qq * nconf;
+      reinterpret_cast<int32_t*>(R.sym[qq] + R.sym_conf_off)[(par * 8 + R.rank) * conf_stride + w] = __ldcg(a.conf + w);
+    }
     __syncthreads();
-    if (tid < R.world) st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 8 + R.rank, seq + 1);
+    if (tid < R.world) {
+      __threadfence_system();
+      st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 8 + R.rank, seq + 1);
+    }
   }
   const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
   if (CS == 1 || crank != mrank) {   // ---- aggregation: wait for every peer's partial (flag A), sum in rank order
@@ -961,7 +968,8 @@ __device__ void p2p_tail(const TcArgs& a) {
     for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) {
       const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
       const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
-      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[qq] + R.sym_conf_off) + par * conf_stride;
+      // the counts were pushed into THIS rank's buffer by their owners: a local read, no NVLink round trip
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + qq) * conf_stride;
       R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
     }
     __syncthreads();

@@ -33,7 +33,7 @@ class SymLayout:
 
     @property
     def flag_off(self) -> int:
-        return (self.conf_off + 2 * self.conf_slots * C2 * 4 + 255) // 256 * 256
+        return (self.conf_off + 2 * 8 * self.conf_slots * C2 * 4 + 255) // 256 * 256   # areas (parity, source rank)
 
     @property
     def nbytes(self) -> int:

@@ -107,7 +107,7 @@ typedef struct FedbTile {
 /* Per-rank argument block of the cross-GPU aggregation kernel (fedb_fedavg_p2p).  All pointers are
  * device pointers valid on the launching GPU; sym[q] is rank q's symmetric buffer as mapped into
  * this process (CUDA IPC).  Symmetric buffer layout (bytes): partial[2][global_total] fp32 at
- * sym_partial_off, conf[2][conf_slots][64] int32 at sym_conf_off, flags[8] u64 at sym_flag_off. */
+ * sym_partial_off, conf[2][8 source ranks][conf_slots][64] int32 at sym_conf_off, flags[16] u64 at sym_flag_off. */
 typedef struct FedbP2PRank {
   int32_t rank, world;
   int32_t n_feds, n_groups_local;
