@@ -22,6 +22,8 @@
 // one device: nothing guarantees they are co-resident).
 #include <cooperative_groups.h>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "p2p_common.cuh"
 
@@ -29,7 +31,7 @@ namespace fedb {
 
 constexpr int P2P_THREADS = 256;
 
-__global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* __restrict__ ranks) {
+__global__ void __launch_bounds__(P2P_THREADS, 4) k_fedavg_p2p(const FedbP2PRank* __restrict__ ranks) {
   const FedbP2PRank& R = ranks[blockIdx.y];
   const int tid = threadIdx.x;
   const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
@@ -52,13 +54,24 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
     for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
       const int e = e4 * 4;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int k = 0; k < F.n_clients; ++k) {
-        const FedbGroup& G = R.groups[F.first_group + k];
-        const float4 w = *reinterpret_cast<const float4*>(R.params + G.slab_off + e);
-        acc.x += __fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den);
-        acc.y += __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den);
-        acc.z += __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den);
-        acc.w += __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den);
+      for (int k0 = 0; k0 < F.n_clients; k0 += 4) {   // 4 clients' loads in flight; accumulation stays in client order
+        float4 w[4];
+        float num[4], den[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (k0 + u < F.n_clients) {
+            const FedbGroup& G = R.groups[F.first_group + k0 + u];
+            w[u] = __ldcs(reinterpret_cast<const float4*>(R.params + G.slab_off + e));
+            num[u] = G.agg_num; den[u] = G.agg_den;
+          }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (k0 + u < F.n_clients) {
+            acc.x += __fdiv_rn(__fmul_rn(w[u].x, num[u]), den[u]);
+            acc.y += __fdiv_rn(__fmul_rn(w[u].y, num[u]), den[u]);
+            acc.z += __fdiv_rn(__fmul_rn(w[u].z, num[u]), den[u]);
+            acc.w += __fdiv_rn(__fmul_rn(w[u].w, num[u]), den[u]);
+          }
       }
       *reinterpret_cast<float4*>(my_partial + F.global_off + e) = acc;
     }
@@ -103,9 +116,16 @@ __global__ void __launch_bounds__(P2P_THREADS) k_fedavg_p2p(const FedbP2PRank* _
         acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
       }
       *reinterpret_cast<float4*>(R.global + F.global_off + e) = acc;
-      if (R.write_back)
+      if (R.write_back) {
         for (int k = 0; k < F.n_clients; ++k)
-          *reinterpret_cast<float4*>(R.params + R.groups[F.first_group + k].slab_off + e) = acc;
+          __stcs(reinterpret_cast<float4*>(R.params + R.groups[F.first_group + k].slab_off + e), acc);
+        if (R.shadow) {   // wide path: every client's bf16 GEMM operands follow the averaged weights in the same pass
+          const __nv_bfloat162 lo2 = __floats2bfloat162_rn(acc.x, acc.y), hi2 = __floats2bfloat162_rn(acc.z, acc.w);
+          const uint2 pk = make_uint2(*reinterpret_cast<const uint32_t*>(&lo2), *reinterpret_cast<const uint32_t*>(&hi2));
+          for (int k = 0; k < F.n_clients; ++k)
+            __stcs(reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(R.shadow) + R.groups[F.first_group + k].slab_off + e), pk);
+        }
+      }
     }
   }
   // ---- metrics + early stop, identically on every rank (C:165-192) --------------------------------

@@ -251,7 +251,7 @@ P2PRANK_DTYPE = np.dtype([
     ("fed_state", "u8"), ("params", "u8"), ("global", "u8"), ("conf", "u8"), ("conf_all", "u8"), ("hist_local", "u8"),
     ("hist_global", "u8"), ("conf_src_rank", "u8"), ("conf_src_slot", "u8"), ("sym", "u8", (8,)),
     ("sym_partial_off", "i8"), ("sym_conf_off", "i8"), ("sym_flag_off", "i8"), ("seq", "u8"), ("bar", "u8"), ("err", "u8"),
-    ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"), ("begin_next", "i4"), ("pad_", "i4"),
+    ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"), ("begin_next", "i4"), ("pad_", "i4"), ("shadow", "u8"),
 ], align=True)
 
 

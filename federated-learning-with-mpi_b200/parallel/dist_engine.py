@@ -127,7 +127,8 @@ class DistFedEngine(FedEngine):
         self.sym_ptrs = list(sym_ptrs)
         self.rank_record = p2p.make_rank_record(self, rank, world, self.sym_layout, self.sym_ptrs, self.feds_global, self.conf_all,
                                                 self.hist_local, self.hist_global, self.src_rank, self.src_slot, self.seq,
-                                                self.bar, self.err, g_total, timeout_s)
+                                                self.bar, self.err, g_total, timeout_s,
+                                                shadow=(self.wide.shadow if self.precision_name == "bf16_wide" else None))
         self.rank_dev = K.upload_table(self.rank_record, d)
         self.p2p_blocks = p2p.blocks_for(self.tb.max_slab)
 
@@ -159,9 +160,7 @@ class DistFedEngine(FedEngine):
         return FedEngine.launches_per_round.fget(self)
 
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> None:
-        p2p.launch(self.rank_dev, 1, self.p2p_blocks)   # begin_next is baked into the rank record (always on)
-        if self.precision_name == "bf16_wide":
-            self.wide.refresh_shadow()                  # averaged fp32 weights -> bf16 GEMM operands
+        p2p.launch(self.rank_dev, 1, self.p2p_blocks)   # begin_next (and the bf16 shadow of the wide path) are baked into the rank record
 
     @property
     def kernel_names(self) -> List[str]:

@@ -88,7 +88,8 @@ class SymmetricBuffer:
 def make_rank_record(eng, rank: int, world: int, lay: SymLayout, sym_ptrs: Sequence[int], feds_global: torch.Tensor,
                      conf_all: torch.Tensor, hist_local: torch.Tensor, hist_global: torch.Tensor, src_rank: torch.Tensor,
                      src_slot: torch.Tensor, seq: torch.Tensor, bar: torch.Tensor, err: torch.Tensor, n_groups_total: int,
-                     timeout_s: float = 5.0, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True) -> np.ndarray:
+                     timeout_s: float = 5.0, write_back: bool = True, do_metrics: bool = True, begin_next: bool = True,
+                     shadow: Optional[torch.Tensor] = None) -> np.ndarray:
     if eng.n_feds > 256:
         raise ValueError("the cross-GPU aggregation kernel handles at most 256 federations per launch")
     r = np.zeros(1, dtype=nat.P2PRANK_DTYPE)
@@ -106,6 +107,7 @@ def make_rank_record(eng, rank: int, world: int, lay: SymLayout, sym_ptrs: Seque
     r["seq"], r["bar"], r["err"] = seq.data_ptr(), bar.data_ptr(), err.data_ptr()
     r["timeout_cycles"] = int(timeout_s * 1.9e9)
     r["write_back"], r["do_metrics"], r["begin_next"] = int(write_back), int(do_metrics), int(begin_next)
+    r["shadow"] = 0 if shadow is None else shadow.data_ptr()
     return r
 
 
@@ -120,4 +122,4 @@ def blocks_for(max_slab: int, n_ranks_here: int = 1, sm_count: int = 148) -> int
     """Enough 256-thread blocks to cover the largest slab once, bounded so the cooperative grid
     (blocks_x * emulated ranks) stays co-resident."""
     want = max(1, (max_slab // 4 + 255) // 256)
-    return int(max(1, min(want, sm_count // max(1, n_ranks_here))))
+    return int(max(1, min(want, (4 * sm_count) // max(1, n_ranks_here))))   # 4 co-resident blocks per SM (launch bounds)

@@ -133,6 +133,7 @@ typedef struct FedbP2PRank {
   int64_t timeout_cycles;
   int32_t write_back, do_metrics;
   int32_t begin_next, pad_;
+  void* shadow;                         /* optional bf16 arena (params layout) that receives the averaged weights too */
 } FedbP2PRank;
 
 /* Grouped tensor-core GEMM of the wide-MLP path (csrc/fedb_gemm.cu).  blockIdx.z = group (client);
