@@ -1,0 +1,282 @@
+// K2d, 2-CTA variant: the grouped GEMM of fedb_gemm_tma.cu on CTA PAIRS (thread-block cluster of 2,
+// tcgen05 cta_group::2).  One pair computes a 256 x 256 output tile: each CTA owns 128 rows of A and
+// HALF of the B tile, a single tcgen05.mma.cta_group::2 issued by the leader CTA reads both halves and
+// writes 128 x 256 fp32 accumulators into EACH CTA's tensor memory.  Per SM and k-step that is 32 KB of
+// operands for 128 x 256 x 64 MACs — twice the arithmetic intensity of the single-CTA 128 x 128 tile,
+// which is what the L2 -> SM operand stream limits.  Both CTAs' TMA loads complete on the LEADER's
+// "full" barrier (cp.async.bulk.tensor ... cta_group::2); tcgen05.commit ... multicast::cluster releases
+// the stage in both CTAs.  Epilogues and arguments are those of fedb_gemm_tma (FedbGemm).
+// Requires M % 256 == 0 and N % 256 == 0; other shapes use the single-CTA kernel.
+#include <cooperative_groups.h>
+#include <cuda.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace fedb {
+namespace {
+
+constexpr int T_THREADS = 192;
+constexpr int BM = 128, BN = 256, BNH = 128, BK = 64;      // per CTA: 128 rows x 256 cols; it loads 128 of the 256 B columns
+constexpr int STAGES = 3;
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BNH * BK * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;             // 32 KB per CTA
+constexpr int TILE_LD = 128 + 4;                           // the epilogue stages 128 columns at a time
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;                // shared::cluster address of the same offset in the pair's even CTA
+constexpr long long WAIT_LIMIT = 20000000ll;               // ~10 ms: a protocol bug must end the kernel, not hang the GPU
+
+__device__ __forceinline__ void tma2_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t leader_bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
+      "l"(map), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "l"(0x1000000000000000ull)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mma2_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void commit2(uint64_t* bar) {   // arrive on the barrier at this offset in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(tc::smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// bounded wait: returns false on timeout
+__device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity) {
+  const long long t0 = clock64();
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(done)
+        : "r"(tc::smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!done && clock64() - t0 > WAIT_LIMIT) return false;
+  } while (!done);
+  return true;
+}
+
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T_THREADS)
+k_gemm_tma2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, FedbGemm p, int* __restrict__ err) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ StepScalars sc_s;
+  __shared__ FedbGroup Gs;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();          // 0 = leader (issues the MMAs)
+  const uint32_t raw = tc::smem_u32(smem_raw);
+  const uint32_t sm = (raw + 1023u) & ~1023u;
+  uint8_t* smp = smem_raw + (sm - raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = blockIdx.z, m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int nh0 = n0 + rank * BNH;                     // the half of the B tile this CTA loads
+  const int KT = (p.K + BK - 1) / BK;
+
+  if (p.epilogue == FEDB_GEMM_WGRAD_OPT && tid < (int)(sizeof(FedbGroup) / 4))
+    reinterpret_cast<int32_t*>(&Gs)[tid] = reinterpret_cast<const int32_t*>(p.groups + g)[tid];
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(&tmem_slot)), "n"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    tc::mbar_init(&done_bar, 1);
+    tc::fence_mbar_init();
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  tc::tc_fence_before();
+  cluster.sync();                                       // the peer's barriers exist before anything signals them
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (p.epilogue == FEDB_GEMM_WGRAD_OPT && tid == 64) sc_s = step_scalars_fast(Gs, p.step[g]);
+  bool ok = true;
+
+  if (warp == 0) {
+    // ===== TMA producer (one lane per CTA): own A rows + own half of B; completion on the LEADER's full barrier =====
+    if (lane == 0) {
+      for (int kt = 0; kt < KT && ok; ++kt) {
+        const int s = kt % STAGES, k0 = kt * BK;
+        if (kt >= STAGES) ok = mbar_wait_to(&empty_bar[s], ((kt / STAGES) - 1) & 1);
+        if (!ok) break;
+        if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+        const uint32_t lbar = tc::smem_u32(&full_bar[s]) & PEER_MASK;
+        const uint32_t a_dst = sm + s * STAGE_BYTES, b_dst = a_dst + A_BYTES;
+        if (!p.a_mn) tma2_load_3d(a_dst, &tmA, k0, m0, g, lbar);
+        else { tma2_load_3d(a_dst, &tmA, m0, k0, g, lbar); tma2_load_3d(a_dst + BK * 128, &tmA, m0 + 64, k0, g, lbar); }
+        if (!p.b_mn) tma2_load_3d(b_dst, &tmB, k0, nh0, g, lbar);
+        else { tma2_load_3d(b_dst, &tmB, nh0, k0, g, lbar); tma2_load_3d(b_dst + BK * 128, &tmB, nh0 + 64, k0, g, lbar); }
+      }
+    }
+  } else if (warp == 1 && rank == 0) {
+    // ===== MMA issuer: one lane of the leader CTA drives both SMs' tensor cores =====
+    if (lane == 0) {
+      const uint32_t idesc = tc::make_idesc_bf16(2 * BM, BN, p.a_mn != 0, p.b_mn != 0);
+      for (int kt = 0; kt < KT && ok; ++kt) {
+        const int s = kt % STAGES;
+        ok = mbar_wait_to(&full_bar[s], (kt / STAGES) & 1);
+        if (!ok) break;
+        tc::tc_fence_after();
+        const int k_cnt = min(BK, p.K - kt * BK);
+        const uint32_t a_base = sm + s * STAGE_BYTES, b_base = a_base + A_BYTES;
+        for (int k = 0; k < (k_cnt >> 4); ++k) {
+          const uint64_t ad = p.a_mn ? tc::make_desc(a_base + 2048 * k, BK * 128, 1024) : tc::make_desc(a_base + 32 * k, 0, 1024);
+          const uint64_t bd = p.b_mn ? tc::make_desc(b_base + 2048 * k, BK * 128, 1024) : tc::make_desc(b_base + 32 * k, 0, 1024);
+          mma2_bf16(tmem, ad, bd, idesc, (kt | k) != 0);
+        }
+        commit2(&empty_bar[s]);
+        if (kt == KT - 1) commit2(&done_bar);
+      }
+    }
+  }
+  // ===== epilogue: each CTA drains its own 128 x 256 accumulator, 128 columns at a time =====
+  float* tile = reinterpret_cast<float*>(smp);
+  if (warp >= 2) ok = mbar_wait_to(&done_bar, 0);
+  if (!ok && err) *err = FEDB_E_TIMEOUT;
+  tc::tc_fence_after();
+  for (int hc = 0; hc < 2; ++hc) {
+    const int nc0 = n0 + hc * 128;                     // global column base of this pass
+    if (warp >= 2) {
+      const int quad = warp & 3;
+      const int r = quad * 32 + lane;
+      const uint32_t tl = tmem + ((uint32_t)(quad * 32) << 16) + hc * 128;
+      for (int c0 = 0; c0 < 128; c0 += 16) {
+        float v[16];
+        tc::tmem_ld16(tl + c0, v);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4)
+          *reinterpret_cast<float4*>(tile + r * TILE_LD + c0 + 4 * q4) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+      }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (p.epilogue == FEDB_GEMM_WGRAD_OPT) {
+      const StepScalars sc = sc_s;
+      const bool use_v = p.Vel && Gs.opt != FEDB_OPT_SGD;
+      const bool use_m = p.Mom && !(Gs.opt == FEDB_OPT_SGD && Gs.momentum == 0.f);
+      const float l2 = Gs.alpha * p.l2_scale;
+      constexpr int NW = T_THREADS / 32, UR = 4;
+      for (int r0 = warp; r0 < BM; r0 += NW * UR) {
+        size_t off[UR];
+        float4 w[UR], mm[UR], vv[UR];
+#pragma unroll
+        for (int u = 0; u < UR; ++u) {
+          const int r = r0 + u * NW;
+          off[u] = (size_t)g * p.w_group_stride + (size_t)(m0 + r) * p.ldw + nc0 + 4 * lane;
+          if (r < BM) {
+            w[u] = *reinterpret_cast<const float4*>(p.W + off[u]);
+            mm[u] = use_m ? *reinterpret_cast<const float4*>(p.Mom + off[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            vv[u] = use_v ? *reinterpret_cast<const float4*>(p.Vel + off[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UR; ++u) {
+          const int r = r0 + u * NW;
+          if (r < BM) {
+            const float4 gr = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+            float4 x = w[u];
+            x.x = opt_update(Gs, sc, x.x, fmaf(l2, x.x, gr.x), mm[u].x, vv[u].x);
+            x.y = opt_update(Gs, sc, x.y, fmaf(l2, x.y, gr.y), mm[u].y, vv[u].y);
+            x.z = opt_update(Gs, sc, x.z, fmaf(l2, x.z, gr.z), mm[u].z, vv[u].z);
+            x.w = opt_update(Gs, sc, x.w, fmaf(l2, x.w, gr.w), mm[u].w, vv[u].w);
+            *reinterpret_cast<float4*>(p.W + off[u]) = x;
+            if (use_m) *reinterpret_cast<float4*>(p.Mom + off[u]) = mm[u];
+            if (use_v) *reinterpret_cast<float4*>(p.Vel + off[u]) = vv[u];
+            if (p.Wsh) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.Wsh) + off[u]) = make_uint2(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w));
+          }
+        }
+      }
+    } else if (p.epilogue == FEDB_GEMM_STORE_F32) {
+      for (int r = warp; r < BM; r += T_THREADS / 32)
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)g * p.c_group_stride + (size_t)(m0 + r) * p.ldc + nc0 + 4 * lane) =
+            *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+    } else {
+      const float4 bias4 = (p.epilogue == FEDB_GEMM_FWD_BIAS_RELU && p.bias)
+                               ? *reinterpret_cast<const float4*>(p.bias + (size_t)g * p.bias_group_stride + nc0 + 4 * lane)
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = warp; r < BM; r += T_THREADS / 32) {
+        float4 v = *reinterpret_cast<const float4*>(tile + r * TILE_LD + 4 * lane);
+        if (p.epilogue == FEDB_GEMM_FWD_BIAS_RELU) {
+          v.x = fmaxf(v.x + bias4.x, 0.f); v.y = fmaxf(v.y + bias4.y, 0.f); v.z = fmaxf(v.z + bias4.z, 0.f); v.w = fmaxf(v.w + bias4.w, 0.f);
+        } else {
+          const uint2 a = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.act) + (size_t)g * p.act_group_stride +
+                                                          (size_t)(m0 + r) * p.ldact + nc0 + 4 * lane);
+          const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(&a);
+          v.x = __bfloat162float(ab[0]) > 0.f ? v.x : 0.f; v.y = __bfloat162float(ab[1]) > 0.f ? v.y : 0.f;
+          v.z = __bfloat162float(ab[2]) > 0.f ? v.z : 0.f; v.w = __bfloat162float(ab[3]) > 0.f ? v.w : 0.f;
+        }
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)g * p.c_group_stride + (size_t)(m0 + r) * p.ldc + nc0 + 4 * lane) =
+            make_uint2(tc::pack_bf16(v.x, v.y), tc::pack_bf16(v.z, v.w));
+      }
+    }
+    __syncthreads();                                   // the staging tile is rewritten by the next pass
+  }
+  tc::tc_fence_before();
+  cluster.sync();                                      // both CTAs are done with tensor memory
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(256) : "memory");
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_map2(CUtensorMap* m, const void* base, int64_t inner, int64_t rows, int64_t groups, int64_t ld, int64_t group_stride,
+                     int box_rows) {
+  static EncodeTiledFn2 enc = nullptr;
+  if (!enc) {
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      enc = (EncodeTiledFn2)fp;
+  }
+  if (!enc) return set_err(FEDB_E_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)groups};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)(groups > 1 ? group_stride : ld * rows) * 2};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_err(FEDB_E_CUDA, "cuTensorMapEncodeTiled failed");
+  return FEDB_OK;
+}
+
+// err_dev: optional device int that receives FEDB_E_TIMEOUT if the pair's barrier protocol stalls.
+extern "C" int fedb_gemm_tma2(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, void* stream) {
+  const FedbGemm& p = *args_host;
+  FEDB_REQUIRE(n_groups > 0 && p.M % 256 == 0 && p.N % 256 == 0 && p.K % 16 == 0 && p.K > 0, "2-CTA GEMM needs M % 256 == 0, N % 256 == 0, K % 16 == 0");
+  FEDB_REQUIRE(p.lda % 8 == 0 && p.ldb % 8 == 0 && p.a_group_stride % 8 == 0 && p.b_group_stride % 8 == 0, "strides must be multiples of 8 elements");
+  alignas(64) CUtensorMap tmA, tmB;
+  if (int rc = p.a_mn ? make_map2(&tmA, p.A, p.M, p.K, n_groups, p.lda, p.a_group_stride, 64)
+                      : make_map2(&tmA, p.A, p.K, p.M, n_groups, p.lda, p.a_group_stride, 128)) return rc;
+  if (int rc = p.b_mn ? make_map2(&tmB, p.B, p.N, p.K, n_groups, p.ldb, p.b_group_stride, 64)
+                      : make_map2(&tmB, p.B, p.K, p.N, n_groups, p.ldb, p.b_group_stride, 128)) return rc;
+  static bool attr_set = false;
+  const int tile_bytes = BM * TILE_LD * 4;
+  const int smem = (STAGES * STAGE_BYTES > tile_bytes ? STAGES * STAGE_BYTES : tile_bytes) + 1024;
+  if (!attr_set) {
+    FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_gemm_tma2, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  dim3 grid(p.M / BM, p.N / BN, n_groups);            // grid.x is even: consecutive x form the CTA pair
+  k_gemm_tma2<<<grid, T_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, p, err_dev);
+  FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}

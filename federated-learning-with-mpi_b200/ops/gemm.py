@@ -39,6 +39,26 @@ def gemm(n_groups: int, M: int, N: int, K_: int, A, a_stride: int, lda: int, a_m
     a["act"], a["act_group_stride"], a["ldact"] = _p(act), act_stride, ldact
     a["W"], a["Mom"], a["Vel"], a["Wsh"], a["w_group_stride"], a["ldw"], a["l2_scale"] = _p(W), _p(Mom), _p(Vel), _p(Wsh), w_stride, ldw, l2_scale
     a["groups"], a["step"] = _p(groups), _p(step)
-    fn = lib.fedb_gemm_tc if os.environ.get("FEDB200_GEMM", "tma") == "cpasync" else lib.fedb_gemm_tma
-    nat.check(fn(a.ctypes.data, n_groups, nat.cuda_stream()))
+    mode = os.environ.get("FEDB200_GEMM", "tma")
+    if mode == "tma2" and M % 256 == 0 and N % 256 == 0:      # CTA-pair kernel (csrc/fedb_gemm_tma2.cu)
+        nat.check(lib.fedb_gemm_tma2(a.ctypes.data, n_groups, _p(_pair_err()), nat.cuda_stream()))
+    else:
+        fn = lib.fedb_gemm_tc if mode == "cpasync" else lib.fedb_gemm_tma
+        nat.check(fn(a.ctypes.data, n_groups, nat.cuda_stream()))
     K._count()
+
+
+_PAIR_ERR: Optional[torch.Tensor] = None
+
+
+def _pair_err() -> torch.Tensor:
+    """Device flag the CTA-pair kernel sets if its barrier protocol stalls (see ``pair_status``)."""
+    global _PAIR_ERR
+    if _PAIR_ERR is None:
+        _PAIR_ERR = torch.zeros(1, dtype=torch.int32, device="cuda")
+    return _PAIR_ERR
+
+
+def pair_status() -> int:
+    """0 if every CTA-pair GEMM so far completed its pipeline; a FEDB_E_* code otherwise (synchronises)."""
+    return 0 if _PAIR_ERR is None else int(_PAIR_ERR.item())

@@ -260,6 +260,9 @@ int32_t fedb_gemm_args_size(void);
 int fedb_gemm_tc(const FedbGemm* args_host, int32_t n_groups, void* stream);   /* cp.async-fed variant (fallback) */
 /* Main variant: TMA-fed (3-D tensor maps encoded per call), warp-specialised, coalesced epilogues. */
 int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream);
+/* CTA-pair variant (cluster of 2, tcgen05 cta_group::2, 256 x 256 tile per pair).  Needs M % 256 == 0 and
+ * N % 256 == 0.  err_dev (optional device int32) receives FEDB_E_TIMEOUT if a pair's pipeline stalls. */
+int fedb_gemm_tma2(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, void* stream);
 
 /* Wide-MLP path, the kernels around fedb_gemm_tc (csrc/fedb_wide.cu).  A* / dZ are bf16 [G][B][d]
  * activation buffers (B rows per client, padded shards must be equal-sized); dz is fp32 [G][B][8]. */

@@ -80,3 +80,37 @@ def test_wgrad_store_and_fused_sgd(G, B, IN, OUT):
     torch.cuda.synchronize()
     _close(W, W0 - 0.5 * want, 5e-3)
     assert torch.equal(Wsh, W.to(torch.bfloat16))
+
+
+# ---------------------------------------------------------------------------------------------------
+# CTA-pair kernel (csrc/fedb_gemm_tma2.cu): 256 x 256 tiles on tcgen05 cta_group::2
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("G,B,IN,OUT", [(1, 256, 64, 256), (2, 512, 192, 256), (2, 256, 4096, 512)])
+def test_pair_forward_dgrad_wgrad(G, B, IN, OUT, monkeypatch):
+    from fedb200.ops import gemm as gm
+    monkeypatch.setenv("FEDB200_GEMM", "tma2")
+    g = torch.Generator(device="cuda").manual_seed(5)
+    X = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
+    W = _bf(torch.randn(G, OUT, IN, device="cuda", generator=g) / IN ** 0.5)
+    b = torch.randn(G, OUT, device="cuda", generator=g)
+    Y = torch.empty(G, B, OUT, device="cuda", dtype=torch.bfloat16)
+    gm.gemm(G, B, OUT, IN, X, B * IN, IN, False, W, OUT * IN, IN, False, gm.FWD_BIAS_RELU, C=Y, c_stride=B * OUT, ldc=OUT,
+            bias=b, bias_stride=OUT)
+    torch.cuda.synchronize()
+    assert gm.pair_status() == 0
+    _close(Y, torch.relu(torch.einsum("gbi,goi->gbo", X.float(), W.float()) + b[:, None, :]))
+    if IN % 256 == 0:
+        # dgrad: dX[B][IN] = dZ[B][OUT] @ W[OUT][IN], W as an MN-major operand
+        dZ = _bf(torch.randn(G, B, OUT, device="cuda", generator=g))
+        dX = torch.empty(G, B, IN, device="cuda", dtype=torch.bfloat16)
+        gm.gemm(G, B, IN, OUT, dZ, B * OUT, OUT, False, W, OUT * IN, IN, True, gm.DGRAD_MASK, C=dX, c_stride=B * IN, ldc=IN,
+                act=X, act_stride=B * IN, ldact=IN)
+        torch.cuda.synchronize()
+        assert gm.pair_status() == 0
+        _close(dX, torch.einsum("gbo,goi->gbi", dZ.float(), W.float()) * (X.float() > 0))
+        # wgrad: dW[OUT][IN] = dZ^T @ X, both operands MN-major
+        dW = torch.empty(G, OUT, IN, device="cuda", dtype=torch.float32)
+        gm.gemm(G, OUT, IN, B, dZ, B * OUT, OUT, True, X, B * IN, IN, True, gm.STORE_F32, C=dW, c_stride=OUT * IN, ldc=IN)
+        torch.cuda.synchronize()
+        assert gm.pair_status() == 0
+        _close(dW, torch.einsum("gbo,gbi->goi", dZ.float(), X.float()), 5e-3)
