@@ -168,6 +168,34 @@ __device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalar
   }
 }
 
+// Register-resident form of the optimizer for streaming epilogues (the wgrad GEMMs): the group's constants are
+// read once per thread, the two Adam flavours share one expression (sklearn's has inv_sqrt_bc2 = 1), and the square
+// root / quotient use the SFU approximations (2 ulp) — the update feeds bf16 tensor-core operands, and a lone CTA's
+// warps must keep up with their SM's share of HBM while the neighbouring CTA runs its main loop.
+struct OptRegs {
+  float b1, omb1, b2, omb2, eps, lr_eff, isb2, mom, l2;
+  int adam, nesterov;
+};
+__device__ __forceinline__ OptRegs opt_regs(const FedbGroup& G, const StepScalars& sc, float l2) {
+  OptRegs o;
+  o.b1 = G.beta1; o.omb1 = 1.f - G.beta1; o.b2 = G.beta2; o.omb2 = 1.f - G.beta2; o.eps = G.eps;
+  o.lr_eff = sc.lr_eff; o.isb2 = sc.inv_sqrt_bc2; o.mom = G.momentum; o.l2 = l2;
+  o.adam = G.opt != FEDB_OPT_SGD; o.nesterov = G.nesterov;
+  return o;
+}
+__device__ __forceinline__ float opt_update_fast(const OptRegs& o, float w, float g, float& m, float& v) {
+  g = fmaf(o.l2, w, g);
+  if (o.adam) {
+    m = fmaf(o.b1, m, o.omb1 * g);
+    v = fmaf(o.b2, v, o.omb2 * g * g);
+    float sq;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
+    return fmaf(-o.lr_eff, __fdividef(m, fmaf(sq, o.isb2, o.eps)), w);
+  }
+  m = fmaf(o.mom, m, -o.lr_eff * g);
+  return w + (o.nesterov ? fmaf(o.mom, m, -o.lr_eff * g) : m);
+}
+
 
 // ---- metrics from confusion counts + early stop (K3/K5), shared by the aggregation kernels ---------
 // a / b to ~1e-14 relative: single-precision quotient plus one double-precision residual correction.

@@ -39,8 +39,14 @@ def gemm(n_groups: int, M: int, N: int, K_: int, A, a_stride: int, lda: int, a_m
     a["act"], a["act_group_stride"], a["ldact"] = _p(act), act_stride, ldact
     a["W"], a["Mom"], a["Vel"], a["Wsh"], a["w_group_stride"], a["ldw"], a["l2_scale"] = _p(W), _p(Mom), _p(Vel), _p(Wsh), w_stride, ldw, l2_scale
     a["groups"], a["step"] = _p(groups), _p(step)
-    mode = os.environ.get("FEDB200_GEMM", "tma")
-    if mode == "tma2" and M % 256 == 0 and N % 256 == 0:      # CTA-pair kernel (csrc/fedb_gemm_tma2.cu)
+    # FEDB200_GEMM: "auto" (default) = CTA-pair kernel when M and N are multiples of 256, else the single-CTA TMA kernel;
+    # "tma" = always single-CTA; "cpasync" = the cp.async fallback.
+    mode = os.environ.get("FEDB200_GEMM", "auto")
+    if mode == "auto":
+        mode = "tma2"
+    if mode == "tma2" and M % 256 == 0 and N % 256 == 0 and PROF is not None:
+        nat.check(lib.fedb_gemm_tma2_prof(a.ctypes.data, n_groups, _p(_pair_err()), _p(PROF), nat.cuda_stream()))
+    elif mode == "tma2" and M % 256 == 0 and N % 256 == 0:      # CTA-pair kernel (csrc/fedb_gemm_tma2.cu)
         nat.check(lib.fedb_gemm_tma2(a.ctypes.data, n_groups, _p(_pair_err()), nat.cuda_stream()))
     else:
         fn = lib.fedb_gemm_tc if mode == "cpasync" else lib.fedb_gemm_tma
@@ -49,6 +55,7 @@ def gemm(n_groups: int, M: int, N: int, K_: int, A, a_stride: int, lda: int, a_m
 
 
 _PAIR_ERR: Optional[torch.Tensor] = None
+PROF: Optional[torch.Tensor] = None      # set to an int64 device tensor of 8 * n_ctas to collect phase stamps (tools/gemm_timeline.py)
 
 
 def _pair_err() -> torch.Tensor:

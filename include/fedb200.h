@@ -263,6 +263,9 @@ int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream);
 /* CTA-pair variant (cluster of 2, tcgen05 cta_group::2, 256 x 256 tile per pair).  Needs M % 256 == 0 and
  * N % 256 == 0.  err_dev (optional device int32) receives FEDB_E_TIMEOUT if a pair's pipeline stalls. */
 int fedb_gemm_tma2(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, void* stream);
+/* Same launch with per-CTA phase stamps: prof_dev = 8 uint64 per CTA in grid order (x, y, group): globaltimer ns at
+ * start, main loop done, pass 0 staged, pass 0 done, pass 1 staged, end; then the SM id (tools/gemm_timeline.py). */
+int fedb_gemm_tma2_prof(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, uint64_t* prof_dev, void* stream);
 
 /* Wide-MLP path, the kernels around fedb_gemm_tc (csrc/fedb_wide.cu).  A* / dZ are bf16 [G][B][d]
  * activation buffers (B rows per client, padded shards must be equal-sized); dz is fp32 [G][B][8]. */

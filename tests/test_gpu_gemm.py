@@ -7,9 +7,10 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["tma", "cpasync"], autouse=True)
+@pytest.fixture(params=["auto", "tma", "cpasync"], autouse=True)
 def _variant(request, monkeypatch):
-    """Every case runs on both the TMA-fed main kernel and the cp.async fallback."""
+    """Every case runs on the default dispatch (CTA-pair kernel where the shape allows), the single-CTA TMA kernel and the
+    cp.async fallback."""
     monkeypatch.setenv("FEDB200_GEMM", request.param)
 
 
