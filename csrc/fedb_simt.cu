@@ -572,27 +572,60 @@ k_fedavg(const FedbGroup* __restrict__ groups, const FedbFed* __restrict__ feds,
   const int f = blockIdx.y;
   const FedbFed& F = feds[f];
   if (state[f].stop) return;
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q * 4 < F.slab_size) {
-    const int e = q * 4;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int k = 0; k < F.n_clients; ++k) {
-      const FedbGroup& G = groups[F.first_group + k];
-      const float4 w = *reinterpret_cast<const float4*>(params + G.slab_off + e);
-      // reference arithmetic, term by term: (w * n_k) / N, accumulated in client order
-      acc.x += __fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den);
-      acc.y += __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den);
-      acc.z += __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den);
-      acc.w += __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den);
+  // The clients' slab offsets and weights are staged in shared memory a chunk at a time, so that the loop over clients
+  // is plain address arithmetic and eight independent 16-byte loads are in flight per thread: with 128 clients the
+  // pass is a pure stream (4 bytes read, 4 + 2 written per client and element) and wants all the memory parallelism
+  // it can get.  The arithmetic and its order are unchanged.
+  constexpr int CH = 128, UR = 8;
+  __shared__ long long s_off[CH];
+  __shared__ float s_num[CH], s_den[CH];
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const bool active = e < F.slab_size;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int k0 = 0; k0 < F.n_clients; k0 += CH) {
+    const int cnt = min(CH, F.n_clients - k0);
+    if (k0) __syncthreads();
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+      const FedbGroup& G = groups[F.first_group + k0 + i];
+      s_off[i] = G.slab_off; s_num[i] = G.agg_num; s_den[i] = G.agg_den;
     }
+    __syncthreads();
+    if (active) {
+      for (int k = 0; k < cnt; k += UR) {
+        float4 w[UR];
+#pragma unroll
+        for (int u = 0; u < UR; ++u)
+          if (k + u < cnt) w[u] = __ldcs(reinterpret_cast<const float4*>(params + s_off[k + u] + e));
+#pragma unroll
+        for (int u = 0; u < UR; ++u)
+          if (k + u < cnt) {
+            // reference arithmetic, term by term: (w * n_k) / N, accumulated in client order
+            const float num = s_num[k + u], den = s_den[k + u];
+            acc.x += __fdiv_rn(__fmul_rn(w[u].x, num), den);
+            acc.y += __fdiv_rn(__fmul_rn(w[u].y, num), den);
+            acc.z += __fdiv_rn(__fmul_rn(w[u].z, num), den);
+            acc.w += __fdiv_rn(__fmul_rn(w[u].w, num), den);
+          }
+      }
+    }
+  }
+  if (active) {
     *reinterpret_cast<float4*>(global + F.global_off + e) = acc;
     if (write_back) {
-      for (int k = 0; k < F.n_clients; ++k)
-        *reinterpret_cast<float4*>(params + groups[F.first_group + k].slab_off + e) = acc;
-      if (shadow) {   // wide path: the bf16 GEMM operands of every client follow the averaged weights in the same pass
-        const __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
-        const uint2 pk = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
-        for (int k = 0; k < F.n_clients; ++k) *reinterpret_cast<uint2*>(shadow + groups[F.first_group + k].slab_off + e) = pk;
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
+      const uint2 pk = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+      if (F.n_clients <= CH) {                         // offsets are still staged
+        for (int k = 0; k < F.n_clients; ++k) {
+          *reinterpret_cast<float4*>(params + s_off[k] + e) = acc;
+          // wide path: the bf16 GEMM operands of every client follow the averaged weights in the same pass
+          if (shadow) *reinterpret_cast<uint2*>(shadow + s_off[k] + e) = pk;
+        }
+      } else {
+        for (int k = 0; k < F.n_clients; ++k) {
+          const long long off = groups[F.first_group + k].slab_off;
+          *reinterpret_cast<float4*>(params + off + e) = acc;
+          if (shadow) *reinterpret_cast<uint2*>(shadow + off + e) = pk;
+        }
       }
     }
   }

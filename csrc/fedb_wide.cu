@@ -120,9 +120,11 @@ k_wide_head_fwd(const FedbGroup* __restrict__ groups, const float* __restrict__ 
   loss_rows[(size_t)g * B + r] = loss;
 }
 
-// One thread per column j of the last hidden layer: dW_head[c][j] = sum_r dz[r][c] A[r][j] -> optimizer;
-// dZ[r][j] = (A[r][j] > 0) * sum_c dz[r][c] W_head[c][j] (with the weights as they were before the update).
-// Block (0, g) additionally updates the head bias and reduces the loss.  grid = (d / 256, G).
+// Head weight gradient + optimizer and dZ of the last hidden layer.  A block owns 128 columns j of that layer (a lane
+// owns 4 consecutive ones, so a warp moves a 256-byte row segment per access) and its 8 warps split the rows:
+//   dZ[r][j] = (A[r][j] > 0) * sum_c dz[r][c] W_head[c][j]      (weights as they were before the update; row-independent)
+//   dW_head[c][j] = sum_r dz[r][c] A[r][j]                       (per-warp partial sums, combined in warp order)
+// Block (0, g) additionally updates the head bias and reduces the loss.  grid = (ceil(d / 128), G).
 __global__ void __launch_bounds__(256)
 k_wide_head_bwd(const FedbGroup* __restrict__ groups, float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
                 __nv_bfloat16* __restrict__ shadow, const __nv_bfloat16* __restrict__ A, int B, int d, const float* __restrict__ dz,
@@ -135,47 +137,80 @@ k_wide_head_bwd(const FedbGroup* __restrict__ groups, float* __restrict__ params
   const SlabLayout lay = slab_layout(G.dims, L);
   const size_t wbase = (size_t)G.slab_off + lay.w_off[L - 1], bbase = (size_t)G.slab_off + lay.b_off[L - 1];
   const int ldw = lay.ld[L - 1];
-  __shared__ float dz_s[64][FEDB_MAX_CLASSES];
+  constexpr int RCH = 256;                                   // rows of dz staged at a time
+  __shared__ float dz_s[RCH][FEDB_MAX_CLASSES];
+  __shared__ float red[8][FEDB_MAX_CLASSES][128];            // per-warp partial head gradients
   __shared__ StepScalars sc_s;
   if (threadIdx.x == 0) sc_s = step_scalars_fast(G, step[g]);
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  float wj[FEDB_MAX_CLASSES], gw[FEDB_MAX_CLASSES];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j0 = blockIdx.x * 128 + lane * 4;                // d is a multiple of 4 (padded layer width)
+  const bool col_ok = j0 < d;
+  float wj[FEDB_MAX_CLASSES][4], gw[FEDB_MAX_CLASSES][4];
 #pragma unroll
-  for (int c = 0; c < FEDB_MAX_CLASSES; ++c) { wj[c] = (c < C && j < d) ? params[wbase + (size_t)c * ldw + j] : 0.f; gw[c] = 0.f; }
+  for (int c = 0; c < FEDB_MAX_CLASSES; ++c) {
+    const float4 q = (c < C && col_ok) ? *reinterpret_cast<const float4*>(params + wbase + (size_t)c * ldw + j0) : make_float4(0.f, 0.f, 0.f, 0.f);
+    wj[c][0] = q.x; wj[c][1] = q.y; wj[c][2] = q.z; wj[c][3] = q.w;
+    gw[c][0] = gw[c][1] = gw[c][2] = gw[c][3] = 0.f;
+  }
   const __nv_bfloat16* Ag = A + (size_t)g * B * d;
   __nv_bfloat16* dZg = dZ + (size_t)g * B * d;
-  for (int r0 = 0; r0 < B; r0 += 64) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < 64 * FEDB_MAX_CLASSES; i += 256)
+  for (int r0 = 0; r0 < B; r0 += RCH) {
+    if (r0) __syncthreads();
+    for (int i = threadIdx.x; i < RCH * FEDB_MAX_CLASSES; i += 256)
       dz_s[i / FEDB_MAX_CLASSES][i % FEDB_MAX_CLASSES] = (r0 + i / FEDB_MAX_CLASSES < B) ? dz[((size_t)g * B + r0) * FEDB_MAX_CLASSES + i] : 0.f;
     __syncthreads();
-    if (j < d) {
-#pragma unroll 4
-      for (int rr = 0; rr < 64 && r0 + rr < B; ++rr) {
-        const float a = __bfloat162float(Ag[(size_t)(r0 + rr) * d + j]);
-        float da = 0.f;
+    if (col_ok) {
+      const int rend = min(RCH, B - r0);
+      for (int rr = warp; rr < rend; rr += 32) {             // 4 rows of this warp in flight
+        uint2 q[4];
 #pragma unroll
-        for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
-          if (c < C) { gw[c] = fmaf(dz_s[rr][c], a, gw[c]); da = fmaf(dz_s[rr][c], wj[c], da); }
-        dZg[(size_t)(r0 + rr) * d + j] = __float2bfloat16_rn(a > 0.f ? da : 0.f);
+        for (int u = 0; u < 4; ++u)
+          if (rr + 8 * u < rend) q[u] = __ldcs(reinterpret_cast<const uint2*>(Ag + (size_t)(r0 + rr + 8 * u) * d + j0));
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (rr + 8 * u < rend) {
+            const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(&q[u]);
+            float a[4], da[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = __bfloat162float(ab[i]);
+#pragma unroll
+            for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
+              if (c < C) {
+                const float z = dz_s[rr + 8 * u][c];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { gw[c][i] = fmaf(z, a[i], gw[c][i]); da[i] = fmaf(z, wj[c][i], da[i]); }
+              }
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(a[0] > 0.f ? da[0] : 0.f, a[1] > 0.f ? da[1] : 0.f);
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(a[2] > 0.f ? da[2] : 0.f, a[3] > 0.f ? da[3] : 0.f);
+            *reinterpret_cast<uint2*>(dZg + (size_t)(r0 + rr + 8 * u) * d + j0) =
+                make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+          }
+        }
       }
     }
   }
+#pragma unroll
+  for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
+    if (c < C) *reinterpret_cast<float4*>(&red[warp][c][lane * 4]) = make_float4(gw[c][0], gw[c][1], gw[c][2], gw[c][3]);
+  __syncthreads();
   const StepScalars sc = sc_s;
   const bool use_v = v && G.opt != FEDB_OPT_SGD;
-  if (j < d) {
-    const float l2 = G.alpha / (float)G.n_rows;
+  for (int t = threadIdx.x; t < C * 128; t += 256) {
+    const int c = t >> 7, col = t & 127, j = blockIdx.x * 128 + col;
+    if (j < d) {
+      float gsum = 0.f;
 #pragma unroll
-    for (int c = 0; c < FEDB_MAX_CLASSES; ++c)
-      if (c < C) {
-        const size_t o = wbase + (size_t)c * ldw + j;
-        float mm = m ? m[o] : 0.f, vv = use_v ? v[o] : 0.f;
-        const float w = opt_update(G, sc, wj[c], fmaf(l2, wj[c], gw[c]), mm, vv);
-        params[o] = w;
-        if (m) m[o] = mm;
-        if (use_v) v[o] = vv;
-        if (shadow) shadow[o] = __float2bfloat16_rn(w);
-      }
+      for (int w = 0; w < 8; ++w) gsum += red[w][c][col];
+      const float l2 = G.alpha / (float)G.n_rows;
+      const size_t o = wbase + (size_t)c * ldw + j;
+      const float w0 = params[o];
+      float mm = m ? m[o] : 0.f, vv = use_v ? v[o] : 0.f;
+      const float w = opt_update(G, sc, w0, fmaf(l2, w0, gsum), mm, vv);
+      params[o] = w;
+      if (m) m[o] = mm;
+      if (use_v) v[o] = vv;
+      if (shadow) shadow[o] = __float2bfloat16_rn(w);
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // head bias + loss: one warp, fixed order
     const int lane = threadIdx.x;
@@ -265,7 +300,7 @@ extern "C" int fedb_wide_head_fwd(const FedbGroup* groups, int32_t n_groups, con
 extern "C" int fedb_wide_head_bwd(const FedbGroup* groups, int32_t n_groups, float* params, float* m, float* v, void* shadow,
                                   const void* A, int32_t B, int32_t d, const float* dz, const float* loss_rows, void* dZ,
                                   const int32_t* step, const FedbFedState* fed_state, float* loss_out, void* stream) {
-  dim3 grid((d + 255) / 256, n_groups);
+  dim3 grid((d + 127) / 128, n_groups);
   k_wide_head_bwd<<<grid, 256, 0, (cudaStream_t)stream>>>(groups, params, m, v, (__nv_bfloat16*)shadow, (const __nv_bfloat16*)A, B, d, dz,
                                                           loss_rows, (__nv_bfloat16*)dZ, step, fed_state, loss_out);
   FEDB_LAUNCH_OK();
