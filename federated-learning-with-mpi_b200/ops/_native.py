@@ -237,6 +237,7 @@ OPTIONAL_SIGS = {
     "fedb_gemm_tc": ([_P, _I32, _P], _I32),
     "fedb_gemm_tma": ([_P, _I32, _P], _I32),
     "fedb_gemm_tma2": ([_P, _I32, _P, _P], _I32),
+    "fedb_gemm_tma2p": ([_P, _I32, _P, _P], _I32),
     "fedb_gemm_tma2_prof": ([_P, _I32, _P, _P, _P], _I32),
     "fedb_p2p_rank_size": ([], _I32),
     "fedb_fedavg_p2p": ([_P, _I32, _I32, _P], _I32),

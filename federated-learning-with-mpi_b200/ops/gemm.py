@@ -39,14 +39,17 @@ def gemm(n_groups: int, M: int, N: int, K_: int, A, a_stride: int, lda: int, a_m
     a["act"], a["act_group_stride"], a["ldact"] = _p(act), act_stride, ldact
     a["W"], a["Mom"], a["Vel"], a["Wsh"], a["w_group_stride"], a["ldw"], a["l2_scale"] = _p(W), _p(Mom), _p(Vel), _p(Wsh), w_stride, ldw, l2_scale
     a["groups"], a["step"] = _p(groups), _p(step)
-    # FEDB200_GEMM: "auto" (default) = CTA-pair kernel when M and N are multiples of 256, else the single-CTA TMA kernel;
-    # "tma" = always single-CTA; "cpasync" = the cp.async fallback.
+    # FEDB200_GEMM: "auto" (default) = CTA-pair kernels when M and N are multiples of 256 (the persistent one for the
+    # HBM-bound optimizer epilogue, the one-tile-per-cluster one otherwise: measured faster for fwd/dgrad), else the
+    # single-CTA TMA kernel; "tma2" / "tma2p" / "tma" force one kernel; "cpasync" = the cp.async fallback.
     mode = os.environ.get("FEDB200_GEMM", "auto")
     if mode == "auto":
-        mode = "tma2"
-    if mode == "tma2" and M % 256 == 0 and N % 256 == 0 and PROF is not None:
+        mode = "tma2p" if epilogue == WGRAD_OPT else "tma2"
+    if mode == "tma2p" and M % 256 == 0 and N % 256 == 0:       # persistent CTA-pair kernel (csrc/fedb_gemm_tma2p.cu)
+        nat.check(lib.fedb_gemm_tma2p(a.ctypes.data, n_groups, _p(_pair_err()), nat.cuda_stream()))
+    elif mode in ("tma2", "tma2p") and M % 256 == 0 and N % 256 == 0 and PROF is not None:
         nat.check(lib.fedb_gemm_tma2_prof(a.ctypes.data, n_groups, _p(_pair_err()), _p(PROF), nat.cuda_stream()))
-    elif mode == "tma2" and M % 256 == 0 and N % 256 == 0:      # CTA-pair kernel (csrc/fedb_gemm_tma2.cu)
+    elif mode in ("tma2", "tma2p") and M % 256 == 0 and N % 256 == 0:      # CTA-pair kernel (csrc/fedb_gemm_tma2.cu)
         nat.check(lib.fedb_gemm_tma2(a.ctypes.data, n_groups, _p(_pair_err()), nat.cuda_stream()))
     else:
         fn = lib.fedb_gemm_tc if mode == "cpasync" else lib.fedb_gemm_tma

@@ -263,6 +263,9 @@ int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream);
 /* CTA-pair variant (cluster of 2, tcgen05 cta_group::2, 256 x 256 tile per pair).  Needs M % 256 == 0 and
  * N % 256 == 0.  err_dev (optional device int32) receives FEDB_E_TIMEOUT if a pair's pipeline stalls. */
 int fedb_gemm_tma2(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, void* stream);
+/* Persistent CTA-pair variant: one cluster per SM pair walks a static tile list, two accumulators in tensor memory, so
+ * the epilogue of a tile overlaps the main loop of the next.  Same requirements and err_dev as fedb_gemm_tma2. */
+int fedb_gemm_tma2p(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, void* stream);
 /* Same launch with per-CTA phase stamps: prof_dev = 8 uint64 per CTA in grid order (x, y, group): globaltimer ns at
  * start, main loop done, pass 0 staged, pass 0 done, pass 1 staged, end; then the SM id (tools/gemm_timeline.py). */
 int fedb_gemm_tma2_prof(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, uint64_t* prof_dev, void* stream);

@@ -86,10 +86,11 @@ def test_wgrad_store_and_fused_sgd(G, B, IN, OUT):
 # ---------------------------------------------------------------------------------------------------
 # CTA-pair kernel (csrc/fedb_gemm_tma2.cu): 256 x 256 tiles on tcgen05 cta_group::2
 # ---------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("G,B,IN,OUT", [(1, 256, 64, 256), (2, 512, 192, 256), (2, 256, 4096, 512)])
-def test_pair_forward_dgrad_wgrad(G, B, IN, OUT, monkeypatch):
+@pytest.mark.parametrize("mode", ["tma2", "tma2p"])
+@pytest.mark.parametrize("G,B,IN,OUT", [(1, 256, 64, 256), (2, 512, 192, 256), (2, 256, 4096, 512), (5, 1024, 1024, 2048)])
+def test_pair_forward_dgrad_wgrad(G, B, IN, OUT, mode, monkeypatch):
     from fedb200.ops import gemm as gm
-    monkeypatch.setenv("FEDB200_GEMM", "tma2")
+    monkeypatch.setenv("FEDB200_GEMM", mode)
     g = torch.Generator(device="cuda").manual_seed(5)
     X = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
     W = _bf(torch.randn(G, OUT, IN, device="cuda", generator=g) / IN ** 0.5)
@@ -115,3 +116,51 @@ def test_pair_forward_dgrad_wgrad(G, B, IN, OUT, monkeypatch):
         torch.cuda.synchronize()
         assert gm.pair_status() == 0
         _close(dW, torch.einsum("gbo,gbi->goi", dZ.float(), X.float()), 5e-3)
+
+
+@pytest.mark.parametrize("mode", ["auto", "tma", "tma2", "tma2p"])
+@pytest.mark.parametrize("opt", ["adam", "sgd_momentum", "sgd"])
+def test_wgrad_fused_optimizer_matches_torch(mode, opt, monkeypatch):
+    """dW = dZ^T @ A with the optimizer in the epilogue, several groups with different steps, against fp32 torch math
+    (torch-style Adam: m, v, bias correction; SGD with sklearn-style momentum buffer)."""
+    from fedb200.ops import gemm as gm
+    from fedb200.ops import _native as nat
+    monkeypatch.setenv("FEDB200_GEMM", mode)
+    G, B, IN, OUT = 3, 512, 512, 256
+    g = torch.Generator(device="cuda").manual_seed(7)
+    dZ = _bf(torch.randn(G, B, OUT, device="cuda", generator=g) / B ** 0.5)
+    A = _bf(torch.randn(G, B, IN, device="cuda", generator=g))
+    groups = np.zeros(G, dtype=nat.GROUP_DTYPE)
+    lr, b1, b2, eps, mom = 1e-2, 0.9, 0.999, 1e-8, 0.9
+    if opt == "adam":
+        groups["opt"], groups["beta1"], groups["beta2"], groups["eps"] = nat.OPT_IDS["adam_torch"], b1, b2, eps
+    else:
+        groups["opt"], groups["momentum"] = nat.OPT_IDS["sgd"], (mom if opt == "sgd_momentum" else 0.0)
+    groups["lr"], groups["lr_gamma"] = lr, 1.0
+    d_groups = torch.from_numpy(groups.view(np.uint8).copy()).cuda()
+    steps = torch.tensor([1, 2, 5], dtype=torch.int32, device="cuda")
+    W = torch.randn(G, OUT, IN, device="cuda", generator=g)
+    Mo = torch.randn(G, OUT, IN, device="cuda", generator=g) * 0.01
+    Ve = torch.rand(G, OUT, IN, device="cuda", generator=g) * 1e-3
+    W0, M0, V0 = W.clone(), Mo.clone(), Ve.clone()
+    Wsh = torch.zeros(G, OUT, IN, device="cuda", dtype=torch.bfloat16)
+    gm.gemm(G, OUT, IN, B, dZ, B * OUT, OUT, True, A, B * IN, IN, True, gm.WGRAD_OPT, W=W, Mom=Mo, Vel=Ve, Wsh=Wsh,
+            w_stride=OUT * IN, ldw=IN, groups=d_groups, step=steps)
+    torch.cuda.synchronize()
+    assert gm.pair_status() == 0
+    dW = torch.einsum("gbo,gbi->goi", dZ.float(), A.float())
+    t = steps.float()[:, None, None]
+    if opt == "adam":
+        m = b1 * M0 + (1 - b1) * dW
+        v = b2 * V0 + (1 - b2) * dW * dW
+        want = W0 - (lr / (1 - b1 ** t)) * m / (v.sqrt() / (1 - b2 ** t).sqrt() + eps)
+        assert torch.allclose(Mo, m, rtol=1e-3, atol=1e-5) and torch.allclose(Ve, v, rtol=1e-3, atol=1e-7)
+    elif opt == "sgd_momentum":
+        m = mom * M0 - lr * dW
+        want = W0 + m
+        assert torch.allclose(Mo, m, rtol=1e-3, atol=1e-5)
+    else:
+        want = W0 - lr * dW
+        assert torch.equal(Mo, M0) and torch.equal(Ve, V0)          # plain SGD leaves the state arrays alone
+    assert torch.allclose(W, want, rtol=1e-3, atol=2e-4), (W - want).abs().max().item()
+    assert torch.allclose(Wsh.float(), W, rtol=1e-2, atol=1e-2)
