@@ -93,6 +93,21 @@ def test_eval_confusion_and_fedavg_exact(income):
     assert list(sc["round"]) == list(sg["round"]) == [1, 1]
 
 
+def test_fedavg_exact_with_many_clients(income):
+    """300 clients in one federation: the aggregation kernel stages client descriptors 128 at a time; the result must
+    still be the reference's term-by-term sum in client order, bit for bit."""
+    problems = [FedProblem.custom(14, 2, make_shards("contiguous", 3000, 300), hidden=(9,), patience=0),
+                FedProblem.custom(14, 2, make_shards("contiguous", 3000, 128), hidden=(5, 6), patience=0, weighting="uniform")]
+    cpu, gpu = _pair(problems, income, 3000, max_rounds=2)
+    for e in (cpu, gpu):
+        from fedb200.ops import kernels as K
+        K.round_begin(e.tb, e.fed_state, e.conf)
+        e.enqueue_eval_local()
+        e.enqueue_aggregate()
+    torch.cuda.synchronize()
+    assert torch.equal(cpu.global_, gpu.global_.cpu()) and torch.equal(cpu.params, gpu.params.cpu())
+
+
 def test_shuffle_bitwise(income_nomean):
     cpu, gpu = _pair(_problems(income_nomean, "sklearn"), income_nomean, 3000, max_rounds=2)
     from fedb200.ops import kernels as K
