@@ -178,9 +178,13 @@ def run_ours(args):
                           "rounds_per_sec": K / (ms_warm / 1e3)},
         "e2e": {"value": samples * K / (ms_e2e / 1e3), "unit": "client-samples/s", "ms_per_step": ms_e2e / K,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "how": "per step: cudaMemcpyAsync of the step's rows + labels from pinned host memory, the round, the federation "
-                       "state (stop flag + 4 global metrics) stored by the round kernel into mapped pinned host memory (a memcpy node "
-                       "on the non-fused paths), stream synchronise, host reads it"},
+                "h2d_by": "round kernel (loads from pinned host memory, written through to the device copy)"
+                          if eng.pulls_host_inputs() else "copy engine (cudaMemcpyAsync nodes in the step's graph)",
+                "how": "per step, through FedEngine.step_e2e: the step's rows + labels travel from pinned host memory to the device "
+                       "(single-launch rounds: the round kernel reads them over the host link, one 64-byte request per row, and writes "
+                       "them through to the device-resident X / y; other paths: two cudaMemcpyAsync nodes), the round runs, the "
+                       "federation state (stop flag + 4 global metrics) is stored by the round kernel into mapped pinned host memory "
+                       "(a memcpy node on the non-fused paths), stream synchronise, host reads it"},
         "gpu_launches": K * eng.launches_per_round, "launches_per_step": eng.launches_per_round,
         "kernels": eng.kernel_names, "clocks": clk.summary(),
         "final_global_accuracy_train_shards": float(hist["last"][0][0]), "rounds_run": int(hist["rounds"][0]),

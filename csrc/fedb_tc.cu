@@ -59,6 +59,10 @@ struct TcArgs {
   const FedbGroup* groups;
   const float* X;
   const int32_t* y;
+  // optional: this step's inputs in (pinned, device-visible) host memory, same layout as X / y.  The kernel then performs the
+  // host-to-device copy itself: rows are read over the host link and written through to X / y on their way to the X panel.
+  const float* x_host;
+  const int32_t* y_host;
   const int32_t* idx;
   float* params;
   float* m;
@@ -174,6 +178,54 @@ __device__ __forceinline__ RowRegs fetch_row(const TcArgs& a, int64_t pos, bool 
     r.q[1] = __ldg(src + 1);
     r.label = __ldg(a.y + row);
   }
+  return r;
+}
+// Host-input mode (TcArgs::x_host): the tile's rows come from pinned host memory.  Over the host link the request size is
+// what matters (tools/host_pull_bench.cu: 1000 rows as 2 x 16 B per thread 13.7 us, as one 64-byte request per row 6.2 us,
+// against 3.7 us from device memory), so four lanes fetch one whole row with a single instruction: warp w takes tile rows
+// 16w .. 16w+15, two instructions of eight rows.  host_deliver() later passes the rows through shared memory (the H1 panel,
+// idle at that point) to the threads that own them, and writes them through to the device-resident X / y, 64 bytes per row.
+struct HostRegs {
+  float4 v[2];
+  int grow[2], label[2];   // global row index (-1: none) and, on the row's first lane, its label
+};
+__device__ __forceinline__ HostRegs host_fetch(const TcArgs& a, int64_t pos0, int nvalid, int tid) {
+  HostRegs h;
+  const int w = tid >> 5, lane = tid & 31, c = lane & 3;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int rl = 16 * w + 8 * j + (lane >> 2);
+    h.v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    h.grow[j] = -1;
+    h.label[j] = 0;
+    if (rl < nvalid) {
+      const int row = __ldg(a.idx + pos0 + rl);
+      h.grow[j] = row;
+      h.v[j] = __ldcv(reinterpret_cast<const float4*>(a.x_host + (size_t)row * a.ldx) + c);
+      if (c == 0) h.label[j] = __ldcv(a.y_host + row);
+    }
+  }
+  return h;
+}
+__device__ __forceinline__ RowRegs host_deliver(uint8_t* sm, const TcArgs& a, const HostRegs& h, int tid, int row, int half) {
+  float* stage = reinterpret_cast<float*>(sm + SM_H1);           // 128 rows x 16 floats, then 128 labels
+  int* stage_lab = reinterpret_cast<int*>(sm + SM_H1 + TC_ROWS * 64);
+  const int w = tid >> 5, lane = tid & 31, c = lane & 3;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int rl = 16 * w + 8 * j + (lane >> 2);
+    *reinterpret_cast<float4*>(stage + rl * 16 + 4 * c) = h.v[j];
+    if (c == 0) stage_lab[rl] = h.label[j];
+    if (h.grow[j] >= 0) {
+      *(reinterpret_cast<float4*>(const_cast<float*>(a.X) + (size_t)h.grow[j] * a.ldx) + c) = h.v[j];
+      if (c == 0) const_cast<int32_t*>(a.y)[h.grow[j]] = h.label[j];
+    }
+  }
+  __syncthreads();
+  RowRegs r;
+  r.q[0] = *reinterpret_cast<const float4*>(stage + row * 16 + 8 * half);
+  r.q[1] = *reinterpret_cast<const float4*>(stage + row * 16 + 8 * half + 4);
+  r.label = stage_lab[row];
   return r;
 }
 __device__ __forceinline__ int store_row(uint8_t* sm, const RowRegs& r, bool valid, const Shape& s, int row, int half) {
@@ -370,7 +422,10 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
 #define STAMP(i) do { if (a.prof && blockIdx.x == 0 && tid == 0) a.prof[i] = clock64(); } while (0)
   STAMP(0);
   // first tile's row: issue its loads before the weight conversion so both latencies overlap
-  RowRegs rr = fetch_row(a, G.idx_off + b0 + q * TC_ROWS + row, q < ntiles && q * TC_ROWS + row < nb, half);
+  RowRegs rr;
+  HostRegs hr;
+  if (a.x_host) hr = host_fetch(a, G.idx_off + b0 + q * TC_ROWS, q < ntiles ? min(TC_ROWS, nb - q * TC_ROWS) : 0, tid);
+  else rr = fetch_row(a, G.idx_off + b0 + q * TC_ROWS + row, q < ntiles && q * TC_ROWS + row < nb, half);
   tc::mbar_wait(&wbar, wph); wph ^= 1;
   convert_weights(sm, landing, lay, s);
   STAMP(1);
@@ -400,7 +455,12 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       const bool acc = my_tiles > 0;
       const int r = tile * TC_ROWS + row;
       const bool valid = r < nb;
-      if (my_tiles > 0 || st > 0) rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+      if (a.x_host) {
+        if (my_tiles > 0 || st > 0) hr = host_fetch(a, G.idx_off + b0 + tile * TC_ROWS, min(TC_ROWS, nb - tile * TC_ROWS), tid);
+        rr = host_deliver(sm, a, hr, tid, row, half);
+      } else if (my_tiles > 0 || st > 0) {
+        rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+      }
       const int label = store_row(sm, rr, valid, s, row, half);
       handoff();
       STAMP(2);
@@ -753,7 +813,12 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
       if (ntiles <= CS && a.n_steps > 0) {
         label = rr.label;   // single tile per CTA: the X panel from the training step is still in place
       } else {
-        rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+        if (a.x_host) {
+          hr = host_fetch(a, G.idx_off + b0 + tile * TC_ROWS, min(TC_ROWS, nb - tile * TC_ROWS), tid);
+          rr = host_deliver(sm, a, hr, tid, row, half);
+        } else {
+          rr = fetch_row(a, G.idx_off + b0 + r, valid, half);
+        }
         label = store_row(sm, rr, valid, s, row, half);
       }
       handoff();
@@ -1094,12 +1159,15 @@ extern "C" int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t 
 // The whole round of a multi-GPU federation with ONE resident client per rank in one launch per rank:
 // local steps + (partial published, flag raised) + local evaluation + cross-GPU aggregation over NVLink
 // peer memory + metrics + early stop (see p2p_tail).  rank_dev: this rank's FedbP2PRank record.
-extern "C" int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
-                                 const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
-                                 FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
-                                 const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream) {
+extern "C" int fedb_round_tc_p2p_hostin(const FedbGroup* groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                                        const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m,
+                                        float* v, int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out,
+                                        int32_t* conf, float* scratch, int32_t n_steps, const FedbP2PRank* rank_dev,
+                                        FedbFedState* state_mirror, void* stream) {
   FEDB_REQUIRE(rank_dev != nullptr, "rank record required");
+  FEDB_REQUIRE((x_host == nullptr) == (y_host == nullptr), "x_host and y_host come together");
   TcArgs a{};
+  a.x_host = x_host; a.y_host = y_host;
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
   a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
   a.n_steps = n_steps; a.do_eval = 1; a.prof = nullptr; a.tail_mode = 2; a.n_groups = 1; a.n_feds = 1; a.p2p = rank_dev;
@@ -1107,14 +1175,44 @@ extern "C" int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, 
   return launch_tc(a, 1, cluster_size, stream);
 }
 
+extern "C" int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float* X, int32_t ldx, const int32_t* y,
+                                 const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
+                                 FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
+                                 const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream) {
+  return fedb_round_tc_p2p_hostin(groups, cluster_size, const_cast<float*>(X), ldx, const_cast<int32_t*>(y), nullptr, nullptr, idx, params,
+                                  m, v, step, active, fed_state, loss_out, conf, scratch, n_steps, rank_dev, state_mirror, stream);
+}
+
+extern "C" int fedb_round_tc_hostin(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                                    const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v,
+                                    int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                                    float* scratch, int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global,
+                                    float* hist_local, float* hist_global, int32_t conf_ints, uint32_t* tail_count,
+                                    FedbFedState* state_mirror, long long* prof, void* stream);
+
 extern "C" int fedb_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
                                   const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                                   const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                                   int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
                                   float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror,
                                   long long* prof, void* stream) {
+  return fedb_round_tc_hostin(groups, n_groups, cluster_size, const_cast<float*>(X), ldx, const_cast<int32_t*>(y), nullptr, nullptr, idx,
+                              params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps, feds, n_feds, global, hist_local,
+                              hist_global, conf_ints, tail_count, state_mirror, prof, stream);
+}
+
+// fedb_round_tc with this step's inputs taken from pinned host memory by the kernel itself (x_host / y_host: device-visible
+// addresses of host arrays laid out like X / y; rows are written through to X / y).  Both null: identical to fedb_round_tc.
+extern "C" int fedb_round_tc_hostin(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                                    const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v,
+                                    int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                                    float* scratch, int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global,
+                                    float* hist_local, float* hist_global, int32_t conf_ints, uint32_t* tail_count,
+                                    FedbFedState* state_mirror, long long* prof, void* stream) {
   FEDB_REQUIRE(feds && fed_state && global && tail_count && n_feds > 0, "bad tail arguments");
+  FEDB_REQUIRE((x_host == nullptr) == (y_host == nullptr), "x_host and y_host come together");
   TcArgs a{};
+  a.x_host = x_host; a.y_host = y_host;
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
   a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
   a.n_steps = n_steps; a.do_eval = 1; a.prof = prof;

@@ -13,6 +13,8 @@ sklearn-style "fit until the loss stalls" local training (S:101, H:91) is `fit_l
 """
 from __future__ import annotations
 
+import os
+
 import math
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
@@ -212,6 +214,7 @@ class FedEngine:
         self.tail_count = z(1, torch.int32)
         # mapped pinned host copy of the federation state: the fused round kernels store their result there too
         self._state_pinned = torch.zeros(self.fed_state.numel(), dtype=torch.uint8).pin_memory() if d.type == "cuda" else None
+        self._e2e_cache: Dict = {}   # (x_host ptr, y_host ptr) -> (graph replay, stream sync, result view, buffers kept alive)
 
     def _ensure_wide(self):
         if getattr(self, "_wide_pending", False):
@@ -282,17 +285,20 @@ class FedEngine:
                 and self.params_total <= self.FUSED_TAIL_MAX_FLOATS and self.n_feds <= 256
                 and max(p.n_clients for p in self.problems) <= 32)
 
-    def enqueue_round(self) -> None:
+    def enqueue_round(self, host_inputs=None) -> None:
         """The custom script's round (C:130-201): local step(s), local eval, metrics, FedAvg (+ the next
         round's begin bookkeeping).  Requires :meth:`prime` once before the first round.  On the
-        tensor-core path with a small arena this is ONE launch (fedb_round_tc)."""
+        tensor-core path with a small arena this is ONE launch (fedb_round_tc).  ``host_inputs`` =
+        (x_host, y_host) pinned tensors (single-launch rounds only, see :meth:`pulls_host_inputs`): the
+        kernel copies the step's rows from host memory itself."""
         if self._fused_round_ok():
             from ..ops import tc
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
                         self.fed_state, self.loss, self.conf, self.scratch, E, self.global_, self.hist_local, self.hist_global,
-                        self.tail_count, state_mirror=self._state_pinned)
+                        self.tail_count, state_mirror=self._state_pinned, host_inputs=host_inputs)
             return
+        assert host_inputs is None, "host inputs are pulled by the single-launch round only"
         if not self._begin_is_fused():
             self.enqueue_round_begin()
         with trace.span("fedb200.local_train_eval"):
@@ -542,8 +548,19 @@ class FedEngine:
         state: stop flag + the four global metrics) back to the host.  Returns the
         ``FedbFedState`` records.  This mirrors what the reference does every round
         (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic.
-        On CUDA the two uploads, the round and the read-back are ONE graph launch (captured per
-        pair of host buffers), followed by one stream synchronisation."""
+        On CUDA the uploads, the round and the read-back are ONE graph launch (captured per
+        pair of host buffers), followed by one stream synchronisation.  When the round is a single
+        launch (:meth:`pulls_host_inputs`) that launch performs the upload itself: the kernel reads the
+        rows it trains on from the pinned buffers over the host link and writes them through to the
+        device-resident X / y — two copy-engine nodes (13 us for 64 KB inside a graph) become ~3 us of
+        loads that overlap the weight staging."""
+        # steady state: everything about this pair of host buffers is cached; the host does a dict lookup, a graph launch and
+        # a stream synchronisation per step (its time between the sync and the next launch is GPU idle time)
+        ent = self._e2e_cache.get((x_host.data_ptr(), y_host.data_ptr())) if self._primed else None
+        if ent is not None:
+            ent[0]()
+            ent[1]()
+            return ent[2]
         self.prime()
         if self.device.type != "cuda":
             self.X[: self.n_train].copy_(x_host)
@@ -552,27 +569,41 @@ class FedEngine:
             return self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
         key = f"e2e:{x_host.data_ptr()}:{y_host.data_ptr()}"
         mirrored = self._result_is_mirrored()   # the round kernel itself writes the result into mapped host memory
+        pull = self.pulls_host_inputs() and x_host.is_pinned() and y_host.is_pinned() \
+            and tuple(x_host.shape) == (self.n_train, self.ldx) and x_host.dtype == torch.float32 and y_host.dtype == torch.int32
 
         def body():
-            self.X[: self.n_train].copy_(x_host, non_blocking=True)
-            self.y[: self.n_train].copy_(y_host, non_blocking=True)
-            self.enqueue_round()
+            if pull:
+                self.enqueue_round(host_inputs=(x_host, y_host))
+            else:
+                self.X[: self.n_train].copy_(x_host, non_blocking=True)
+                self.y[: self.n_train].copy_(y_host, non_blocking=True)
+                self.enqueue_round()
             if not mirrored:
                 self._state_pinned.copy_(self.fed_state, non_blocking=True)
 
+        stream = torch.cuda.current_stream()
+        view = self._state_pinned.numpy().view(nat.FEDSTATE_DTYPE)
         if x_host.is_pinned() and y_host.is_pinned():
             if key + "x1" not in self._graphs:
                 snap = self._snapshot()
                 self._graph(key, body, 1)
                 self._restore(snap)
-            self._graphs[key + "x1"].replay()
+            g = self._graphs[key + "x1"]
+            self._e2e_cache[(x_host.data_ptr(), y_host.data_ptr())] = (g.replay, stream.synchronize, view, x_host, y_host)
+            g.replay()
         else:
             body()
-        torch.cuda.current_stream().synchronize()
-        return self._state_pinned.numpy().view(nat.FEDSTATE_DTYPE)
+        stream.synchronize()
+        return view
 
     def _result_is_mirrored(self) -> bool:
         return self._fused_round_ok()
+
+    def pulls_host_inputs(self) -> bool:
+        """True if :meth:`step_e2e` lets the round kernel read its inputs from pinned host memory
+        (single-launch rounds; FEDB200_E2E_MEMCPY=1 forces the copy-engine path)."""
+        return self._fused_round_ok() and os.environ.get("FEDB200_E2E_MEMCPY") is None
 
     def e2e_bytes(self):
         return self.n_train * self.ldx * 4 + self.n_train * 4, int(self.fed_state.numel())

@@ -106,10 +106,13 @@ def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active,
 
 
 def round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
-             global_, hist_local, hist_global, tail_count, prof=None, state_mirror=None) -> None:
-    """The whole round in one launch (see fedb_round_tc in include/fedb200.h)."""
+             global_, hist_local, hist_global, tail_count, prof=None, state_mirror=None, host_inputs=None) -> None:
+    """The whole round in one launch (see fedb_round_tc / fedb_round_tc_hostin in include/fedb200.h).
+    ``host_inputs`` = (x_host, y_host) pinned tensors: the kernel pulls the step's rows from them itself."""
     lib = nat.lib(required=True)
-    nat.check(lib.fedb_round_tc_prof(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
+    xh, yh = host_inputs if host_inputs is not None else (None, None)
+    nat.check(lib.fedb_round_tc_hostin(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y),
+                                nat.ptr(xh), nat.ptr(yh), nat.ptr(idx),
                                 nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
                                 nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(tb.d_feds), tb.n_feds,
                                 nat.ptr(global_), nat.ptr(hist_local), nat.ptr(hist_global), conf.numel(), nat.ptr(tail_count),
@@ -119,10 +122,11 @@ def round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_s
 
 
 def round_tc_p2p(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
-                 rank_dev, state_mirror=None) -> None:
-    """Multi-GPU round in one launch per rank (one federation, one resident client): fedb_round_tc_p2p."""
+                 rank_dev, state_mirror=None, host_inputs=None) -> None:
+    """Multi-GPU round in one launch per rank (one federation, one resident client): fedb_round_tc_p2p[_hostin]."""
     lib = nat.lib(required=True)
-    nat.check(lib.fedb_round_tc_p2p(nat.ptr(tb.d_groups), cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx),
+    xh, yh = host_inputs if host_inputs is not None else (None, None)
+    nat.check(lib.fedb_round_tc_p2p_hostin(nat.ptr(tb.d_groups), cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(xh), nat.ptr(yh), nat.ptr(idx),
                                     nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
                                     nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(rank_dev), nat.ptr(state_mirror),
                                     nat.cuda_stream()))

@@ -144,13 +144,18 @@ class DistFedEngine(FedEngine):
     def _result_is_mirrored(self) -> bool:
         return self._fused_p2p_ok()
 
-    def enqueue_round(self) -> None:
+    def pulls_host_inputs(self) -> bool:
+        return self._fused_p2p_ok() and os.environ.get("FEDB200_E2E_MEMCPY") is None
+
+    def enqueue_round(self, host_inputs=None) -> None:
         if self._fused_p2p_ok():
             from ..ops import tc
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc_p2p(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
-                            self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, state_mirror=self._state_pinned)
+                            self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, state_mirror=self._state_pinned,
+                            host_inputs=host_inputs)
             return
+        assert host_inputs is None, "host inputs are pulled by the single-launch round only"
         super().enqueue_round()
 
     @property

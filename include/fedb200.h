@@ -292,6 +292,21 @@ int fedb_round_tc_p2p(const FedbGroup* groups, int32_t cluster_size, const float
                       const int32_t* idx, float* params, float* m, float* v, int32_t* step, const int32_t* active,
                       FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch, int32_t n_steps,
                       const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream);
+/* The two single-launch rounds with the step's inputs pulled from pinned host memory by the kernel itself: x_host / y_host are
+ * device-visible addresses of host arrays laid out like X / y (cudaHostAlloc / torch pin_memory under UVA); every row the round
+ * uses is read over the host link, written through to X / y, and fed to the first layer.  This replaces two copy-engine nodes in
+ * front of the round (13 us for 64 KB inside a CUDA graph) by ~3 us of loads that overlap the weight staging.  Both null: the
+ * plain entry points.  prof as in fedb_round_tc_prof (may be null). */
+int fedb_round_tc_hostin(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                         const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v,
+                         int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                         float* scratch, int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
+                         float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror, long long* prof,
+                         void* stream);
+int fedb_round_tc_p2p_hostin(const FedbGroup* groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y, const float* x_host,
+                             const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                             const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
+                             int32_t n_steps, const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream);
 
 /* K1b: one launch per rank per round — local weighted partial sums, cross-GPU arrival flags,
  * peer loads over NVLink of every rank's partial, write-back, metrics and early stop
