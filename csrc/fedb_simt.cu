@@ -11,6 +11,8 @@
 //   k_eval        C:75-83, S:104 (predict) ; counts replace the sklearn metric calls C:85-90
 //   k_fedavg      C:101-120, S:108-122, H:24-46 (aggregation) + C:165-192 (global metrics,
 //                 early stop)
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include <cuda_bf16.h>
 
@@ -51,19 +53,23 @@ __host__ __device__ inline SmemPlan smem_plan(const int32_t* dims, int L) {
 
 // z[j][r] = act(b[j] + sum_k a_in[k][r] * W[j][k]);  W row-major [d_out][ld], pad cols zero.
 // Rows j in [d_out, ru4(d_out)) of a_out are written as 0 (they are the next layer's K pad).
-// WS = weights staged in shared memory (plain loads) vs read through L1 from global (__ldg).
-template <bool WS>
+// WS = where the weights are read from: 1 = staged in shared memory (plain loads), 0 = global memory through the
+// read-only path (__ldg: the weights do not change during the kernel), 2 = global memory, L2-coherent (__ldcg: the
+// persistent fit kernel, whose weights are rewritten by other CTAs between mini-batches).
+template <int WS>
 __device__ __forceinline__ float4 ldw4(const float* p) {
-  if constexpr (WS) return *reinterpret_cast<const float4*>(p);
+  if constexpr (WS == 1) return *reinterpret_cast<const float4*>(p);
+  else if constexpr (WS == 2) return __ldcg(reinterpret_cast<const float4*>(p));
   else return __ldg(reinterpret_cast<const float4*>(p));
 }
-template <bool WS>
+template <int WS>
 __device__ __forceinline__ float ldw1(const float* p) {
-  if constexpr (WS) return *p;
+  if constexpr (WS == 1) return *p;
+  else if constexpr (WS == 2) return __ldcg(p);
   else return __ldg(p);
 }
 
-template <bool WS>
+template <int WS>
 __device__ void layer_forward(const float* __restrict__ W, const float* __restrict__ b, int ld, int d_out,
                               const float* a_in, float* a_out, int act, bool apply_act) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -143,7 +149,7 @@ __device__ void layer_wgrad(const float* dz, const float* a, int d_in_ld, int d_
 }
 
 // dz_prev[k][r] = act'(a_l[k][r]) * sum_j dz[j][r] W[j][k]
-template <bool WS>
+template <int WS>
 __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d_out, const float* dz,
                             const float* a_l, float* dz_prev, int act) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -171,13 +177,14 @@ __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d
 
 // Loads the tile's rows, feature-major, into a0; labels into ylab. Rows >= nvalid replicate
 // the last valid row (finite values; their dz is forced to 0 later).
+template <bool COH = false>   // COH: the row-index array is rewritten during the kernel (per-epoch shuffle of the fit kernel)
 __device__ void load_tile(const float* __restrict__ X, int ldx, const int32_t* __restrict__ y,
-                          const int32_t* __restrict__ idx, int64_t base, int nvalid, int ld0, float* a0,
+                          const int32_t* idx, int64_t base, int nvalid, int ld0, float* a0,
                           int* ylab) {
   const int q4 = ld0 >> 2;
   for (int e = threadIdx.x; e < FEDB_TILE_ROWS * q4; e += blockDim.x) {
     const int r = e / q4, q = e - r * q4;
-    const int row = __ldg(idx + base + min(r, nvalid - 1));
+    const int row = COH ? __ldcg(idx + base + min(r, nvalid - 1)) : __ldg(idx + base + min(r, nvalid - 1));
     const float4 v = __ldg(reinterpret_cast<const float4*>(X + (size_t)row * ldx) + q);
     a0[(4 * q + 0) * LDS + r] = v.x;
     a0[(4 * q + 1) * LDS + r] = v.y;
@@ -185,17 +192,18 @@ __device__ void load_tile(const float* __restrict__ X, int ldx, const int32_t* _
     a0[(4 * q + 3) * LDS + r] = v.w;
   }
   if (threadIdx.x < FEDB_TILE_ROWS) {
-    const int row = __ldg(idx + base + min((int)threadIdx.x, nvalid - 1));
+    const int row = COH ? __ldcg(idx + base + min((int)threadIdx.x, nvalid - 1)) : __ldg(idx + base + min((int)threadIdx.x, nvalid - 1));
     ylab[threadIdx.x] = __ldg(y + row);
   }
 }
 
 // Cooperative, fully coalesced copy of a client's slab into shared memory (one L2 round trip
 // with every thread's loads in flight) so that the layer loops read weights at smem latency.
-__device__ void stage_weights(const float* __restrict__ src, float* dst, int n_floats) {
+template <bool COH = false>
+__device__ void stage_weights(const float* src, float* dst, int n_floats) {
   const float4* s4 = reinterpret_cast<const float4*>(src);
   float4* d4 = reinterpret_cast<float4*>(dst);
-  for (int i = threadIdx.x; i < (n_floats >> 2); i += blockDim.x) d4[i] = __ldg(s4 + i);
+  for (int i = threadIdx.x; i < (n_floats >> 2); i += blockDim.x) d4[i] = COH ? __ldcg(s4 + i) : __ldg(s4 + i);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -293,23 +301,18 @@ __global__ void k_shuffle(const FedbGroup* __restrict__ groups, const int32_t* _
 // ---------------------------------------------------------------------------------------
 // K2 part 1: forward + loss + backward, one 32-row tile per CTA
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NTHREADS)
-k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ tiles, const float* __restrict__ params,
-          const float* __restrict__ X, int ldx, const int32_t* __restrict__ y, const int32_t* __restrict__ idx,
-          int batch, float* __restrict__ scratch, int32_t* __restrict__ step, const int32_t* __restrict__ active,
-          const FedbFedState* __restrict__ fed_state, int smem_floats) {
-  extern __shared__ __align__(16) float smem[];
-  const FedbTile T = tiles[blockIdx.x];
-  const int g = T.owner;
-  const FedbGroup& G = groups[g];
-  if (active && !active[g]) return;
-  if (fed_state && fed_state[G.fed].stop) return;
+// One 32-row tile of one mini-batch of group g: forward, loss, backward; the tile's partial gradients + loss go to its record.
+// COH: parameters / row indices may have been rewritten by other CTAs earlier in this kernel (persistent fit kernel).
+template <bool COH>
+__device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* params, const float* __restrict__ X, int ldx,
+                             const int32_t* __restrict__ y, const int32_t* idx, int batch, float* scratch, int32_t* step,
+                             int smem_floats, float* smem) {
   const int n = G.n_rows;
   const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
   const int b0 = batch * bs;
   if (b0 >= n) return;
   const int nb = min(bs, n - b0);
-  const int r0 = T.tile * FEDB_TILE_ROWS;
+  const int r0 = tile * FEDB_TILE_ROWS;
   if (r0 >= nb) return;
   const int nvalid = min(FEDB_TILE_ROWS, nb - r0);
   const int L = G.n_layers;
@@ -317,23 +320,23 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
   const SmemPlan sp = smem_plan(G.dims, L);
   const bool ws = sp.total_floats + lay.end <= smem_floats;  // weights fit next to the activations
   const float* P = params + G.slab_off;
-  float* rec = scratch + G.scratch_off + (size_t)T.tile * (G.slab_size + FEDB_LOSS_SLOTS);
+  float* rec = scratch + G.scratch_off + (size_t)tile * (G.slab_size + FEDB_LOSS_SLOTS);
   int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
   const int lane = threadIdx.x & 31;
 
-  if (T.tile == 0 && threadIdx.x == 0) step[g] += 1;  // optimizer step counter (t in Adam)
+  if (tile == 0 && threadIdx.x == 0) step[g] += 1;  // optimizer step counter (t in Adam)
 
   if (ws) {
-    stage_weights(P, smem + sp.total_floats, lay.end);
+    stage_weights<COH>(P, smem + sp.total_floats, lay.end);
     P = smem + sp.total_floats;
   }
-  load_tile(X, ldx, y, idx, G.idx_off + b0 + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
+  load_tile<COH>(X, ldx, y, idx, G.idx_off + b0 + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
   __syncthreads();
 
   for (int l = 0; l < L; ++l) {
-    if (ws) layer_forward<true>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+    if (ws) layer_forward<1>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                                 smem + sp.a_off[l + 1], G.act, l + 1 < L);
-    else layer_forward<false>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+    else layer_forward<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                               smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
   }
@@ -379,9 +382,9 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
     const float* dzc = smem + sp.dz_off[cur];
     layer_wgrad(dzc, smem + sp.a_off[l], lay.ld[l], G.dims[l + 1], rec + lay.w_off[l], rec + lay.b_off[l]);
     if (l > 0) {
-      if (ws) layer_dgrad<true>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+      if (ws) layer_dgrad<1>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                                 smem + sp.dz_off[cur ^ 1], G.act);
-      else layer_dgrad<false>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+      else layer_dgrad<COH ? 2 : 0>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                               smem + sp.dz_off[cur ^ 1], G.act);
     }
     __syncthreads();
@@ -389,18 +392,29 @@ k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ til
   }
 }
 
-// ---------------------------------------------------------------------------------------
-// K2 part 2: fixed-order reduction over tiles + L2 + optimizer
-// ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NTHREADS)
-k_reduce_opt(const FedbGroup* __restrict__ groups, float* __restrict__ params, float* __restrict__ m,
-             float* __restrict__ v, const float* __restrict__ scratch, int batch, const int32_t* __restrict__ step,
-             const int32_t* __restrict__ active, const FedbFedState* __restrict__ fed_state,
-             float* __restrict__ loss_out, double* __restrict__ batch_stats, int max_batches) {
-  const int g = blockIdx.y;
+k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ tiles, const float* __restrict__ params,
+          const float* __restrict__ X, int ldx, const int32_t* __restrict__ y, const int32_t* __restrict__ idx,
+          int batch, float* __restrict__ scratch, int32_t* __restrict__ step, const int32_t* __restrict__ active,
+          const FedbFedState* __restrict__ fed_state, int smem_floats) {
+  extern __shared__ __align__(16) float smem[];
+  const FedbTile T = tiles[blockIdx.x];
+  const int g = T.owner;
   const FedbGroup& G = groups[g];
   if (active && !active[g]) return;
   if (fed_state && fed_state[G.fed].stop) return;
+  fwd_bwd_tile<false>(G, g, T.tile, params, X, ldx, y, idx, batch, scratch, step, smem_floats, smem);
+}
+
+// ---------------------------------------------------------------------------------------
+// K2 part 2: fixed-order reduction over tiles + L2 + optimizer
+// ---------------------------------------------------------------------------------------
+// Block `vblock` of `nvblocks` (256 slab float4s each) of group g's reduction + optimizer step for mini-batch `batch`.
+// COH: the gradient records and the step counter were written by other CTAs earlier in this kernel.
+template <bool COH>
+__device__ void reduce_opt_block(const FedbGroup& G, int g, int vblock, int nvblocks, float* params, float* m, float* v,
+                                 const float* scratch, int batch, const int32_t* step, float* loss_out, double* batch_stats,
+                                 int max_batches) {
   const int n = G.n_rows;
   const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
   const int b0 = batch * bs;
@@ -413,19 +427,20 @@ k_reduce_opt(const FedbGroup* __restrict__ groups, float* __restrict__ params, f
 
   __shared__ StepScalars sc_s;
   __shared__ float red[NTHREADS / 32];
-  if (threadIdx.x == 0) sc_s = step_scalars(G, step[g]);
+  if (threadIdx.x == 0) sc_s = step_scalars(G, COH ? __ldcg(step + g) : step[g]);
   __syncthreads();
   const StepScalars sc = sc_s;
 
   float sumsq = 0.f;
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int q = vblock * blockDim.x + threadIdx.x;
   if (q * 4 < lay.end) {
     const int e = q * 4;
     bool is_w = false;
     for (int l = 0; l < G.n_layers; ++l) is_w |= (e >= lay.w_off[l] && e < lay.b_off[l]);
     float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int t = 0; t < ntiles; ++t) {
-      const float4 p = *reinterpret_cast<const float4*>(rec + (size_t)t * stride + e);
+      const float4 p = COH ? __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * stride + e))
+                           : *reinterpret_cast<const float4*>(rec + (size_t)t * stride + e);
       gsum.x += p.x; gsum.y += p.y; gsum.z += p.z; gsum.w += p.w;
     }
     float4 w = *reinterpret_cast<float4*>(params + G.slab_off + e);
@@ -458,32 +473,42 @@ k_reduce_opt(const FedbGroup* __restrict__ groups, float* __restrict__ params, f
       float s = 0.f;
       for (int i = 0; i < NTHREADS / 32; ++i) s += red[i];
       // per (group, batch): slot 0 = data loss sum, slots 1.. = per-block sumsq
-      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + gridDim.x);
-      bsrow[2 + blockIdx.x] = (double)s;
+      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + nvblocks);
+      bsrow[2 + vblock] = (double)s;
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+  if (vblock == 0 && threadIdx.x == 0) {
     float ls = 0.f;
-    for (int t = 0; t < ntiles; ++t) ls += rec[(size_t)t * stride + P];
+    for (int t = 0; t < ntiles; ++t) ls += COH ? __ldcg(rec + (size_t)t * stride + P) : rec[(size_t)t * stride + P];
     if (loss_out) loss_out[g] = ls / (float)nb;
     if (batch_stats) {
-      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + gridDim.x);
+      double* bsrow = batch_stats + ((size_t)g * max_batches + batch) * (2 + nvblocks);
       bsrow[0] = (double)ls;
       bsrow[1] = (double)nb;
     }
   }
 }
 
+__global__ void __launch_bounds__(NTHREADS)
+k_reduce_opt(const FedbGroup* __restrict__ groups, float* __restrict__ params, float* __restrict__ m,
+             float* __restrict__ v, const float* __restrict__ scratch, int batch, const int32_t* __restrict__ step,
+             const int32_t* __restrict__ active, const FedbFedState* __restrict__ fed_state,
+             float* __restrict__ loss_out, double* __restrict__ batch_stats, int max_batches) {
+  const int g = blockIdx.y;
+  const FedbGroup& G = groups[g];
+  if (active && !active[g]) return;
+  if (fed_state && fed_state[G.fed].stop) return;
+  reduce_opt_block<false>(G, g, blockIdx.x, gridDim.x, params, m, v, scratch, batch, step, loss_out, batch_stats, max_batches);
+}
+
 // ---------------------------------------------------------------------------------------
 // sklearn epoch end: loss curve + tol / n_iter_no_change (SK:750-777)
 // ---------------------------------------------------------------------------------------
-__global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, const double* __restrict__ batch_stats,
-                            int max_batches, int nblk, double tol, int n_iter_no_change, int max_iter,
-                            int32_t* __restrict__ active, int32_t* __restrict__ epoch, int32_t* __restrict__ no_improve,
-                            double* __restrict__ best_loss, double* __restrict__ last_loss) {
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n_groups || !active[g]) return;
-  const FedbGroup& G = groups[g];
+// COH: batch_stats rows were written by other CTAs earlier in this kernel
+template <bool COH>
+__device__ void epoch_end_group(const FedbGroup& G, int g, const double* batch_stats, int max_batches, int nblk, double tol,
+                                int n_iter_no_change, int max_iter, int32_t* active, int32_t* epoch, int32_t* no_improve,
+                                double* best_loss, double* last_loss) {
   const int n = G.n_rows;
   const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
   const int nbatches = (n + bs - 1) / bs;
@@ -491,9 +516,9 @@ __global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, 
   for (int b = 0; b < nbatches; ++b) {
     const double* row = batch_stats + ((size_t)g * max_batches + b) * (2 + nblk);
     double ss = 0.0;
-    for (int k = 0; k < nblk; ++k) ss += row[2 + k];
+    for (int k = 0; k < nblk; ++k) ss += COH ? __ldcg(row + 2 + k) : row[2 + k];
     // batch_loss = mean logloss + 0.5*alpha*||W||^2 / n_b ; accumulated += batch_loss * n_b
-    accumulated += row[0] + 0.5 * (double)G.alpha * ss;
+    accumulated += (COH ? __ldcg(row) : row[0]) + 0.5 * (double)G.alpha * ss;
   }
   const double loss = accumulated / (double)n;
   last_loss[g] = loss;
@@ -501,6 +526,84 @@ __global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, 
   if (loss > best_loss[g] - tol) no_improve[g] += 1; else no_improve[g] = 0;
   if (loss < best_loss[g]) best_loss[g] = loss;
   if (no_improve[g] > n_iter_no_change || epoch[g] >= max_iter) active[g] = 0;
+}
+
+__global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, const double* __restrict__ batch_stats,
+                            int max_batches, int nblk, double tol, int n_iter_no_change, int max_iter,
+                            int32_t* __restrict__ active, int32_t* __restrict__ epoch, int32_t* __restrict__ no_improve,
+                            double* __restrict__ best_loss, double* __restrict__ last_loss) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_groups || !active[g]) return;
+  epoch_end_group<false>(groups[g], g, batch_stats, max_batches, nblk, tol, n_iter_no_change, max_iter, active, epoch, no_improve,
+                         best_loss, last_loss);
+}
+
+// ---------------------------------------------------------------------------------------
+// K2b, persistent form: a client's whole local fit (SK:703-777) in ONE launch.  A thread-block cluster owns a client and
+// loops over epochs and mini-batches on the device: per-epoch shuffle, one tile of the mini-batch per CTA (fwd_bwd_tile),
+// cluster barrier, fixed-order reduction + optimizer over the slab split in the same 256-float4 blocks k_reduce_opt uses
+// (so the per-block sums of squares, and with them the loss curve and the stopping epoch, are bit-identical to the
+// launch-per-mini-batch path), cluster barrier, and at the end of the epoch the tol / n_iter_no_change rule.  Clients are
+// independent until the aggregation, so clusters never wait for each other and need not be co-resident.  Data another CTA
+// wrote earlier in the kernel (weights, row order, gradient records, statistics) is read with L2-coherent loads.
+// ---------------------------------------------------------------------------------------
+struct FitArgs {
+  const FedbGroup* groups;
+  float *params, *m, *v, *scratch, *loss_out;
+  const float* X;
+  const int32_t *y, *idx_in;
+  int32_t *idx_epoch, *step, *active, *epoch, *no_improve;
+  const FedbFedState* fed_state;
+  double *batch_stats, *best_loss, *last_loss;
+  double tol;
+  int ldx, n_batches, max_batches, nvblocks, n_iter_no_change, max_iter, max_epochs, shuffle, smem_floats;
+  uint32_t s0, s1;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1) k_fit_cluster(const FitArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int CS = (int)cluster.num_blocks(), q = (int)cluster.block_rank();
+  const int g = blockIdx.x / CS;
+  const FedbGroup& G = a.groups[g];
+  if (a.fed_state && a.fed_state[G.fed].stop) return;      // whole cluster: the federation has stopped
+  const int n = G.n_rows;
+  const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
+  const int ntiles = (bs + FEDB_TILE_ROWS - 1) / FEDB_TILE_ROWS;
+  const int32_t* idx = a.shuffle ? a.idx_epoch : a.idx_in;
+  int bits = 1;
+  while ((1u << bits) < (uint32_t)n) ++bits;
+  const int half = (bits + 1) >> 1;
+  for (int ep = 0; ep < a.max_epochs; ++ep) {
+    if (!__ldcg(a.active + g)) break;                       // same value in every CTA: written before the last cluster barrier
+    if (a.shuffle) {
+      const uint32_t ka = a.s0 ^ (uint32_t)(g * 0x9E3779B1u), kb = a.s1 + (uint32_t)__ldcg(a.epoch + g);
+      for (uint32_t i = q * blockDim.x + threadIdx.x; i < (uint32_t)n; i += CS * blockDim.x)
+        a.idx_epoch[G.idx_off + i] = a.idx_in[G.idx_off + feistel_perm(i, n, half, ka, kb)];
+      __threadfence();
+      cluster.sync();
+    }
+    for (int b = 0; b < a.n_batches; ++b) {
+      for (int tile = q; tile < ntiles; tile += CS) {
+        fwd_bwd_tile<true>(G, g, tile, a.params, a.X, a.ldx, a.y, idx, b, a.scratch, a.step, a.smem_floats, smem);
+        __syncthreads();
+      }
+      __threadfence();
+      cluster.sync();
+      for (int vb = q; vb < a.nvblocks; vb += CS) {
+        reduce_opt_block<true>(G, g, vb, a.nvblocks, a.params, a.m, a.v, a.scratch, b, a.step, a.loss_out, a.batch_stats, a.max_batches);
+        __syncthreads();
+      }
+      __threadfence();
+      cluster.sync();
+    }
+    if (q == 0 && threadIdx.x == 0)
+      epoch_end_group<true>(G, g, a.batch_stats, a.max_batches, a.nvblocks, a.tol, a.n_iter_no_change, a.max_iter, a.active, a.epoch,
+                            a.no_improve, a.best_loss, a.last_loss);
+    __threadfence();
+    cluster.sync();
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -672,7 +775,9 @@ static int set_smem(const void* fn, int64_t bytes) {
   static const void* done[8] = {nullptr};
   if (bytes <= 48 * 1024) return FEDB_OK;
   for (int i = 0; i < 8; ++i) if (done[i] == fn) return FEDB_OK;
-  FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  cudaFuncAttributes fa;
+  FEDB_CUDA_OK(cudaFuncGetAttributes(&fa, fn));   // static shared memory counts against the same 227 KB
+  FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
   for (int i = 0; i < 8; ++i) if (done[i] == nullptr) { done[i] = fn; break; }
   return FEDB_OK;
 }
@@ -745,6 +850,37 @@ extern "C" int fedb_epoch_end(const FedbGroup* groups, int32_t n_groups, const d
                                                                       tol, n_iter_no_change, max_iter, active, epoch,
                                                                       no_improve, best_loss, last_loss);
   FEDB_LAUNCH_OK();
+  return FEDB_OK;
+}
+
+// The whole local fit of every client in one launch (see k_fit_cluster).  Runs up to max_epochs further epochs per client (clients
+// whose active flag is 0, or that converge, stop by themselves); the arguments are those of fedb_shuffle / fedb_fwd_bwd /
+// fedb_reduce_opt / fedb_epoch_end, which this replaces call for call.  cluster_size CTAs (1..8) share a client's mini-batch tiles.
+extern "C" int fedb_fit_cluster(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, int32_t cluster_size, float* params,
+                                float* m, float* v, const float* X, int32_t ldx, const int32_t* y, const int32_t* idx_in,
+                                int32_t* idx_epoch, float* scratch, int32_t* step, int32_t* active,
+                                const FedbFedState* fed_state, int32_t* epoch, int32_t* no_improve, double* best_loss, double* last_loss, float* loss_out, double* batch_stats,
+                                int32_t max_batches, int32_t n_batches, double tol, int32_t n_iter_no_change, int32_t max_iter,
+                                int32_t max_epochs, int32_t shuffle, uint64_t seed, int64_t smem_bytes, void* stream) {
+  FEDB_REQUIRE(n_groups > 0 && max_slab > 0 && cluster_size >= 1 && cluster_size <= 8, "bad sizes");
+  FEDB_REQUIRE(ldx % 4 == 0, "ldx must be a multiple of 4");
+  FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
+  FEDB_REQUIRE(batch_stats && active && epoch && no_improve && best_loss && last_loss, "fit state arrays required");
+  if (int rc = set_smem((const void*)k_fit_cluster, smem_bytes)) return rc;
+  FitArgs a{};
+  a.groups = groups; a.params = params; a.m = m; a.v = v; a.scratch = scratch; a.loss_out = loss_out; a.X = X; a.y = y;
+  a.idx_in = idx_in; a.idx_epoch = idx_epoch; a.step = step; a.active = active; a.fed_state = fed_state; a.epoch = epoch; a.no_improve = no_improve;
+  a.batch_stats = batch_stats; a.best_loss = best_loss; a.last_loss = last_loss; a.tol = tol; a.ldx = ldx; a.n_batches = n_batches;
+  a.max_batches = max_batches; a.nvblocks = (max_slab / 4 + NTHREADS - 1) / NTHREADS; a.n_iter_no_change = n_iter_no_change;
+  a.max_iter = max_iter; a.max_epochs = max_epochs; a.shuffle = shuffle; a.smem_floats = (int)(smem_bytes / 4);
+  a.s0 = (uint32_t)seed; a.s1 = (uint32_t)(seed >> 32);
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)cluster_size; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.gridDim = dim3((unsigned)(n_groups * cluster_size)); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = (size_t)smem_bytes;
+  cfg.stream = (cudaStream_t)stream; cfg.attrs = at; cfg.numAttrs = 1;
+  FEDB_CUDA_OK(cudaLaunchKernelEx(&cfg, k_fit_cluster, a));
   return FEDB_OK;
 }
 

@@ -416,10 +416,33 @@ class FedEngine:
         K.epoch_end(self.tb, self.batch_stats, self.n_batches, h.tol, h.n_iter_no_change, h.max_iter, self.active,
                     self.epoch, self.no_improve, self.best_loss, self.last_loss)
 
+    def _fit_in_one_launch(self) -> bool:
+        """Whether :meth:`fit_local` runs as one persistent launch (fedb_fit_cluster).  FEDB200_FIT=cluster | launches forces
+        the choice; by default the persistent kernel is used while every client's cluster can be resident at once (measured:
+        0.83 s against 0.92 s for the 4-client sklearn script; with the 360 clients of the grid the per-step launches balance
+        the uneven fits better: 5.1 s against 5.6 s)."""
+        if self.device.type != "cuda" or self.tb.smem_bytes <= 0:
+            return False
+        mode = os.environ.get("FEDB200_FIT", "auto")
+        if mode in ("cluster", "launches"):
+            return mode == "cluster"
+        return self.n_groups * 8 <= 2 * torch.cuda.get_device_properties(self.device).multi_processor_count
+
     def fit_local(self, max_iter: Optional[int] = None, shuffle: bool = True, check_every: int = 8) -> np.ndarray:
         """Train every client until its loss stalls (SK:750-777) or ``max_iter`` epochs.
         Returns the number of epochs each client ran (sklearn's ``n_iter_``)."""
         max_iter = max_iter or max(p.hyper.max_iter for p in self.problems)
+        if self._fit_in_one_launch():
+            # K2b, persistent form: epochs, mini-batches and the stopping rule all run on the device (fedb_fit_cluster)
+            h = self.problems[0].hyper
+            tiles_per_batch = max(-(-min(int(g["batch_size"]) or int(g["n_rows"]), int(g["n_rows"])) // nat.TILE_ROWS) for g in self.tb.groups)
+            K.fit_cluster(self.tb, max(1, min(8, tiles_per_batch)), self.params, self.m, self.v, self.X, self.y, self.idx, self.idx_epoch,
+                          self.scratch, self.step, self.active, self.fed_state, self.epoch, self.no_improve, self.best_loss,
+                          self.last_loss, self.loss, self.batch_stats, self.n_batches, h.tol, h.n_iter_no_change, h.max_iter,
+                          max_iter, shuffle, self.seed + 0x5EED)
+            n_iter = self.epoch.cpu().numpy().copy()
+            self.active.fill_(1)
+            return n_iter
         use_graph = self.device.type == "cuda"
         if use_graph and "epochx1" not in self._graphs:
             snap = self._snapshot()

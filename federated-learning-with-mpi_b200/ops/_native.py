@@ -223,6 +223,8 @@ OPTIONAL_SIGS = {
     "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
     "fedb_tc_smem_bytes": ([], _I64),
     "fedb_tc_max_slab": ([], _I32),
+    "fedb_fit_cluster": ([_P, _I32, _I32, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _F64, _I32,
+                          _I32, _I32, _I32, _U64, _I64, _P], _I32),
     "fedb_round_tc_p2p_hostin": ([_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P], _I32),
     "fedb_round_tc_hostin": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P, _P, _P], _I32),
     "fedb_round_tc_p2p": ([_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P], _I32),

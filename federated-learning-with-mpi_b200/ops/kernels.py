@@ -156,6 +156,20 @@ def epoch_end(tb: DeviceTables, batch_stats, max_batches: int, tol: float, n_ite
                       no_improve, best_loss, last_loss)
 
 
+def fit_cluster(tb: DeviceTables, cluster_size: int, params, m, v, X, y, idx_in, idx_epoch, scratch, step, active, fed_state, epoch,
+                no_improve, best_loss, last_loss, loss_out, batch_stats, n_batches: int, tol: float, n_iter_no_change: int,
+                max_iter: int, max_epochs: int, shuffle_rows: bool, seed: int) -> None:
+    """CUDA only: every client's whole local fit in one launch (fedb_fit_cluster) — the device-side equivalent of looping
+    ``shuffle`` + ``n_batches`` x (``fwd_bwd`` + ``reduce_opt``) + ``epoch_end`` for ``max_epochs`` epochs."""
+    nat.check(_L().fedb_fit_cluster(nat.ptr(tb.d_groups), tb.n_groups, tb.max_slab, cluster_size, nat.ptr(params), nat.ptr(m), nat.ptr(v),
+                                    nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(idx_in), nat.ptr(idx_epoch), nat.ptr(scratch),
+                                    nat.ptr(step), nat.ptr(active), nat.ptr(fed_state), nat.ptr(epoch), nat.ptr(no_improve),
+                                    nat.ptr(best_loss), nat.ptr(last_loss), nat.ptr(loss_out), nat.ptr(batch_stats), n_batches,
+                                    n_batches, float(tol), n_iter_no_change, max_iter, max_epochs, int(shuffle_rows),
+                                    seed & (2 ** 64 - 1), tb.smem_bytes, nat.cuda_stream()))
+    _count()
+
+
 def batch_stats_stride(max_slab: int) -> int:
     return ref.batch_stats_stride(max_slab)
 

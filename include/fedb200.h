@@ -210,6 +210,16 @@ int fedb_epoch_end(const FedbGroup* groups, int32_t n_groups, const double* batc
                    int32_t max_batches, int32_t max_slab, double tol, int32_t n_iter_no_change, int32_t max_iter,
                    int32_t* active, int32_t* epoch, int32_t* no_improve, double* best_loss,
                    double* last_loss, void* stream);
+/* K2b in persistent form: the whole local fit of every client (per-epoch shuffle, mini-batch steps, tol / n_iter_no_change
+ * stopping: SK:703-777) in ONE launch.  A cluster of cluster_size CTAs (1..8) owns a client and loops on the device; arguments
+ * as for fedb_shuffle / fedb_fwd_bwd / fedb_reduce_opt / fedb_epoch_end, which it replaces call for call with bit-identical
+ * results.  Runs at most max_epochs further epochs; clients with active == 0 or a stopped federation return at once. */
+int fedb_fit_cluster(const FedbGroup* groups, int32_t n_groups, int32_t max_slab, int32_t cluster_size, float* params, float* m,
+                     float* v, const float* X, int32_t ldx, const int32_t* y, const int32_t* idx_in, int32_t* idx_epoch,
+                     float* scratch, int32_t* step, int32_t* active, const FedbFedState* fed_state, int32_t* epoch,
+                     int32_t* no_improve, double* best_loss, double* last_loss, float* loss_out, double* batch_stats,
+                     int32_t max_batches, int32_t n_batches, double tol, int32_t n_iter_no_change, int32_t max_iter,
+                     int32_t max_epochs, int32_t shuffle, uint64_t seed, int64_t smem_bytes, void* stream);
 
 /* K3 — forward + argmax / threshold + confusion counts (C:75-83, S:104; SK:1283-1290). */
 int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const FedbTile* tiles, int32_t n_tiles,

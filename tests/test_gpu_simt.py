@@ -145,6 +145,31 @@ def test_sklearn_epoch_matches_reference(income_nomean):
     assert torch.equal(cpu.epoch, gpu.epoch.cpu()) and torch.equal(cpu.step, gpu.step.cpu())
 
 
+@pytest.mark.parametrize("shuffle", [True, False])
+def test_one_launch_fit_is_bit_identical_to_per_step_launches(income_nomean, shuffle, monkeypatch):
+    """fedb_fit_cluster (device-side epoch / mini-batch loop + stopping rule) against the same fit driven from the host with one
+    launch per step: identical epoch counts, losses and parameters."""
+    def fit(mode, max_iter):
+        monkeypatch.setenv("FEDB200_FIT", mode)
+        e = FedEngine(_problems(income_nomean, "sklearn"), income_nomean.X_train[:3000], income_nomean.y_train[:3000],
+                      income_nomean.X_test, income_nomean.y_test, device="cuda", max_rounds=2)
+        assert e._fit_in_one_launch() == (mode == "cluster")
+        if mode == "cluster":
+            monkeypatch.delenv("FEDB200_FIT")
+            assert e._fit_in_one_launch()                 # 12 clients: the default is the persistent kernel
+            monkeypatch.setenv("FEDB200_FIT", mode)
+        n_iter = e.fit_local(max_iter=max_iter, shuffle=shuffle)
+        torch.cuda.synchronize()
+        return e, n_iter
+    for max_iter in (3, 40):
+        a, na = fit("cluster", max_iter)
+        b, nb = fit("launches", max_iter)
+        assert np.array_equal(na, nb) and na.max() == max_iter or na.max() <= max_iter
+        assert torch.equal(a.step, b.step) and torch.equal(a.epoch, b.epoch) and torch.equal(a.no_improve, b.no_improve)
+        assert torch.equal(a.last_loss, b.last_loss) and torch.equal(a.best_loss, b.best_loss)
+        assert torch.equal(a.params, b.params) and torch.equal(a.m, b.m) and torch.equal(a.v, b.v)
+
+
 def test_early_stop_freezes_state(income):
     probs = [FedProblem.custom(14, 2, make_shards("contiguous", 2000, 2), patience=2, atol=1.0)]  # everything "close"
     gpu = FedEngine(probs, income.X_train[:2000], income.y_train[:2000], device="cuda", max_rounds=20)
