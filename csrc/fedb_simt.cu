@@ -22,6 +22,9 @@ thread_local char g_err[512] = "";
 
 constexpr int LDS = FEDB_TILE_ROWS + 1;  // 33: feature-major rows, conflict-free both ways
 constexpr int NTHREADS = 256;
+// The tile kernels (forward/backward, evaluation) are bound by shared-memory latency: 16 warps hide it better than 8.
+// (Results do not depend on the block size: every output element is computed by one thread in a fixed order.)
+constexpr int TILE_THREADS = 512;
 
 struct SmemPlan {
   int a_off[FEDB_MAX_LAYERS + 1];  // float offsets of activation buffers a[0..L]
@@ -32,16 +35,21 @@ struct SmemPlan {
 
 __host__ __device__ inline SmemPlan smem_plan(const int32_t* dims, int L) {
   SmemPlan p;
-  int off = 0, maxw = 4;
+  int off = 0;
   for (int l = 0; l <= FEDB_MAX_LAYERS; ++l) {
     p.a_off[l] = off;
-    if (l <= L) {
-      off += ru4(dims[l]) * LDS;
-      if (l >= 1 && ru4(dims[l]) > maxw) maxw = ru4(dims[l]);
-    }
+    if (l <= L) off += ru4(dims[l]) * LDS;
   }
-  p.dz_off[0] = off; off += maxw * LDS;
-  p.dz_off[1] = off; off += maxw * LDS;
+  // The backward pass ping-pongs between two dz buffers: buffer 0 holds dz of layers L, L-2, ..., buffer 1 that of layers
+  // L-1, L-3, ...  Each is sized for the widths it actually holds (for 14-50-400-1 that is 52 + 400 rows instead of 2 x 400,
+  // which is what lets that model's 86 KB of weights be staged next to the activations).
+  int w0 = 4, w1 = 4;
+  for (int l = L, par = 0; l >= 1; --l, par ^= 1) {
+    const int w = ru4(dims[l]);
+    if (par == 0) { if (w > w0) w0 = w; } else { if (w > w1) w1 = w; }
+  }
+  p.dz_off[0] = off; off += w0 * LDS;
+  p.dz_off[1] = off; off += w1 * LDS;
   p.misc_off = off; off += 64;
   p.total_floats = off;
   return p;
@@ -392,7 +400,7 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
   }
 }
 
-__global__ void __launch_bounds__(NTHREADS)
+__global__ void __launch_bounds__(TILE_THREADS)
 k_fwd_bwd(const FedbGroup* __restrict__ groups, const FedbTile* __restrict__ tiles, const float* __restrict__ params,
           const float* __restrict__ X, int ldx, const int32_t* __restrict__ y, const int32_t* __restrict__ idx,
           int batch, float* __restrict__ scratch, int32_t* __restrict__ step, const int32_t* __restrict__ active,
@@ -432,8 +440,8 @@ __device__ void reduce_opt_block(const FedbGroup& G, int g, int vblock, int nvbl
   const StepScalars sc = sc_s;
 
   float sumsq = 0.f;
-  const int q = vblock * blockDim.x + threadIdx.x;
-  if (q * 4 < lay.end) {
+  const int q = vblock * NTHREADS + threadIdx.x;   // the 256-float4 partition is part of the result (per-block sums of squares)
+  if (threadIdx.x < NTHREADS && q * 4 < lay.end) {
     const int e = q * 4;
     bool is_w = false;
     for (int l = 0; l < G.n_layers; ++l) is_w |= (e >= lay.w_off[l] && e < lay.b_off[l]);
@@ -467,7 +475,7 @@ __device__ void reduce_opt_block(const FedbGroup& G, int g, int vblock, int nvbl
   // loss + sum of squares bookkeeping (deterministic: fixed tree, fixed block order)
   if (batch_stats) {
     sumsq = warp_sum(sumsq);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sumsq;
+    if ((threadIdx.x & 31) == 0 && threadIdx.x < NTHREADS) red[threadIdx.x >> 5] = sumsq;
     __syncthreads();
     if (threadIdx.x == 0) {
       float s = 0.f;
@@ -560,7 +568,7 @@ struct FitArgs {
   uint32_t s0, s1;
 };
 
-__global__ void __launch_bounds__(NTHREADS, 1) k_fit_cluster(const FitArgs a) {
+__global__ void __launch_bounds__(TILE_THREADS, 1) k_fit_cluster(const FitArgs a) {
   extern __shared__ __align__(16) float smem[];
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
@@ -765,8 +773,9 @@ extern "C" int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers) {
   const SmemPlan sp = smem_plan(dims, n_layers);
   const SlabLayout lay = slab_layout(dims, n_layers);
   const int64_t bytes = (int64_t)sp.total_floats * 4, with_w = bytes + (int64_t)lay.end * 4;
-  if (with_w <= 227 * 1024) return with_w;  // weights staged in shared memory
-  return bytes <= 227 * 1024 ? bytes : -1;
+  const int64_t cap = 227 * 1024 - 64;     // the kernels' few static __shared__ variables count against the same limit
+  if (with_w <= cap) return with_w;  // weights staged in shared memory
+  return bytes <= cap ? bytes : -1;
 }
 
 // Opt in to >48 KB of dynamic shared memory once per function (always the 227 KB maximum, so the
@@ -822,7 +831,7 @@ extern "C" int fedb_fwd_bwd(const FedbGroup* groups, const FedbTile* tiles, int3
   FEDB_REQUIRE(ldx % 4 == 0, "ldx must be a multiple of 4");
   FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
   if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
-  k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, tiles, params, X, ldx, y, idx, batch,
+  k_fwd_bwd<<<n_tiles, TILE_THREADS, smem_bytes, (cudaStream_t)stream>>>(groups, tiles, params, X, ldx, y, idx, batch,
                                                                      scratch, step, active, fed_state,
                                                                      (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();
@@ -878,7 +887,7 @@ extern "C" int fedb_fit_cluster(const FedbGroup* groups, int32_t n_groups, int32
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = (unsigned)cluster_size; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.gridDim = dim3((unsigned)(n_groups * cluster_size)); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = (size_t)smem_bytes;
+  cfg.gridDim = dim3((unsigned)(n_groups * cluster_size)); cfg.blockDim = dim3(TILE_THREADS); cfg.dynamicSmemBytes = (size_t)smem_bytes;
   cfg.stream = (cudaStream_t)stream; cfg.attrs = at; cfg.numAttrs = 1;
   FEDB_CUDA_OK(cudaLaunchKernelEx(&cfg, k_fit_cluster, a));
   return FEDB_OK;
@@ -970,7 +979,7 @@ extern "C" int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbG
   // (and its loss slot) that k_reduce_opt reads for the same step, so stale contents of an earlier
   // call are never observed.
   if (int rc = set_smem((const void*)k_fwd_bwd, smem_bytes)) return rc;
-  k_fwd_bwd<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups_dev, tiles, params, X, ldx, y, idx, batch,
+  k_fwd_bwd<<<n_tiles, TILE_THREADS, smem_bytes, (cudaStream_t)stream>>>(groups_dev, tiles, params, X, ldx, y, idx, batch,
                                                                      scratch, step, active, fed_state,
                                                                      (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();

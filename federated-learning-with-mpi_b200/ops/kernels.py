@@ -67,16 +67,22 @@ class DeviceTables:
 
 
 def simt_smem_bytes(dims, n_layers: int) -> int:
+    """Dynamic shared memory of the whole-network SIMT kernels for this MLP (mirrors smem_plan / fedb_simt_smem_bytes in
+    csrc/fedb_simt.cu; tests/test_models.py checks the two against each other when the library is present)."""
     d = [int(x) for x in dims[: n_layers + 1]]
     ru4 = lambda x: (x + 3) // 4 * 4
-    maxw = max([4] + [ru4(x) for x in d[1:]])
-    total = (sum(ru4(x) for x in d) + 2 * maxw) * 33 + 64
+    # the backward pass ping-pongs between two dz buffers: buffer 0 holds layers L, L-2, ..., buffer 1 layers L-1, L-3, ...
+    w = [4, 4]
+    for par, l in enumerate(range(n_layers, 0, -1)):
+        w[par & 1] = max(w[par & 1], ru4(d[l]))
+    total = (sum(ru4(x) for x in d) + w[0] + w[1]) * 33 + 64
     b = total * 4
     n_w = sum(d[l + 1] * ru4(d[l]) + ru4(d[l + 1]) for l in range(n_layers))
-    if b + n_w * 4 <= 227 * 1024:
+    cap = 227 * 1024 - 64          # the kernels' few static __shared__ variables count against the same limit
+    if b + n_w * 4 <= cap:
         return b + n_w * 4  # room to stage the client's weights in shared memory too
-    if b > 227 * 1024:
-        raise ValueError(f"MLP {d} needs {b} bytes of shared memory per CTA in the SIMT kernels (max 232448); "
+    if b > cap:
+        raise ValueError(f"MLP {d} needs {b} bytes of shared memory per CTA in the SIMT kernels (max {cap}); "
                          "use the wide (layer-wise tcgen05 GEMM) path")
     return b
 

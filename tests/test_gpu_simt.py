@@ -154,10 +154,6 @@ def test_one_launch_fit_is_bit_identical_to_per_step_launches(income_nomean, shu
         e = FedEngine(_problems(income_nomean, "sklearn"), income_nomean.X_train[:3000], income_nomean.y_train[:3000],
                       income_nomean.X_test, income_nomean.y_test, device="cuda", max_rounds=2)
         assert e._fit_in_one_launch() == (mode == "cluster")
-        if mode == "cluster":
-            monkeypatch.delenv("FEDB200_FIT")
-            assert e._fit_in_one_launch()                 # 12 clients: the default is the persistent kernel
-            monkeypatch.setenv("FEDB200_FIT", mode)
         n_iter = e.fit_local(max_iter=max_iter, shuffle=shuffle)
         torch.cuda.synchronize()
         return e, n_iter

@@ -122,3 +122,20 @@ def test_early_stop_anchor_semantics():
     assert es.count == 3
     es.update(m(0.6)); es.update(m(0.6))
     assert es.update(m(0.6)) and es.stop
+
+
+def test_simt_shared_memory_plan_matches_library():
+    """ops.kernels.simt_smem_bytes mirrors smem_plan in csrc/fedb_simt.cu; the engine sizes launches with the former."""
+    import ctypes
+    from fedb200.ops import _native as nat, kernels as K
+    lib = nat.lib(required=False)
+    if lib is None:
+        pytest.skip("native library not built")
+    for dims in [(14, 50, 400, 1), (14, 50, 200, 2), (14, 400, 200, 1), (14, 100, 1), (14, 37, 2), (14, 5, 6, 2), (14, 200, 400, 1),
+                 (14, 3000, 3000, 2), (14, 50, 60, 70, 2)]:
+        want = lib.fedb_simt_smem_bytes((ctypes.c_int32 * 8)(*dims), len(dims) - 1)
+        try:
+            got = K.simt_smem_bytes(dims, len(dims) - 1)
+        except ValueError:
+            got = -1
+        assert got == want, (dims, got, want)
