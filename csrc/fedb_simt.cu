@@ -617,7 +617,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) k_fit_cluster(const FitArgs a
 // ---------------------------------------------------------------------------------------
 // K3: eval
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NTHREADS)
+__global__ void __launch_bounds__(TILE_THREADS)
 k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ jobs, const FedbTile* __restrict__ tiles,
        const float* __restrict__ params, const float* __restrict__ global, const float* __restrict__ X, int ldx,
        const int32_t* __restrict__ y, const int32_t* __restrict__ idx, int32_t* __restrict__ conf,
@@ -900,7 +900,7 @@ extern "C" int fedb_eval(const FedbGroup* groups, const FedbEvalJob* jobs, const
   FEDB_REQUIRE(n_tiles > 0, "n_tiles must be positive");
   FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
   if (int rc = set_smem((const void*)k_eval, smem_bytes)) return rc;
-  k_eval<<<n_tiles, NTHREADS, smem_bytes, (cudaStream_t)stream>>>(groups, jobs, tiles, params, global, X, ldx, y, idx,
+  k_eval<<<n_tiles, TILE_THREADS, smem_bytes, (cudaStream_t)stream>>>(groups, jobs, tiles, params, global, X, ldx, y, idx,
                                                                   conf, fed_state, (int)(smem_bytes / 4));
   FEDB_LAUNCH_OK();
   return FEDB_OK;

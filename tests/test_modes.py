@@ -91,3 +91,21 @@ def test_cli_sklearn_and_tune_smoke(capsys):
     assert "Final Global Weight Statistics:" in capsys.readouterr().out
     assert cli_main(["tune", "--clients", "2", "--max-iter", "2", "--small", "--device", "cpu", "--quiet", "--synthetic-rows", "400"]) == 0
     assert "Best" not in capsys.readouterr().err
+
+
+def test_step_e2e_on_cpu_streams_new_inputs(income):
+    """The streaming API on the CPU engine: each step trains on whatever the host buffers hold at that moment."""
+    from fedb200 import FedEngine, FedProblem, make_shards
+    mk = lambda: FedEngine([FedProblem.custom(14, 2, make_shards("contiguous", 600, 3), hidden=(8, 12), patience=0)],
+                           income.X_train[:600], income.y_train[:600], income.X_test, income.y_test, device="cpu", max_rounds=8)
+    a, b = mk(), mk()
+    assert not a.pulls_host_inputs()
+    xh, yh = a.pinned_train_inputs()
+    s1 = a.step_e2e(xh, yh).copy()
+    b.run(1)
+    assert s1["done"][0] == 1 and np.allclose(s1["last"][0], b.history()["global"][0, 0], atol=1e-6)
+    xh[:, :14] *= -1.0
+    a.step_e2e(xh, yh)
+    b.run(1)
+    assert not np.allclose(a.params.numpy(), b.params.numpy())          # a trained on the changed inputs
+    assert a.e2e_bytes()[0] == 600 * a.ldx * 4 + 600 * 4
