@@ -638,8 +638,8 @@ class FedEngine:
         if self._fused_round_ok():
             return ["k_local_round_tc[train+eval+fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
-            return ["k_round_begin", "k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
-                    "k_fedavg[+bf16 shadow]"]
+            return ["k_round_begin", "k_gemm_tma2[fwd+bias+relu|dgrad+mask] (k_gemm_tma off the 256-multiples)", "k_gemm_tma2p[wgrad+optimizer]",
+                    "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt", "k_fedavg[+bf16 shadow]"]
         if self.precision_name == "bf16":
             return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]
         return ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]
