@@ -318,7 +318,15 @@ __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int 
     st.done = st.round;
     if (begin_next) begin_next_round(st);
     S = st;
-    if (host_mirror) *host_mirror = st;   // mapped pinned host memory: the round's result reaches the host without a memcpy node
+    if (host_mirror) {
+      // mapped pinned host memory: the round's result reaches the host without a memcpy node.  `done` is published last,
+      // behind a system-scope fence, so a host that polls it (FedEngine.step_e2e) never reads a half-written record.
+      FedbFedState t = st;
+      t.done = -1;
+      *host_mirror = t;
+      __threadfence_system();
+      *reinterpret_cast<volatile int32_t*>(&host_mirror->done) = st.done;
+    }
   }
   __syncwarp();
 }

@@ -214,7 +214,8 @@ class FedEngine:
         self.tail_count = z(1, torch.int32)
         # mapped pinned host copy of the federation state: the fused round kernels store their result there too
         self._state_pinned = torch.zeros(self.fed_state.numel(), dtype=torch.uint8).pin_memory() if d.type == "cuda" else None
-        self._e2e_cache: Dict = {}   # (x_host ptr, y_host ptr) -> (graph replay, stream sync, result view, buffers kept alive)
+        self._e2e_cache: Dict = {}   # (x_host ptr, y_host ptr) -> (graph replay, stream sync, result view, buffers kept alive, done view)
+        self._e2e_expect = -1        # value of `done` the next polled step will publish (-1: synchronise instead)
 
     def _ensure_wide(self):
         if getattr(self, "_wide_pending", False):
@@ -360,6 +361,7 @@ class FedEngine:
         st = self.fed_state_host()
         done = int(st["done"].max()) if len(st) else 0
         rounds = min(rounds, self.max_rounds - done)
+        self._e2e_expect = -1
         self.prime()
         use_graph = (self.device.type == "cuda") if use_graph is None else use_graph
         if not use_graph:
@@ -391,6 +393,7 @@ class FedEngine:
     def _restore(self, snap) -> None:
         for n, t in snap.items():
             getattr(self, n).copy_(t)
+        self._e2e_expect = -1
 
     # ------------------------------------------------------------- sklearn-style local fit
     def reset_fit_state(self, keep_no_improvement: bool = False) -> None:
@@ -579,8 +582,20 @@ class FedEngine:
         # a stream synchronisation per step (its time between the sync and the next launch is GPU idle time)
         ent = self._e2e_cache.get((x_host.data_ptr(), y_host.data_ptr())) if self._primed else None
         if ent is not None:
-            ent[0]()
-            ent[1]()
+            ent[0]()                                     # one graph launch
+            done = ent[5]
+            if done is None or self._e2e_expect < 0:
+                ent[1]()                                 # stream synchronise
+            else:
+                # the round kernel publishes `done` last (system-scope fence) into mapped pinned memory: poll it instead of
+                # waiting for the whole kernel to retire, so the next launch overlaps this kernel's teardown
+                want, spins = self._e2e_expect, 0
+                while done[0] != want:
+                    spins += 1
+                    if spins > 4000:                     # stopped federation (no new round) or an unusually slow step
+                        ent[1]()
+                        break
+                self._e2e_expect = int(done[0]) + 1 if not ent[2]["stop"][0] else -1
             return ent[2]
         self.prime()
         if self.device.type != "cuda":
@@ -611,11 +626,14 @@ class FedEngine:
                 self._graph(key, body, 1)
                 self._restore(snap)
             g = self._graphs[key + "x1"]
-            self._e2e_cache[(x_host.data_ptr(), y_host.data_ptr())] = (g.replay, stream.synchronize, view, x_host, y_host)
+            poll = mirrored and self.n_feds == 1 and os.environ.get("FEDB200_E2E_SYNC") is None
+            self._e2e_cache[(x_host.data_ptr(), y_host.data_ptr())] = (g.replay, stream.synchronize, view, x_host, y_host,
+                                                                        view["done"] if poll else None)
             g.replay()
         else:
             body()
         stream.synchronize()
+        self._e2e_expect = -1 if view["stop"][0] else int(view["done"][0]) + 1
         return view
 
     def _result_is_mirrored(self) -> bool:
@@ -646,6 +664,7 @@ class FedEngine:
 
     def step_graph(self) -> None:
         """Enqueue exactly one round (graph replay on CUDA); no host synchronisation."""
+        self._e2e_expect = -1          # the polled end-to-end path must re-arm on the state this round leaves behind
         self.prime()
         if self.device.type != "cuda":
             self.enqueue_round()

@@ -57,3 +57,30 @@ def test_kernel_pull_reads_the_host_buffers_every_step(income):
     chk.X[: chk.n_train].copy_(xh); chk.y[: chk.n_train].copy_(yh)
     chk.step_graph(); torch.cuda.synchronize()
     assert torch.equal(chk.params, e.params)
+
+
+def test_polled_result_matches_synchronised_and_survives_interleaving(income, monkeypatch):
+    """The steady-state step polls `done` in the mapped result record instead of synchronising the stream; mixing it with
+    other stepping calls, and running past an early stop, must give the same states as the synchronising path."""
+    def drive(e):
+        xh, yh = e.pinned_train_inputs()
+        out = []
+        for i in range(12):
+            if i in (4, 9):
+                e.step_graph()                     # a round outside the polled path: expectation must re-arm
+            out.append(e.step_e2e(xh, yh).copy())
+        torch.cuda.synchronize()
+        return out
+    a = drive(_engine(income, 1))
+    monkeypatch.setenv("FEDB200_E2E_SYNC", "1")
+    b = drive(_engine(income, 1))
+    for sa, sb in zip(a, b):
+        assert sa["done"][0] == sb["done"][0] and np.array_equal(sa["last"], sb["last"]) and sa["stop"][0] == sb["stop"][0]
+    assert a[-1]["done"][0] == 14
+    # early stop: patience 1 with a huge tolerance stops after two rounds; further steps return the frozen state
+    monkeypatch.delenv("FEDB200_E2E_SYNC")
+    e = FedEngine([FedProblem.custom(14, 2, make_shards("contiguous", 1000, 1), patience=1, atol=1.0)], income.X_train[:1000],
+                  income.y_train[:1000], income.X_test, income.y_test, device="cuda", max_rounds=64, precision="bf16")
+    xh, yh = e.pinned_train_inputs()
+    states = [e.step_e2e(xh, yh).copy() for _ in range(8)]
+    assert states[-1]["stop"][0] and states[-1]["done"][0] == states[-2]["done"][0] < 8
