@@ -37,7 +37,8 @@ __global__ void __launch_bounds__(P2P_THREADS, 4) k_fedavg_p2p(const FedbP2PRank
   const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
   const int par = (int)(seq & 1);
   const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
-  float* my_partial = reinterpret_cast<float*>(R.sym[R.rank] + R.sym_partial_off) + (int64_t)par * R.global_total;
+  const bool nvls = R.nvls_mc_partial != nullptr;       // partial sums live in multicast-bound memory: the switch adds them
+  float* my_partial = (nvls ? R.nvls_uc_partial : reinterpret_cast<float*>(R.sym[R.rank] + R.sym_partial_off)) + (int64_t)par * R.global_total;
   int32_t* my_confx = reinterpret_cast<int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + R.rank) * conf_stride;   // area (parity, source rank)
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
   const int gthreads = gridDim.x * blockDim.x, gtid = blockIdx.x * blockDim.x + tid;
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(P2P_THREADS, 4) k_fedavg_p2p(const FedbP2PRank
   const long long t0 = clock64();
   if (tid == 0) {
     atomicAdd(R.bar, 1u);
-    const uint32_t target = (uint32_t)((seq + 1) * gridDim.x);
+    const uint32_t target = (uint32_t)(((nvls ? 2 * seq : seq) + 1) * gridDim.x);   // NVLS launches pass two grid barriers
     while ((int32_t)(ld_acquire_gpu_u32(R.bar) - target) < 0)
       if (clock64() - t0 > R.timeout_cycles) { timed_out = true; break; }
   }
@@ -103,17 +104,51 @@ __global__ void __launch_bounds__(P2P_THREADS, 4) k_fedavg_p2p(const FedbP2PRank
   if (timed_out) *R.err = FEDB_E_TIMEOUT;
   __syncthreads();
 
-  // ---- C: sum the partials of all ranks in rank order; write global + every resident client -------
+  if (nvls) {
+    // ---- C (NVLS): reduce-scatter in the switch.  This rank owns a contiguous share of every slab: one multimem.ld_reduce
+    // returns the sum of all ranks' partials, one multimem.st puts it into every rank's result buffer (all replicas receive
+    // the SAME bits, whatever order the switch adds in).  Then a second cross-GPU barrier (flag C) before anyone reads.
+    for (int f = 0; f < R.n_feds; ++f) {
+      const FedbFed& F = R.feds[f];
+      if (s_stop[f]) continue;
+      const int n4 = F.slab_size >> 2, per = (n4 + R.world - 1) / R.world, lo = R.rank * per, hi = min(n4, lo + per);
+      for (int e4 = lo + gtid; e4 < hi; e4 += gthreads) {
+        const float4 acc = multimem_ld_reduce_add_f4(R.nvls_mc_partial + (int64_t)par * R.global_total + F.global_off + 4 * e4);
+        multimem_st_f4(R.nvls_mc_result + F.global_off + 4 * e4, acc);
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+      atomicAdd(R.bar, 1u);
+      const uint32_t target = (uint32_t)((2 * seq + 2) * gridDim.x);
+      while ((int32_t)(ld_acquire_gpu_u32(R.bar) - target) < 0)
+        if (clock64() - t0 > R.timeout_cycles) { timed_out = true; break; }
+    }
+    __syncthreads();
+    if (blockIdx.x == 0 && tid < R.world) st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 16 + R.rank, seq + 1);
+    if (tid < R.world) {
+      while (ld_acquire_sys_u64(my_flags + 16 + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { timed_out = true; break; }
+    }
+    if (timed_out) *R.err = FEDB_E_TIMEOUT;
+    __syncthreads();
+  }
+  // ---- C: sum the partials of all ranks in rank order (or fetch the switch's sum); write global + every resident client ----
   for (int f = 0; f < R.n_feds; ++f) {
     const FedbFed& F = R.feds[f];
     if (s_stop[f]) continue;
     for (int e4 = gtid; e4 * 4 < F.slab_size; e4 += gthreads) {
       const int e = e4 * 4;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int q = 0; q < R.world; ++q) {
-        const float* pq = reinterpret_cast<const float*>(R.sym[q] + R.sym_partial_off) + (int64_t)par * R.global_total;
-        const float4 p = ld_relaxed_sys_f4(pq + F.global_off + e);
-        acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+      if (nvls) {
+        acc = ld_relaxed_sys_f4(R.nvls_uc_result + F.global_off + e);   // written by its owner rank through the multicast mapping
+      } else {
+        for (int q = 0; q < R.world; ++q) {
+          const float* pq = reinterpret_cast<const float*>(R.sym[q] + R.sym_partial_off) + (int64_t)par * R.global_total;
+          const float4 p = ld_relaxed_sys_f4(pq + F.global_off + e);
+          acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
       }
       *reinterpret_cast<float4*>(R.global + F.global_off + e) = acc;
       if (R.write_back) {

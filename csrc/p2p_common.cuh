@@ -29,4 +29,14 @@ __device__ __forceinline__ int ld_relaxed_sys_i32(const int32_t* p) {
   return v;
 }
 
+// NVLS: the address is a multicast mapping; the NVSwitch returns the element-wise sum over every GPU's copy / writes every copy
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 }  // namespace fedb

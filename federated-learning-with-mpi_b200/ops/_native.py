@@ -223,6 +223,12 @@ OPTIONAL_SIGS = {
     "fedb_local_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P], _I32),
     "fedb_tc_smem_bytes": ([], _I64),
     "fedb_tc_max_slab": ([], _I32),
+    "fedb_nvls_supported": ([_I32], _I32),
+    "fedb_nvls_create": ([_I32, _I64, _P, _P, _P], _I32),
+    "fedb_nvls_import": ([_I32, _P], _I32),
+    "fedb_nvls_add_device": ([_U64, _I32], _I32),
+    "fedb_nvls_bind_map": ([_U64, _I32, _I64, _P, _P, _P], _I32),
+    "fedb_nvls_release": ([_U64, _U64, _P, _P, _I64], _I32),
     "fedb_fit_cluster": ([_P, _I32, _I32, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _F64, _I32,
                           _I32, _I32, _I32, _U64, _I64, _P], _I32),
     "fedb_round_tc_p2p_hostin": ([_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P], _I32),
@@ -259,6 +265,7 @@ P2PRANK_DTYPE = np.dtype([
     ("hist_global", "u8"), ("conf_src_rank", "u8"), ("conf_src_slot", "u8"), ("sym", "u8", (8,)),
     ("sym_partial_off", "i8"), ("sym_conf_off", "i8"), ("sym_flag_off", "i8"), ("seq", "u8"), ("bar", "u8"), ("err", "u8"),
     ("timeout_cycles", "i8"), ("write_back", "i4"), ("do_metrics", "i4"), ("begin_next", "i4"), ("pad_", "i4"), ("shadow", "u8"),
+    ("nvls_uc_partial", "u8"), ("nvls_mc_partial", "u8"), ("nvls_uc_result", "u8"), ("nvls_mc_result", "u8"),
 ], align=True)
 
 

@@ -129,6 +129,17 @@ class DistFedEngine(FedEngine):
                                                 self.hist_local, self.hist_global, self.src_rank, self.src_slot, self.seq,
                                                 self.bar, self.err, g_total, timeout_s,
                                                 shadow=(self.wide.shadow if self.precision_name == "bf16_wide" else None))
+        # FEDB200_AGG=nvls: the ranks' partial sums live in multicast-bound memory and the NVSwitch adds them (parallel/nvls.py)
+        self._nvls = None
+        if os.environ.get("FEDB200_AGG") == "nvls" and world > 1 and self._symbuf is not None:
+            from . import nvls
+            if not nvls.supported():
+                raise RuntimeError("FEDB200_AGG=nvls: this device / driver does not support NVLink multicast")
+            self._nvls = nvls.NvlsBuffer(3 * self.global_total * 4, rank, world)      # partial[2][total] | result[total]
+            r = self.rank_record
+            r["nvls_uc_partial"], r["nvls_mc_partial"] = self._nvls.uc_ptr, self._nvls.mc_ptr
+            r["nvls_uc_result"] = self._nvls.uc_ptr + 2 * self.global_total * 4
+            r["nvls_mc_result"] = self._nvls.mc_ptr + 2 * self.global_total * 4
         self.rank_dev = K.upload_table(self.rank_record, d)
         self.p2p_blocks = p2p.blocks_for(self.tb.max_slab)
 
@@ -139,7 +150,7 @@ class DistFedEngine(FedEngine):
         """One federation with exactly one resident client on the tensor-core path: the whole multi-GPU
         round is ONE launch per rank (aggregation inside the round kernel, fedb_round_tc_p2p)."""
         return (self.precision_name == "bf16" and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
-                and os.environ.get("FEDB200_NO_FUSED_P2P") is None)
+                and os.environ.get("FEDB200_NO_FUSED_P2P") is None and getattr(self, "_nvls", None) is None)
 
     def _result_is_mirrored(self) -> bool:
         return self._fused_p2p_ok()
@@ -174,7 +185,7 @@ class DistFedEngine(FedEngine):
         if self.precision_name == "bf16_wide":
             return ["k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt", "k_fedavg_p2p", "k_wide_shadow"]
         local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
-        return local + ["k_fedavg_p2p"]
+        return local + ["k_fedavg_p2p[nvls multimem]" if self._nvls is not None else "k_fedavg_p2p"]
 
     def history(self) -> Dict[str, np.ndarray]:
         st = self.fed_state_host()
@@ -191,6 +202,10 @@ class DistFedEngine(FedEngine):
             raise RuntimeError(f"rank {self.rank}: a peer did not arrive at the aggregation barrier within the timeout")
 
     def close(self) -> None:
+        if getattr(self, "_nvls", None) is not None:
+            torch.cuda.synchronize()
+            self._nvls.close()
+            self._nvls = None
         if self._symbuf is not None:
             torch.cuda.synchronize()
             self._symbuf.close()

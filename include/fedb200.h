@@ -107,7 +107,8 @@ typedef struct FedbTile {
 /* Per-rank argument block of the cross-GPU aggregation kernel (fedb_fedavg_p2p).  All pointers are
  * device pointers valid on the launching GPU; sym[q] is rank q's symmetric buffer as mapped into
  * this process (CUDA IPC).  Symmetric buffer layout (bytes): partial[2][global_total] fp32 at
- * sym_partial_off, conf[2][8 source ranks][conf_slots][64] int32 at sym_conf_off, flags[16] u64 at sym_flag_off. */
+ * sym_partial_off, conf[2][8 source ranks][conf_slots][64] int32 at sym_conf_off, flags[24] u64 at sym_flag_off
+ * (arrival A, counts B, NVLS result C; one word per source rank each). */
 typedef struct FedbP2PRank {
   int32_t rank, world;
   int32_t n_feds, n_groups_local;
@@ -134,6 +135,12 @@ typedef struct FedbP2PRank {
   int32_t write_back, do_metrics;
   int32_t begin_next, pad_;
   void* shadow;                         /* optional bf16 arena (params layout) that receives the averaged weights too */
+  /* optional NVLS (NVLink-SHARP multicast) buffers, see fedb_nvls_*: when nvls_mc_partial is set, k_fedavg_p2p keeps the ranks'
+   * partial sums in multicast-bound memory and lets the NVSwitch add them (multimem.ld_reduce) instead of loading every peer */
+  float* nvls_uc_partial;               /* this GPU's copy: partial[2][global_total] */
+  float* nvls_mc_partial;               /* multicast view of the same */
+  float* nvls_uc_result;                /* this GPU's copy of the reduced global arena [global_total] */
+  float* nvls_mc_result;                /* multicast view: a multimem.st reaches every GPU's copy */
 } FedbP2PRank;
 
 /* Grouped tensor-core GEMM of the wide-MLP path (csrc/fedb_gemm.cu).  blockIdx.z = group (client);
@@ -324,6 +331,15 @@ int fedb_round_tc_p2p_hostin(const FedbGroup* groups, int32_t cluster_size, floa
  * multi-GPU use; R entries emulate R ranks on one GPU (tests).  Cooperative launch. */
 int32_t fedb_p2p_rank_size(void);
 int fedb_fedavg_p2p(const FedbP2PRank* ranks_dev, int32_t n_ranks_here, int32_t blocks_x, void* stream);
+/* NVLS plumbing (csrc/fedb_nvls.cu).  Rank 0 creates a multicast object for n_devices and exports it as a POSIX file descriptor
+ * (pass it to the other ranks with SCM_RIGHTS); they import it; every rank adds its device; after ALL have, every rank binds an
+ * allocation of *bytes_out bytes and gets two views of it: uc_ptr (own copy) and mc_ptr (multicast, multimem.* only). */
+int fedb_nvls_supported(int32_t device);   /* 1 / 0, negative on error */
+int fedb_nvls_create(int32_t n_devices, int64_t bytes, uint64_t* mc_handle_out, int32_t* fd_out, int64_t* bytes_out);
+int fedb_nvls_import(int32_t fd, uint64_t* mc_handle_out);
+int fedb_nvls_add_device(uint64_t mc_handle, int32_t device);
+int fedb_nvls_bind_map(uint64_t mc_handle, int32_t device, int64_t bytes, uint64_t* mem_handle_out, void** uc_ptr, void** mc_ptr);
+int fedb_nvls_release(uint64_t mc_handle, uint64_t mem_handle, void* uc_ptr, void* mc_ptr, int64_t bytes);
 /* Symmetric-memory plumbing: cudaMalloc'ed, zeroed buffer; 64-byte CUDA IPC handle out / in.
  * These four allocate / synchronise and are for set-up only. */
 int fedb_symm_alloc(int64_t bytes, void** out);

@@ -29,3 +29,23 @@ def test_two_gpu_bench_fused_and_standalone_aggregation_agree():
     assert any("k_fedavg_p2p" in k for k in sep["kernels"])
     assert sep["final_global_accuracy_train_shards"] == fused["final_global_accuracy_train_shards"]
     assert sep["rounds_run"] == fused["rounds_run"]
+
+
+def test_two_gpu_nvls_aggregation_matches_peer_loads():
+    """FEDB200_AGG=nvls: the NVSwitch adds the ranks' partial sums (multimem.ld_reduce) instead of peer loads in rank order.
+    Two addends commute, so with two ranks the trajectory must be identical to the P2P kernel's."""
+    import torch
+    sys.path.insert(0, ROOT)
+    from fedb200.parallel import nvls
+    if not nvls.supported(0):
+        pytest.skip("NVLink multicast is not supported on this device / driver")
+    ref = _bench(29543, {"FEDB200_NO_FUSED_P2P": "1"})
+    try:
+        got = _bench(29544, {"FEDB200_AGG": "nvls"})
+    except AssertionError as e:                      # e.g. no fabric manager / multicast not permitted inside this container
+        if "cuMulticast" in str(e) or "multicast" in str(e):
+            pytest.skip("the driver refused to create a multicast object here: " + str(e)[-300:])
+        raise
+    assert any("nvls" in k for k in got["kernels"])
+    assert got["rounds_run"] == ref["rounds_run"]
+    assert got["final_global_accuracy_train_shards"] == ref["final_global_accuracy_train_shards"]
