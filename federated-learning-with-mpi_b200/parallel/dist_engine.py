@@ -183,7 +183,8 @@ class DistFedEngine(FedEngine):
         if self._fused_p2p_ok():
             return ["k_local_round_tc[train+eval+p2p-fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
-            return ["k_gemm_tma[fwd|dgrad|wgrad+opt]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt", "k_fedavg_p2p", "k_wide_shadow"]
+            return ["k_gemm_tma2[fwd|dgrad]", "k_gemm_tma2p[wgrad+optimizer]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
+                    "k_fedavg_p2p[nvls multimem, +bf16 shadow]" if self._nvls is not None else "k_fedavg_p2p[+bf16 shadow]"]
         local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
         return local + ["k_fedavg_p2p[nvls multimem]" if self._nvls is not None else "k_fedavg_p2p"]
 
