@@ -9,6 +9,7 @@
 
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "tma_map.cuh"
 
 namespace fedb {
 namespace {
@@ -247,40 +248,6 @@ __global__ void __launch_bounds__(T_THREADS) k_gemm_tma(const __grid_constant__ 
 
 using namespace fedb;
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  }
-  return fn;
-}
-
-// 3-D bf16 tensor map {inner, rows, groups}; box {64, box_rows, 1}; 128-byte swizzle.
-static int make_map(CUtensorMap* m, const void* base, int64_t inner, int64_t rows, int64_t groups, int64_t ld, int64_t group_stride,
-                    int box_rows) {
-  EncodeTiledFn enc = get_encode();
-  if (!enc) return set_err(FEDB_E_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
-  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)groups};
-  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)(groups > 1 ? group_stride : ld * rows) * 2};
-  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled failed with CUresult %d (inner %lld rows %lld ld %lld)", (int)r, (long long)inner,
-             (long long)rows, (long long)ld);
-    return FEDB_E_CUDA;
-  }
-  return FEDB_OK;
-}
-
 extern "C" int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* stream) {
   const FedbGemm& p = *args_host;
   FEDB_REQUIRE(n_groups > 0 && p.M > 0 && p.N > 0 && p.K > 0, "bad GEMM sizes");
@@ -290,10 +257,7 @@ extern "C" int fedb_gemm_tma(const FedbGemm* args_host, int32_t n_groups, void* 
   FEDB_REQUIRE(((uintptr_t)p.A % 16) == 0 && ((uintptr_t)p.B % 16) == 0, "operands must be 16-byte aligned");
   alignas(64) CUtensorMap tmA, tmB;
   // K-major source [MN rows][K]: inner = K, box rows = 128 (MN).  MN-major source [K rows][MN]: inner = MN, box rows = 64 (K).
-  if (int rc = p.a_mn ? make_map(&tmA, p.A, p.M, p.K, n_groups, p.lda, p.a_group_stride, 64)
-                      : make_map(&tmA, p.A, p.K, p.M, n_groups, p.lda, p.a_group_stride, 128)) return rc;
-  if (int rc = p.b_mn ? make_map(&tmB, p.B, p.N, p.K, n_groups, p.ldb, p.b_group_stride, 64)
-                      : make_map(&tmB, p.B, p.K, p.N, n_groups, p.ldb, p.b_group_stride, 128)) return rc;
+  if (int rc = make_gemm_maps(p, n_groups, &tmA, &tmB)) return rc;
   static bool attr_set = false;
   const int tile_bytes = BM * TILE_LD * 4;
   const int smem = (STAGES * STAGE_BYTES > tile_bytes ? STAGES * STAGE_BYTES : tile_bytes) + 1024;

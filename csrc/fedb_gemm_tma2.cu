@@ -12,6 +12,7 @@
 
 #include "common.cuh"
 #include "pair_common.cuh"
+#include "tma_map.cuh"
 #include "tc_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -259,40 +260,13 @@ k_gemm_tma2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
 using namespace fedb;
 
-typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static int make_map2(CUtensorMap* m, const void* base, int64_t inner, int64_t rows, int64_t groups, int64_t ld, int64_t group_stride,
-                     int box_rows) {
-  static EncodeTiledFn2 enc = nullptr;
-  if (!enc) {
-    void* fp = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      enc = (EncodeTiledFn2)fp;
-  }
-  if (!enc) return set_err(FEDB_E_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
-  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)groups};
-  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)(groups > 1 ? group_stride : ld * rows) * 2};
-  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return set_err(FEDB_E_CUDA, "cuTensorMapEncodeTiled failed");
-  return FEDB_OK;
-}
-
 // err_dev: optional device int that receives FEDB_E_TIMEOUT if the pair's barrier protocol stalls.
 static int gemm_tma2_launch(const FedbGemm* args_host, int32_t n_groups, int32_t* err_dev, unsigned long long* prof_dev, void* stream) {
   const FedbGemm& p = *args_host;
   FEDB_REQUIRE(n_groups > 0 && p.M % 256 == 0 && p.N % 256 == 0 && p.K % 16 == 0 && p.K > 0, "2-CTA GEMM needs M % 256 == 0, N % 256 == 0, K % 16 == 0");
   FEDB_REQUIRE(p.lda % 8 == 0 && p.ldb % 8 == 0 && p.a_group_stride % 8 == 0 && p.b_group_stride % 8 == 0, "strides must be multiples of 8 elements");
   alignas(64) CUtensorMap tmA, tmB;
-  if (int rc = p.a_mn ? make_map2(&tmA, p.A, p.M, p.K, n_groups, p.lda, p.a_group_stride, 64)
-                      : make_map2(&tmA, p.A, p.K, p.M, n_groups, p.lda, p.a_group_stride, 128)) return rc;
-  if (int rc = p.b_mn ? make_map2(&tmB, p.B, p.N, p.K, n_groups, p.ldb, p.b_group_stride, 64)
-                      : make_map2(&tmB, p.B, p.K, p.N, n_groups, p.ldb, p.b_group_stride, 128)) return rc;
+  if (int rc = make_gemm_maps(p, n_groups, &tmA, &tmB)) return rc;
   static bool attr_set = false;
   if (!attr_set) {
     FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_gemm_tma2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<false>::SMEM));
