@@ -16,14 +16,12 @@ from __future__ import annotations
 import os
 
 import math
-from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
 import torch
 
 from ..models import init as minit
-from ..models.spec import MLPSpec
 from ..ops import _native as nat
 from ..ops import kernels as K
 from ..utils import trace

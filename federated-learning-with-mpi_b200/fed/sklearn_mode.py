@@ -21,7 +21,6 @@ from __future__ import annotations
 from typing import Dict, List, Optional
 
 import numpy as np
-import torch
 
 from ..models.checkpoint import weight_statistics
 from . import logging as flog

@@ -9,15 +9,13 @@ Selection rule as in H:114-119: first strictly greater pooled accuracy wins, in 
 """
 from __future__ import annotations
 
-from dataclasses import replace
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, List, Optional, Sequence
 
 import numpy as np
 
-from ..models.spec import MLPSpec
 from . import logging as flog
 from .engine import FedEngine
-from .problem import FedProblem, TrainHyper
+from .problem import FedProblem
 
 # H:73-74, in the reference's iteration order
 HIDDEN_GRID = [(50,), (100,), (50, 50), (100, 50), (50, 100), (50, 200), (50, 400), (100, 400), (400, 200), (200, 400)]

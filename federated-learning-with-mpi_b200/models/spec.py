@@ -21,7 +21,7 @@ transpose performed only at the I/O edge (checkpoint, parity tests).
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Dict, List, Sequence, Tuple
 
 import numpy as np

@@ -1,7 +1,6 @@
 """Grouped tensor-core GEMM (csrc/fedb_gemm.cu) — the building block of the wide-MLP path."""
 from __future__ import annotations
 
-import ctypes
 import os
 from typing import Optional
 

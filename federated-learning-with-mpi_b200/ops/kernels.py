@@ -9,7 +9,6 @@ with a GPU the native library is mandatory (ops/_native.lib raises if it is miss
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Optional
 
 import numpy as np
 import torch

@@ -18,7 +18,7 @@ import numpy as np
 import torch
 
 from ..models.init import philox4x32
-from ._native import (EVALJOB_DTYPE, FEDSTATE_DTYPE, LOSS_SLOTS, MAX_CLASSES, TILE_ROWS)
+from ._native import FEDSTATE_DTYPE, LOSS_SLOTS, MAX_CLASSES, TILE_ROWS
 
 F32 = np.float32
 

@@ -3,7 +3,7 @@ hardware probe used by tests/test_gpu_tc.py to validate the descriptor conventio
 from __future__ import annotations
 
 import ctypes
-from typing import List, Sequence
+from typing import Sequence
 
 import numpy as np
 import torch

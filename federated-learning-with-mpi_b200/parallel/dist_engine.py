@@ -288,7 +288,7 @@ class GlooFedEngine(FedEngine):
         self._group = dist.new_group(backend="gloo") if dist.get_backend() != "gloo" else None
 
     def enqueue_aggregate(self, write_back: bool = True, do_metrics: bool = True, begin_next: bool = False) -> None:
-        from ..fed.metrics import EarlyStop, mean_of_local, pooled
+        from ..fed.metrics import mean_of_local, pooled
         from ..ops import reference as ref
         dist, st = self._dist, self.fed_state.numpy().view(nat.FEDSTATE_DTYPE)
         # local weighted partial sums with the single-process kernel (no write-back, no metrics) ...
