@@ -41,3 +41,20 @@ def test_reference_arm_runs_unmodified_script_on_two_ranks():
     rec = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
     assert rec["impl"] == "reference" and rec["n_gpus"] == 2 and rec["value"] > 0
     assert 0.4 < rec["final_global_accuracy_train_shards"] <= 1.0
+
+
+def test_client_placement_and_symmetric_layout():
+    """Host-side bookkeeping of the multi-GPU engines: every client lands on exactly one rank in contiguous blocks, and the
+    symmetric buffer's regions are 256-byte aligned and do not overlap."""
+    from fedb200.parallel.dist_engine import place_clients
+    from fedb200.parallel.p2p import SymLayout, C2
+    for n, world in [(8, 8), (3, 2), (128, 8), (1024, 8), (5, 4)]:
+        blocks = place_clients(n, world)
+        flat = [k for b in blocks for k in b]
+        assert flat == list(range(n)) and len(blocks) == world
+        assert max(len(b) for b in blocks) - min(len(b) for b in blocks) <= 1
+    lay = SymLayout(global_total=11360, conf_slots=3)
+    assert lay.partial_off == 0 and lay.conf_off % 256 == 0 and lay.flag_off % 256 == 0
+    assert lay.conf_off >= 2 * lay.global_total * 4
+    assert lay.flag_off >= lay.conf_off + 2 * 8 * lay.conf_slots * C2 * 4
+    assert lay.nbytes >= lay.flag_off + 24 * 8          # flag words A, B (fused tail) and C (NVLS), one per source rank
