@@ -276,7 +276,7 @@ __device__ inline void begin_next_round(FedbFedState& S) {
 // (F is taken BY VALUE: through a pointer every field access may be re-fetched from L2 after each store)
 __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
                                           float* hist_local, float* hist_global, int* pool, bool begin_next = false,
-                                          FedbFedState* host_mirror = nullptr) {
+                                          FedbFedState* host_mirror = nullptr, void* host_result = nullptr) {
   const int lane = threadIdx.x & 31;
   const int C = F.n_classes;
   const int r = S.round - 1;  // 0-based index of the round in progress
@@ -319,13 +319,16 @@ __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int 
     if (begin_next) begin_next_round(st);
     S = st;
     if (host_mirror) {
-      // mapped pinned host memory: the round's result reaches the host without a memcpy node.  `done` is published last,
-      // behind a system-scope fence, so a host that polls it (FedEngine.step_e2e) never reads a half-written record.
-      FedbFedState t = st;
-      t.done = -1;
-      *host_mirror = t;
-      __threadfence_system();
-      *reinterpret_cast<volatile int32_t*>(&host_mirror->done) = st.done;
+      // mapped pinned host memory: the round's result reaches the host without a memcpy node (complete once the stream has
+      // synchronised).  A host that does not want to wait for the kernel to retire polls `host_result` instead: four 16-byte
+      // chunks {done, stop, metric i as a double}, each ONE store and so one write on the host link — every chunk carries the
+      // round counter, which makes it valid on its own; no system-scope fence (a ~2 us round trip) is needed to order them.
+      *host_mirror = st;
+      if (host_result) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          reinterpret_cast<int4*>(host_result)[i] = make_int4(st.done, st.stop, __double2loint(st.last[i]), __double2hiint(st.last[i]));
+      }
     }
   }
   __syncwarp();

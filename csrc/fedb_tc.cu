@@ -956,7 +956,8 @@ __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned
       for (int f = 0; f < a.n_feds; ++f) {
         if (s_stop[f]) continue;
         round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true,
-                           a.state_mirror ? a.state_mirror + f : nullptr);
+                           a.state_mirror ? a.state_mirror + f : nullptr,
+                           a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
       }
     __syncthreads();
     if (a.prof && tid == 0) a.prof[21] = clock64();
@@ -1041,7 +1042,7 @@ __device__ void p2p_tail(const TcArgs& a) {
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32 && R.do_metrics)
       round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true,
-                         a.state_mirror);
+                         a.state_mirror, a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) + 15) & ~size_t(15)) : nullptr);
     __syncthreads();
     for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) a.conf[i] = 0;
     if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;

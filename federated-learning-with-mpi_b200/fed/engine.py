@@ -211,7 +211,11 @@ class FedEngine:
         self.idx_epoch = self.idx.clone()
         self.tail_count = z(1, torch.int32)
         # mapped pinned host copy of the federation state: the fused round kernels store their result there too
-        self._state_pinned = torch.zeros(self.fed_state.numel(), dtype=torch.uint8).pin_memory() if d.type == "cuda" else None
+        # ... followed (next multiple of 16 bytes) by 4 self-validating 16-byte result chunks per federation, see include/fedb200.h
+        nst = self.fed_state.numel()
+        self._result_off = (nst + 15) // 16 * 16
+        self._mirror_full = torch.zeros(self._result_off + 64 * self.n_feds, dtype=torch.uint8).pin_memory() if d.type == "cuda" else None
+        self._state_pinned = self._mirror_full[:nst] if d.type == "cuda" else None
         self._e2e_cache: Dict = {}   # (x_host ptr, y_host ptr) -> (graph replay, stream sync, result view, buffers kept alive, done view)
         self._e2e_expect = -1        # value of `done` the next polled step will publish (-1: synchronise instead)
 
@@ -567,8 +571,8 @@ class FedEngine:
     def step_e2e(self, x_host: torch.Tensor, y_host: torch.Tensor) -> np.ndarray:
         """One round the way a caller that streams data would run it: upload this step's
         inputs from (pinned) host memory, run the round, read the round's result (federation
-        state: stop flag + the four global metrics) back to the host.  Returns the
-        ``FedbFedState`` records.  This mirrors what the reference does every round
+        state: stop flag + the four global metrics) back to the host.  Returns ``FedbFedState``
+        records whose ``done``, ``stop`` and ``last`` fields are current (copy them if you keep them).  This mirrors what the reference does every round
         (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic.
         On CUDA the uploads, the round and the read-back are ONE graph launch (captured per
         pair of host buffers), followed by one stream synchronisation.  When the round is a single
@@ -581,20 +585,26 @@ class FedEngine:
         ent = self._e2e_cache.get((x_host.data_ptr(), y_host.data_ptr())) if self._primed else None
         if ent is not None:
             ent[0]()                                     # one graph launch
-            done = ent[5]
-            if done is None or self._e2e_expect < 0:
+            chunks = ent[5]
+            if chunks is None or self._e2e_expect < 0:
                 ent[1]()                                 # stream synchronise
-            else:
-                # the round kernel publishes `done` last (system-scope fence) into mapped pinned memory: poll it instead of
-                # waiting for the whole kernel to retire, so the next launch overlaps this kernel's teardown
-                want, spins = self._e2e_expect, 0
-                while done[0] != want:
-                    spins += 1
-                    if spins > 4000:                     # stopped federation (no new round) or an unusually slow step
-                        ent[1]()
-                        break
-                self._e2e_expect = int(done[0]) + 1 if not ent[2]["stop"][0] else -1
-            return ent[2]
+                if chunks is not None:                   # (re-)arm the polled path on the state this round left behind
+                    self._e2e_expect = -1 if ent[2]["stop"][0] else int(ent[2]["done"][0]) + 1
+                return ent[2]
+            # the round kernel stores four self-validating 16-byte chunks {done, stop, metric} into mapped pinned memory: poll
+            # them instead of waiting for the whole kernel to retire, so the next launch overlaps this kernel's teardown
+            want, spins, d = self._e2e_expect, 0, chunks["done"]
+            while not (d[0] == want and d[1] == want and d[2] == want and d[3] == want):
+                spins += 1
+                if spins > 4000:                         # stopped federation (no new round) or an unusually slow step
+                    ent[1]()
+                    self._e2e_expect = -1 if ent[2]["stop"][0] else int(ent[2]["done"][0]) + 1
+                    return ent[2]
+            out = self._e2e_out
+            out["done"][0], out["stop"][0] = want, chunks["stop"][0]
+            out["last"][0] = chunks["val"]
+            self._e2e_expect = want + 1 if not out["stop"][0] else -1
+            return out
         self.prime()
         if self.device.type != "cuda":
             self.X[: self.n_train].copy_(x_host)
@@ -625,8 +635,10 @@ class FedEngine:
                 self._restore(snap)
             g = self._graphs[key + "x1"]
             poll = mirrored and self.n_feds == 1 and os.environ.get("FEDB200_E2E_SYNC") is None
-            self._e2e_cache[(x_host.data_ptr(), y_host.data_ptr())] = (g.replay, stream.synchronize, view, x_host, y_host,
-                                                                        view["done"] if poll else None)
+            chunks = self._mirror_full.numpy()[self._result_off: self._result_off + 64].view(
+                np.dtype([("done", "i4"), ("stop", "i4"), ("val", "f8")])) if poll else None
+            self._e2e_out = np.zeros(self.n_feds, dtype=nat.FEDSTATE_DTYPE)   # the polled path returns done / stop / last in here
+            self._e2e_cache[(x_host.data_ptr(), y_host.data_ptr())] = (g.replay, stream.synchronize, view, x_host, y_host, chunks)
             g.replay()
         else:
             body()

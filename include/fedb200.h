@@ -265,6 +265,9 @@ int fedb_local_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t clust
  * state_mirror (optional): mapped pinned HOST memory, n_feds records; the tail stores the updated
  * federation state there as well, so a host that syncs on the stream reads the round's result
  * without a device-to-host memcpy. */
+/* state_mirror (fedb_round_tc*, optional): mapped pinned host memory of n_feds FedbFedState records FOLLOWED, at the next multiple
+ * of 16 bytes, by n_feds x 4 chunks of 16 bytes {int32 done, int32 stop, double metric_i}.  The records are complete once the stream
+ * has synchronised; each chunk is a single store that carries the round counter, so a host may poll the chunks instead. */
 int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
                   const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                   const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
