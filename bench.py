@@ -184,8 +184,8 @@ def run_ours(args):
                        "(single-launch rounds: the round kernel reads them over the host link, one 64-byte request per row, and writes "
                        "them through to the device-resident X / y; other paths: two cudaMemcpyAsync nodes), the round runs, the "
                        "federation state (stop flag + 4 global metrics) is stored by the round kernel into mapped pinned host memory "
-                       "(a memcpy node + stream synchronise on the non-fused paths); the host polls that record's round counter, which the kernel "
-                       "publishes last behind a system-scope fence, and reads the state"},
+                       "(a memcpy node + stream synchronise on the non-fused paths) together with four self-validating 16-byte result chunks "
+                       "{round counter, stop flag, metric}; the host polls the chunks and reads the result"},
         "gpu_launches": K * eng.launches_per_round, "launches_per_step": eng.launches_per_round,
         "kernels": eng.kernel_names, "clocks": clk.summary(),
         "final_global_accuracy_train_shards": float(hist["last"][0][0]), "rounds_run": int(hist["rounds"][0]),
