@@ -41,7 +41,7 @@ def parse():
                     help="income = BASELINE config 3 (the headline; default); wide = BASELINE config 5 (4 x 4096 hidden, "
                          "synthetic income-shaped non-IID data, 1024 rows per client, SGD) — ours only")
     ap.add_argument("--width", type=int, default=4096)
-    ap.add_argument("--precision", default=None, help="ours: fp32 (SIMT) | tf32 (tcgen05); default = best available")
+    ap.add_argument("--precision", default=None, help="ours: fp32 (CUDA cores) | tc32 (tcgen05, split fp16 operands, fp32-grade; the default) | bf16 (tcgen05, bf16 operands)")
     ap.add_argument("--no-flush", action="store_true", help="debug: skip the L2 flush between timed steps")
     a = ap.parse_args()
     if a.clients_per_gpu is None:
@@ -172,7 +172,7 @@ def run_ours(args):
     rec.update({
         "value": value, "ms_per_step": ms_flushed / K,
         "vs_baseline": (value / BASELINE_SAMPLES_PER_SEC) if args.config == "income" else None,
-        "dtype": eng.precision_name, "rounds_per_sec": K / (ms_flushed / 1e3),
+        "dtype": eng.dtype_label, "precision": eng.precision_name, "rounds_per_sec": K / (ms_flushed / 1e3),
         "vs_baseline_rounds_per_sec": (K / (ms_flushed / 1e3)) / BASELINE_ROUNDS_PER_SEC,
         "warm_no_flush": {"ms_per_step": ms_warm / K, "client_samples_per_sec": samples * K / (ms_warm / 1e3),
                           "rounds_per_sec": K / (ms_warm / 1e3)},

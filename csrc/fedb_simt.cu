@@ -13,6 +13,8 @@
 //                 early stop)
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include <cuda_bf16.h>
 
@@ -778,16 +780,25 @@ extern "C" int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers) {
   return bytes <= cap ? bytes : -1;
 }
 
-// Opt in to >48 KB of dynamic shared memory once per function (always the 227 KB maximum, so the
-// call is not repeated inside a stream capture after the first, eager, launch).
+// Opt in to >48 KB of dynamic shared memory once per (device, function) — the attribute belongs to the device's context, so
+// a process that drives several GPUs needs it on each (always the 227 KB maximum, so the call is not repeated inside a
+// stream capture after the first, eager, launch).  The table is guarded: entry points may be called from several host threads.
 static int set_smem(const void* fn, int64_t bytes) {
-  static const void* done[8] = {nullptr};
+  constexpr int kDev = 64, kFn = 8;
+  static std::mutex mu;
+  static const void* done[kDev][kFn] = {{nullptr}};
   if (bytes <= 48 * 1024) return FEDB_OK;
-  for (int i = 0; i < 8; ++i) if (done[i] == fn) return FEDB_OK;
+  int dev = 0;
+  FEDB_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  const bool tracked = dev >= 0 && dev < kDev;
+  if (tracked)
+    for (int i = 0; i < kFn; ++i) if (done[dev][i] == fn) return FEDB_OK;
   cudaFuncAttributes fa;
   FEDB_CUDA_OK(cudaFuncGetAttributes(&fa, fn));   // static shared memory counts against the same 227 KB
   FEDB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
-  for (int i = 0; i < 8; ++i) if (done[i] == nullptr) { done[i] = fn; break; }
+  if (tracked)
+    for (int i = 0; i < kFn; ++i) if (done[dev][i] == nullptr) { done[dev][i] = fn; break; }
   return FEDB_OK;
 }
 
@@ -935,6 +946,7 @@ static __device__ __align__(256) float g_noalloc_scratch[FEDB_NOALLOC_SCRATCH_FL
 namespace {
 constexpr int kMaxDevices = 64;
 float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+std::mutex g_noalloc_mu;   // guards g_noalloc_ptr: the entry point may be entered from several host threads
 }  // namespace
 
 extern "C" int64_t fedb_noalloc_scratch_floats(void) { return (int64_t)FEDB_NOALLOC_SCRATCH_FLOATS; }
@@ -949,14 +961,23 @@ extern "C" int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbG
   FEDB_REQUIRE(ldx % 4 == 0, "ldx must be a multiple of 4");
   FEDB_REQUIRE(smem_bytes > 0 && smem_bytes <= 227 * 1024, "model too wide for the SIMT kernel (shared memory)");
   // The records of all groups must fit in the fixed array: check the host copy of the table.
-  int64_t need = 0;
+  // (The kernels index the array from the DEVICE table: groups_host must be byte-identical to it.)  A group's records must
+  // also cover every tile the kernels will touch: k_reduce_opt derives the tile count from n_rows / batch_size, not from
+  // max_tiles, so a table that reserves too few records would run past the group's range — and, for the last group, past
+  // the array.
+  int64_t need = 0, tiles_reserved = 0;
   for (int g = 0; g < n_groups; ++g) {
     const FedbGroup& G = groups_host[g];
-    if (G.scratch_off < 0 || G.max_tiles < 0 || G.slab_size <= 0)
+    if (G.scratch_off < 0 || G.max_tiles < 0 || G.slab_size <= 0 || G.n_rows <= 0)
       return set_err(FEDB_E_ARG, "fedb_local_step_noalloc: malformed group table");
+    const int rows_per_step = G.batch_size > 0 ? (G.batch_size < G.n_rows ? G.batch_size : G.n_rows) : G.n_rows;
+    if (G.max_tiles < (rows_per_step + FEDB_TILE_ROWS - 1) / FEDB_TILE_ROWS)
+      return set_err(FEDB_E_ARG, "fedb_local_step_noalloc: a group's max_tiles is smaller than the tiles of one step");
     const int64_t end = G.scratch_off + (int64_t)G.max_tiles * (G.slab_size + FEDB_LOSS_SLOTS);
     if (end > need) need = end;
+    tiles_reserved += G.max_tiles;
   }
+  if ((int64_t)n_tiles > tiles_reserved) return set_err(FEDB_E_ARG, "fedb_local_step_noalloc: more tiles than the groups reserve records for");
   if (need > (int64_t)FEDB_NOALLOC_SCRATCH_FLOATS) {
     snprintf(g_err, sizeof(g_err),
              "fedb_local_step_noalloc: this step needs %lld floats of gradient records but the built-in scratch holds "
@@ -967,14 +988,18 @@ extern "C" int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbG
   int dev = -1;
   FEDB_CUDA_OK(cudaGetDevice(&dev));
   FEDB_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
-  if (g_noalloc_ptr[dev] == nullptr) {
-    // Once per device, with that device current: translate the symbol into a device address.
-    float* p = nullptr;
-    FEDB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
-    FEDB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
-    g_noalloc_ptr[dev] = p;
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+      // Once per device, with that device current: translate the symbol into a device address.
+      float* p = nullptr;
+      FEDB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+      FEDB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
   }
-  float* scratch = g_noalloc_ptr[dev];
   // Nothing in the scratch has to start at zero: k_fwd_bwd overwrites every float of every record
   // (and its loss slot) that k_reduce_opt reads for the same step, so stale contents of an earlier
   // call are never observed.

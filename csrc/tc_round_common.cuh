@@ -1,0 +1,204 @@
+// Shared by the two fused round kernels (csrc/fedb_tc.cu: bf16 operands, 128-row tiles; csrc/fedb_tcx.cu: split fp16
+// operands, 64-row tiles): the argument block and the two aggregation tails that turn "every client has trained and
+// evaluated" into "the round is over" — single-GPU FedAvg by the last cluster to finish (round_tail), or the cross-GPU
+// exchange over NVLink peer memory by the client's own cluster (p2p_tail).
+#pragma once
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "p2p_common.cuh"
+
+namespace fedb {
+
+constexpr int TC_THREADS = 256;   // both round kernels run 8 warps per CTA
+
+struct TcArgs {
+  const FedbGroup* groups;
+  const float* X;
+  const int32_t* y;
+  // optional: this step's inputs in (pinned, device-visible) host memory, same layout as X / y.  The kernel then performs the
+  // host-to-device copy itself: rows are read over the host link and written through to X / y on their way to the X panel.
+  const float* x_host;
+  const int32_t* y_host;
+  const int32_t* idx;
+  float* params;
+  float* m;
+  float* v;
+  int32_t* step;
+  const int32_t* active;
+  const FedbFedState* fed_state;
+  float* loss_out;
+  int32_t* conf;
+  float* scratch;   // per-group gradient records (FedbGroup::scratch_off; >= cluster_size records each)
+  int ldx, batch, n_steps, do_eval;
+  long long* prof;  // optional: clock64 stamps of CTA 0 / thread 0 (debug, tools/tc_timeline.py)
+  // ---- fused round tail (tail_mode 1): the last cluster to finish aggregates every federation ----
+  int tail_mode, n_groups, n_feds, n_conf;
+  const FedbFed* feds;
+  FedbFedState* fed_state_rw;
+  float* global;
+  float* hist_local;
+  float* hist_global;
+  unsigned int* tail_count;   // wraps to 0 by itself (atomicInc)
+  // ---- fused cross-GPU aggregation (tail_mode 2): one federation, one resident client per rank ----
+  const FedbP2PRank* p2p;
+  FedbFedState* state_mirror;   // optional: mapped pinned host copy of the federation state, written by the tail
+};
+
+// K1 + K5 for small problems, executed by the last cluster to finish: FedAvg of every federation in
+// client order with the reference's arithmetic (C:108-116), write-back (C:119-120), metrics and early
+// stop (C:165-192), then the next round's begin bookkeeping — same results as k_fedavg.
+constexpr int TAIL_MAX_FEDS = 256, TAIL_MAX_CLIENTS = 32;
+
+static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop) {
+  const int tid = threadIdx.x;
+  __shared__ long long t_off[TAIL_MAX_CLIENTS];
+  __shared__ float t_num[TAIL_MAX_CLIENTS], t_den[TAIL_MAX_CLIENTS];
+  // the last CTA of the cluster scores the round (metrics need only the confusion counts) while the
+  // others average; with a single CTA it does both
+  const int mrank = csize - 1, workers = csize > 1 ? csize - 1 : 1;
+  const int nthr = workers * TC_THREADS, gt = crank * TC_THREADS + tid;
+  for (int f = 0; f < a.n_feds && (csize == 1 || crank != mrank); ++f) {
+    if (s_stop[f]) continue;
+    const FedbFed F = a.feds[f];
+    __syncthreads();
+    if (tid < F.n_clients) {
+      const FedbGroup* G = a.groups + F.first_group + tid;
+      t_off[tid] = G->slab_off; t_num[tid] = G->agg_num; t_den[tid] = G->agg_den;
+    }
+    __syncthreads();
+    const int n4 = F.slab_size >> 2;
+    for (int base = gt; base < n4; base += 4 * nthr) {
+      float4 acc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+      for (int k = 0; k < F.n_clients; ++k) {
+        const float num = t_num[k], den = t_den[k];
+        const float4* src = reinterpret_cast<const float4*>(a.params + t_off[k]);
+        float4 w[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (base + u * nthr < n4) w[u] = __ldcg(src + base + u * nthr);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (base + u * nthr < n4) {
+            acc[u].x += __fdiv_rn(__fmul_rn(w[u].x, num), den);
+            acc[u].y += __fdiv_rn(__fmul_rn(w[u].y, num), den);
+            acc[u].z += __fdiv_rn(__fmul_rn(w[u].z, num), den);
+            acc[u].w += __fdiv_rn(__fmul_rn(w[u].w, num), den);
+          }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e4 = base + u * nthr;
+        if (e4 < n4) {
+          reinterpret_cast<float4*>(a.global + F.global_off)[e4] = acc[u];
+          for (int k = 0; k < F.n_clients; ++k) reinterpret_cast<float4*>(a.params + t_off[k])[e4] = acc[u];
+        }
+      }
+    }
+  }
+  if (a.prof && crank == 0 && tid == 0) a.prof[20] = clock64();
+  if (crank == mrank) {
+    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+    if (tid < 32)
+      for (int f = 0; f < a.n_feds; ++f) {
+        if (s_stop[f]) continue;
+        round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true,
+                           a.state_mirror ? a.state_mirror + f : nullptr,
+                           a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
+      }
+    __syncthreads();
+    if (a.prof && tid == 0) a.prof[21] = clock64();
+    for (int i = tid; i < a.n_conf; i += TC_THREADS) a.conf[i] = 0;
+  }
+}
+
+// Cross-GPU FedAvg fused into the round kernel (one federation, one resident client per rank): the
+// protocol of k_fedavg_p2p (csrc/fedb_p2p.cu) executed by the client's own cluster.  The partial
+// (w * n_k) / N was published by the optimizer phase and flag A raised BEFORE the local evaluation, so
+// the NVLink latency hides behind it; here the confusion counts follow (flag B), every CTA but the last
+// sums the R partials in rank order with peer loads and writes the global model + the client's slab,
+// and the last CTA scores the round from all ranks' counts and does the next round's bookkeeping.
+static __device__ void p2p_tail(const TcArgs& a) {
+  cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+  const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x;
+  __shared__ FedbP2PRank R;
+  for (int i = tid; i < (int)(sizeof(FedbP2PRank) / 4); i += TC_THREADS)
+    reinterpret_cast<int32_t*>(&R)[i] = reinterpret_cast<const int32_t*>(a.p2p)[i];
+  __shared__ int s_timeout;
+  if (tid == 0) s_timeout = 0;
+  __syncthreads();
+  const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
+  const int par = (int)(seq & 1);
+  const bool stopped = R.fed_state[0].stop != 0;   // as it stands for THIS round
+  __threadfence();
+  cluster.sync();                                   // all CTAs: evaluation counts are in a.conf; seq / stop have been read
+  if (stopped) return;
+  const long long t0 = clock64();
+  const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
+  if (crank == 0) {   // PUSH this rank's confusion counts into every peer's area (parity, my rank), then flag B
+    const int nconf = R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+    for (int i = tid; i < nconf * R.world; i += TC_THREADS) {
+      const int qq = i / nconf, w = i - qq * nconf;
+      reinterpret_cast<int32_t*>(R.sym[qq] + R.sym_conf_off)[(par * 8 + R.rank) * conf_stride + w] = __ldcg(a.conf + w);
+    }
+    __syncthreads();
+    if (tid < R.world) {
+      __threadfence_system();
+      st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 8 + R.rank, seq + 1);
+    }
+  }
+  const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
+  if (CS == 1 || crank != mrank) {   // ---- aggregation: wait for every peer's partial (flag A), sum in rank order
+    if (tid < R.world)
+      while (ld_acquire_sys_u64(my_flags + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+    __syncthreads();
+    const FedbFed F = R.feds[0];
+    const FedbGroup* G = R.groups + F.first_group;
+    float4* slab = reinterpret_cast<float4*>(R.params + G->slab_off);
+    float4* glob = reinterpret_cast<float4*>(R.global + F.global_off);
+    const int n4 = F.slab_size >> 2;
+    for (int e4 = crank * TC_THREADS + tid; e4 < n4; e4 += workers * TC_THREADS) {
+      float4 pr[8];
+#pragma unroll
+      for (int qq = 0; qq < 8; ++qq)
+        if (qq < R.world)
+          pr[qq] = ld_relaxed_sys_f4(reinterpret_cast<const float*>(R.sym[qq] + R.sym_partial_off) + (int64_t)par * R.global_total + F.global_off + 4 * e4);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int qq = 0; qq < 8; ++qq)
+        if (qq < R.world) { acc.x += pr[qq].x; acc.y += pr[qq].y; acc.z += pr[qq].z; acc.w += pr[qq].w; }
+      glob[e4] = acc;
+      if (R.write_back) slab[e4] = acc;
+    }
+  }
+  if (crank == mrank) {              // ---- metrics from every rank's counts (flag B), early stop, next round's begin
+    if (tid < R.world)
+      while (ld_acquire_sys_u64(my_flags + 8 + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+    __syncthreads();
+    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) {
+      const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
+      const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
+      // the counts were pushed into THIS rank's buffer by their owners: a local read, no NVLink round trip
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + qq) * conf_stride;
+      R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
+    }
+    __syncthreads();
+    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+    if (tid < 32 && R.do_metrics)
+      round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true,
+                         a.state_mirror, a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) + 15) & ~size_t(15)) : nullptr);
+    __syncthreads();
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) a.conf[i] = 0;
+    if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
+  }
+  __syncthreads();
+  if (s_timeout && tid == 0) *R.err = FEDB_E_TIMEOUT;
+}
+
+}  // namespace fedb

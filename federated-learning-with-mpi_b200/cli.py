@@ -53,7 +53,9 @@ def build_parser() -> argparse.ArgumentParser:
     c.add_argument("--partition", default="per_client_shuffle", choices=["per_client_shuffle", "contiguous", "dirichlet"])
     c.add_argument("--dirichlet-alpha", type=float, default=0.5)
     c.add_argument("--weighting", default="samples", choices=["samples", "uniform"])
-    c.add_argument("--precision", default=None, choices=[None, "fp32", "bf16"])
+    c.add_argument("--precision", default=None, choices=[None, "fp32", "tc32", "bf16"],
+                   help="fp32 = CUDA-core kernels; tc32 = tensor cores with split fp16 operands (fp32-grade, default where the "
+                        "model fits); bf16 = tensor cores with bf16 operands")
     c.add_argument("--shared-init", action="store_true", help="all clients start from the same weights")
     c.add_argument("--resume", default=None, help="checkpoint to start from")
 
@@ -108,9 +110,9 @@ def cmd_custom(args) -> int:
                         seed=args.seed, precision=args.precision)
     if args.resume:
         eng.load_checkpoint(args.resume)
-    log = flog.RunLog(args.jsonl, quiet=args.quiet or rank != 0)
+    log = flog.RunLog(args.jsonl if rank == 0 else None, quiet=args.quiet or rank != 0)   # one writer per file
     t0 = time.perf_counter()
-    h = eng.run(args.rounds)
+    h = eng.run(args.rounds)          # ends with check_errors(): a timed-out peer raises here
     dt = time.perf_counter() - t0
     R = int(h["rounds"][0])
     for r in range(R):
@@ -123,8 +125,8 @@ def cmd_custom(args) -> int:
         print(f"\n[fedb200] {R} rounds in {dt:.3f} s ({R / max(dt, 1e-9):.1f} rounds/s, {eng.precision_name}); "
               f"held-out accuracy of the global model: {test['accuracy']:.4f}", flush=True)
         log.record(summary=True, rounds=R, seconds=dt, test=test)
-        if args.checkpoint:
-            eng.save_checkpoint(args.checkpoint, resume=True)
+    if args.checkpoint:
+        eng.save_checkpoint(args.checkpoint, resume=True)    # every rank: the optimizer state is gathered; rank 0 writes
     log.close()
     return 0
 

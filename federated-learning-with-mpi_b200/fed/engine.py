@@ -69,16 +69,20 @@ class FedEngine:
         self.init_params()
 
     def _select_precision(self) -> None:
-        """'fp32' = SIMT kernels; 'bf16' = fused tcgen05 local-round kernel (bf16 operands, fp32
-        accumulate / master weights / optimizer).  Default: bf16 when every model is eligible and
-        training is full-batch on a GPU, else fp32."""
+        """'fp32' = SIMT kernels; 'tc32' = fused tcgen05 round kernel with split fp16 operands (three MMAs per
+        GEMM, fp32-grade results: csrc/fedb_tcx.cu); 'bf16' = the same round with plain bf16 operands
+        (csrc/fedb_tc.cu; faster, 8 significant bits per operand); fp32 accumulation, master weights and
+        optimizer in all of them.  Default: tc32 when every model is eligible and training is full-batch on a
+        GPU, else fp32."""
         from ..ops import tc
         full_batch = all(p.hyper.batch_size <= 0 and p.hyper.max_iter <= 0 for p in self.problems)
         ok = self.device.type == "cuda" and full_batch and tc.tc_eligible(self.tb.groups)
+        ok32 = self.device.type == "cuda" and full_batch and tc.tc_eligible(self.tb.groups, "x2")
         req = self._precision_req
         self.wide = None
+        self.tc_variant = None
         if req in (None, "auto"):
-            req = "bf16" if ok else ("bf16_wide" if (self.tb.smem_bytes < 0 and self.device.type == "cuda") else "fp32")
+            req = "tc32" if ok32 else ("bf16_wide" if (self.tb.smem_bytes < 0 and self.device.type == "cuda") else "fp32")
         if req == "bf16_wide":
             from .wide import WideLocal
             if self.device.type != "cuda":
@@ -86,11 +90,19 @@ class FedEngine:
             self.precision_name = "bf16_wide"
             self._wide_pending = True
             return
-        if req in ("bf16", "tc", "tf32"):
+        if req in ("tc32", "fp32x2", "tf32", "tc"):
+            if not ok32:
+                raise ValueError("the tensor-core path needs a CUDA device, full-batch steps and 3-layer ReLU MLPs with "
+                                 "in<=15, h1<=63, h2<=256, out<=8")
+            self.precision_name = "tc32"
+            self.tc_variant = "x2"
+            self.tc_cluster = tc.tc_cluster_size(self.tb.groups, "x2")
+        elif req == "bf16":
             if not ok:
                 raise ValueError("the tensor-core path needs a CUDA device, full-batch steps and 3-layer ReLU MLPs with "
                                  "in<=15, h1<=63, h2<=256, out<=8")
             self.precision_name = "bf16"
+            self.tc_variant = "bf16"
             self.tc_cluster = tc.tc_cluster_size(self.tb.groups)
         elif req == "fp32":
             self.precision_name = "fp32"
@@ -284,7 +296,7 @@ class FedEngine:
     FUSED_TAIL_MAX_FLOATS = 1 << 20
 
     def _fused_round_ok(self) -> bool:
-        return (self.precision_name == "bf16" and type(self).enqueue_aggregate is FedEngine.enqueue_aggregate
+        return (self.tc_variant is not None and type(self).enqueue_aggregate is FedEngine.enqueue_aggregate
                 and self.params_total <= self.FUSED_TAIL_MAX_FLOATS and self.n_feds <= 256
                 and max(p.n_clients for p in self.problems) <= 32)
 
@@ -299,7 +311,7 @@ class FedEngine:
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
                         self.fed_state, self.loss, self.conf, self.scratch, E, self.global_, self.hist_local, self.hist_global,
-                        self.tail_count, state_mirror=self._state_pinned, host_inputs=host_inputs)
+                        self.tail_count, state_mirror=self._state_pinned, host_inputs=host_inputs, variant=self.tc_variant)
             return
         assert host_inputs is None, "host inputs are pulled by the single-launch round only"
         if not self._begin_is_fused():
@@ -319,10 +331,10 @@ class FedEngine:
             for _ in range(E):
                 self.wide.enqueue_step()
             self.wide.enqueue_eval()
-        elif self.precision_name == "bf16":
+        elif self.tc_variant is not None:
             from ..ops import tc
             tc.local_round_tc(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step,
-                              self.active, self.fed_state, self.loss, self.conf, self.scratch, 0, E, True)
+                              self.active, self.fed_state, self.loss, self.conf, self.scratch, 0, E, True, variant=self.tc_variant)
         else:
             for _ in range(E):
                 for b in range(self.n_batches):
@@ -336,7 +348,7 @@ class FedEngine:
             return 1
         if self.precision_name == "bf16_wide":
             return 1 + E * self.wide.launches_per_step + (self.wide.L - 1) + 1 + 1
-        if self.precision_name == "bf16":
+        if self.tc_variant is not None:
             return 3 if not self._begin_is_fused() else 2
         return 1 + 2 * E * self.n_batches + 2
 
@@ -371,6 +383,7 @@ class FedEngine:
                 self.enqueue_round()
                 if poll and bool(self.fed_state_host()["stop"].all()):
                     break
+            self.check_errors()
             return self.history()
         # Graph capture runs one warm-up round eagerly; snapshot and restore state around it so
         # capture itself is invisible to the training trajectory.
@@ -385,6 +398,7 @@ class FedEngine:
             left -= u
             if poll and bool(self.fed_state_host()["stop"].all()):
                 break
+        self.check_errors()
         return self.history()
 
     def _snapshot(self):
@@ -396,6 +410,22 @@ class FedEngine:
         for n, t in snap.items():
             getattr(self, n).copy_(t)
         self._e2e_expect = -1
+        self._sync_derived_state()
+
+    def _sync_derived_state(self) -> None:
+        """Bring every copy that is derived from ``params`` back in line after they were overwritten from outside a
+        kernel (snapshot restore, checkpoint load): the wide path's bf16 GEMM operands (``WideLocal.shadow``)."""
+        if self.precision_name == "bf16_wide" and self.wide is not None:
+            self.wide.refresh_shadow()
+
+    def check_errors(self) -> None:
+        """Raise if a kernel reported a failure through a device flag (CTA-pair GEMM pipeline stall on the wide path;
+        the multi-GPU engine adds the cross-GPU barrier timeout).  Synchronises the device."""
+        if self.precision_name == "bf16_wide":
+            from ..ops import gemm
+            rc = gemm.pair_status()
+            if rc != 0:
+                raise RuntimeError(f"a CTA-pair GEMM reported failure code {rc} (pipeline stall)")
 
     # ------------------------------------------------------------- sklearn-style local fit
     def reset_fit_state(self, keep_no_improvement: bool = False) -> None:
@@ -519,23 +549,50 @@ class FedEngine:
             out.append(metrics_from_confusion(confusion_matrix(y.cpu().numpy(), pred.cpu().numpy(), s.n_classes)))
         return out
 
+    def _client_opt_state(self, f: int) -> Dict[str, np.ndarray]:
+        """Optimizer state of the clients of federation ``f`` hosted here, rows in local client order."""
+        p = self.problems[f]
+        gs = self.group_of[f]
+        P = p.spec.slab_size
+        o = int(self.tb.groups[gs[0]]["slab_off"])
+        n = len(gs) * P
+        return {"m": self.m[o: o + n].view(len(gs), P).cpu().numpy(), "v": self.v[o: o + n].view(len(gs), P).cpu().numpy(),
+                "step": self.step[gs[0]: gs[0] + len(gs)].cpu().numpy(), "params": self.params[o: o + n].view(len(gs), P).cpu().numpy()}
+
+    def _gather_opt_state(self, f: int) -> Optional[Dict[str, np.ndarray]]:
+        """All clients' optimizer state in GLOBAL client order (single process: this one's; overridden by the multi-process
+        engines, where it is a collective and only rank 0 gets the result)."""
+        return self._client_opt_state(f)
+
     def save_checkpoint(self, path: str, f: int = 0, resume: bool = False) -> None:
+        """Write the global model of federation ``f`` in the coefs_/intercepts_ layout.  ``resume=True`` adds what an exact
+        continuation needs: every client's parameters, moments and step count (rows = global client index) and the
+        federation's round / early-stop state and metric history.  Under torchrun every rank must call this (the
+        optimizer state is gathered); rank 0 writes the file."""
         from ..models.checkpoint import save_checkpoint
         p = self.problems[f]
-        opt = None
+        opt, extras = None, {"name": p.name}
         if resume:
-            gs = self.group_of[f]
-            P = p.spec.slab_size
-            o = int(self.tb.groups[gs[0]]["slab_off"])
-            n = len(gs) * P
-            opt = {"m": self.m[o: o + n].view(len(gs), P), "v": self.v[o: o + n].view(len(gs), P),
-                   "step": self.step[gs[0]: gs[0] + len(gs)], "params": self.params[o: o + n].view(len(gs), P)}
-        save_checkpoint(path, p.spec, self.global_slab(f), int(self.fed_state_host()[f]["done"]),
-                        extras={"name": p.name}, opt_state=opt)
+            opt = self._gather_opt_state(f)
+            st = self.fed_state_host()[f]
+            fs = {k: (st[k].tolist() if st[k].ndim else int(st[k])) for k in nat.FEDSTATE_DTYPE.names}
+            # stored as it stands BETWEEN rounds, before the next round's begin bookkeeping (which the fused tails have
+            # already done at this point: undo it; the loader's first round_begin redoes it, stop promotion included)
+            fs["round"], fs["stop"] = fs["done"], 0
+            extras["fed_state"] = fs
+            if opt is not None:
+                R = int(st["done"])
+                h = self.history()
+                opt = dict(opt, hist_global=h["global"][f][:R].astype(np.float32), hist_local=h["local"][:R].astype(np.float32))
+        if getattr(self, "rank", 0) != 0:
+            return
+        save_checkpoint(path, p.spec, self.global_slab(f), int(self.fed_state_host()[f]["done"]), extras=extras,
+                        opt_state={k: torch.from_numpy(np.ascontiguousarray(v)) for k, v in opt.items()} if opt else None)
 
     def load_checkpoint(self, path: str, f: int = 0) -> Dict:
-        """Load global weights into every client slab of federation ``f`` (and optimizer state
-        when the file has it)."""
+        """Load global weights into every client slab of federation ``f``; when the file carries resume state, also each
+        resident client's own parameters / moments / step count (selected by global client index) and the federation's
+        round counter, early-stop anchor / patience count and metric history, so the run continues as if uninterrupted."""
         from ..models.checkpoint import load_checkpoint
         p = self.problems[f]
         spec, coefs, inter, meta, opt = load_checkpoint(path)
@@ -547,13 +604,35 @@ class FedEngine:
         gs = self.group_of[f]
         for k in range(len(gs)):
             self.client_slab(f, k).copy_(slab)
-        if opt:
+        if opt and "m" in opt:
             P, o = spec.slab_size, int(self.tb.groups[gs[0]]["slab_off"])
             n = len(gs) * P
-            self.m[o: o + n].copy_(torch.from_numpy(opt["m"]).reshape(-1))
-            self.v[o: o + n].copy_(torch.from_numpy(opt["v"]).reshape(-1))
-            self.params[o: o + n].copy_(torch.from_numpy(opt["params"]).reshape(-1))
-            self.step[gs[0]: gs[0] + len(gs)].copy_(torch.from_numpy(opt["step"]))
+            first = int(p.client_offset)
+            if opt["m"].shape[0] < first + len(gs):
+                raise ValueError(f"checkpoint holds optimizer state of {opt['m'].shape[0]} clients; this process hosts clients "
+                                 f"{first}..{first + len(gs) - 1}")
+            rows = slice(first, first + len(gs))
+            self.m[o: o + n].copy_(torch.from_numpy(np.ascontiguousarray(opt["m"][rows])).reshape(-1))
+            self.v[o: o + n].copy_(torch.from_numpy(np.ascontiguousarray(opt["v"][rows])).reshape(-1))
+            self.params[o: o + n].copy_(torch.from_numpy(np.ascontiguousarray(opt["params"][rows])).reshape(-1))
+            self.step[gs[0]: gs[0] + len(gs)].copy_(torch.from_numpy(np.ascontiguousarray(opt["step"][rows])))
+        fs = (meta.get("extras") or {}).get("fed_state")
+        if fs:
+            st = self.fed_state_host()
+            for k in nat.FEDSTATE_DTYPE.names:
+                st[f][k] = fs[k]
+            self.fed_state.copy_(torch.from_numpy(st.view(np.uint8).reshape(-1)).to(self.device))
+            self._primed = False          # the next round's begin bookkeeping is still to be done (see save_checkpoint)
+            self._e2e_expect = -1
+            R = int(fs["done"])
+            if opt and "hist_global" in opt and R:
+                hg = self.hist_global.view(self.n_feds, self.max_rounds, 4)
+                hl = self.hist_local.view(self.max_rounds, -1, 4)
+                r = min(R, self.max_rounds)
+                hg[f, :r].copy_(torch.from_numpy(opt["hist_global"][:r]))
+                if opt["hist_local"].shape[1] == hl.shape[1]:
+                    hl[:r].copy_(torch.from_numpy(opt["hist_local"][:r]))
+        self._sync_derived_state()
         return meta
 
     # ------------------------------------------------------------------ end-to-end stepping
@@ -659,17 +738,28 @@ class FedEngine:
 
     # ------------------------------------------------------------------- bench conveniences
     precision_name = "fp32"
+    tc_variant = None
+
+    @property
+    def tc_kernel(self) -> str:
+        return "k_round_tcx" if self.tc_variant == "x2" else "k_local_round_tc"
+
+    @property
+    def dtype_label(self) -> str:
+        """What the arithmetic of the training step is, for benchmark records."""
+        return {"tc32": "fp32 (operands split into 2 x fp16, 3 tcgen05 MMAs per GEMM; fp32 accumulate, weights, optimizer)",
+                "bf16": "bf16", "bf16_wide": "bf16", "fp32": "fp32"}[self.precision_name]
 
     @property
     def kernel_names(self) -> List[str]:
         """Kernels launched per steady-state round (the first round additionally runs k_round_begin)."""
         if self._fused_round_ok():
-            return ["k_local_round_tc[train+eval+fedavg+metrics]"]
+            return [f"{self.tc_kernel}[train+eval+fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
             return ["k_round_begin", "k_gemm_tma2[fwd+bias+relu|dgrad+mask] (k_gemm_tma off the 256-multiples)", "k_gemm_tma2p[wgrad+optimizer]",
                     "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt", "k_fedavg[+bf16 shadow]"]
-        if self.precision_name == "bf16":
-            return ["k_round_begin", "k_local_round_tc[train+eval]", "k_fedavg"]
+        if self.tc_variant is not None:
+            return ["k_round_begin", f"{self.tc_kernel}[train+eval]", "k_fedavg"]
         return ["k_round_begin", "k_fwd_bwd", "k_reduce_opt", "k_eval", "k_fedavg"]
 
     def step_graph(self) -> None:

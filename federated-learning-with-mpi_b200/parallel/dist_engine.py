@@ -149,7 +149,7 @@ class DistFedEngine(FedEngine):
     def _fused_p2p_ok(self) -> bool:
         """One federation with exactly one resident client on the tensor-core path: the whole multi-GPU
         round is ONE launch per rank (aggregation inside the round kernel, fedb_round_tc_p2p)."""
-        return (self.precision_name == "bf16" and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
+        return (self.tc_variant is not None and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
                 and os.environ.get("FEDB200_NO_FUSED_P2P") is None and getattr(self, "_nvls", None) is None)
 
     def _result_is_mirrored(self) -> bool:
@@ -164,7 +164,7 @@ class DistFedEngine(FedEngine):
             E = max(p.hyper.local_epochs for p in self.problems)
             tc.round_tc_p2p(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
                             self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, state_mirror=self._state_pinned,
-                            host_inputs=host_inputs)
+                            host_inputs=host_inputs, variant=self.tc_variant)
             return
         assert host_inputs is None, "host inputs are pulled by the single-launch round only"
         super().enqueue_round()
@@ -181,11 +181,11 @@ class DistFedEngine(FedEngine):
     @property
     def kernel_names(self) -> List[str]:
         if self._fused_p2p_ok():
-            return ["k_local_round_tc[train+eval+p2p-fedavg+metrics]"]
+            return [f"{self.tc_kernel}[train+eval+p2p-fedavg+metrics]"]
         if self.precision_name == "bf16_wide":
             return ["k_gemm_tma2[fwd|dgrad]", "k_gemm_tma2p[wgrad+optimizer]", "k_wide_head_fwd", "k_wide_head_bwd", "k_wide_bias_opt",
                     "k_fedavg_p2p[nvls multimem, +bf16 shadow]" if self._nvls is not None else "k_fedavg_p2p[+bf16 shadow]"]
-        local = ["k_local_round_tc[train+eval]"] if self.precision_name == "bf16" else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
+        local = [f"{self.tc_kernel}[train+eval]"] if self.tc_variant is not None else ["k_fwd_bwd", "k_reduce_opt", "k_eval"]
         return local + ["k_fedavg_p2p[nvls multimem]" if self._nvls is not None else "k_fedavg_p2p"]
 
     def history(self) -> Dict[str, np.ndarray]:
@@ -199,8 +199,22 @@ class DistFedEngine(FedEngine):
                 "metric_names": np.asarray(METRIC_NAMES)}
 
     def check_errors(self) -> None:
+        """The cross-GPU waits give up after ``timeout_s`` and raise a device flag instead of hanging (the reference
+        aborts the job on any exception, C:203-205): surface it."""
         if int(self.err.item()) != 0:
             raise RuntimeError(f"rank {self.rank}: a peer did not arrive at the aggregation barrier within the timeout")
+        super().check_errors()
+
+    def _gather_opt_state(self, f: int):
+        """Collective: every rank contributes its resident clients' rows; rank 0 returns them in global client order."""
+        import torch.distributed as dist
+        mine = (int(self.problems[f].client_offset), self._client_opt_state(f))
+        parts = [None] * self.world
+        dist.all_gather_object(parts, mine)
+        if self.rank != 0:
+            return None
+        parts.sort(key=lambda t: t[0])
+        return {k: np.concatenate([d[k] for _, d in parts]) for k in parts[0][1]}
 
     def close(self) -> None:
         if getattr(self, "_nvls", None) is not None:
@@ -335,6 +349,8 @@ class GlooFedEngine(FedEngine):
                         st[f]["anchor"], st[f]["has_anchor"], st[f]["count"] = gv, 1, p.patience
                 st[f]["done"] = st[f]["round"]
             g_base += p.n_clients
+
+    _gather_opt_state = DistFedEngine._gather_opt_state
 
     def history(self) -> Dict[str, np.ndarray]:
         st = self.fed_state_host()

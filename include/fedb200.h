@@ -274,6 +274,49 @@ int fedb_round_tc(const FedbGroup* groups, int32_t n_groups, int32_t cluster_siz
                   int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
                   float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror, void* stream);
 
+/* The same launches with an optional trace buffer: prof (may be null) = 32 int64 on the device that receive clock64 stamps of
+ * CTA 0 / thread 0 at the phase boundaries (tools/tc_timeline.py lists them).  The bindings call these forms. */
+int fedb_local_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
+                             const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                             const int32_t* active, const FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                             float* scratch, int32_t batch, int32_t n_steps, int32_t do_eval, long long* prof, void* stream);
+int fedb_round_tc_prof(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
+                       const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                       const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
+                       int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
+                       float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror,
+                       long long* prof, void* stream);
+/* Largest slab (floats) the bf16 round kernel accepts (gradient slices of a cluster must fit one CTA's exchange area). */
+int32_t fedb_tc_max_slab(void);
+/* Hardware probe behind tests/test_gpu_tc.py: a chain of M = 128 tcgen05.mma on operand images laid out by the host; args_host
+ * is the int32 block ops/tc.py:probe() fills (fedb_tc_probe_args_size() bytes).  Synchronises nothing; not a hot path. */
+int fedb_tc_probe(const void* a_img, const void* b_img, const int32_t* args_host, float* out, void* stream);
+int fedb_tc_probe_args_size(void);
+
+/* K2a/K3 at fp32-grade accuracy on tcgen05 (csrc/fedb_tcx.cu): every operand is held as two fp16 numbers (hi + lo, 22
+ * significant bits) and every GEMM is three MMAs into the same fp32 accumulator; the reference trains in fp32 (C:65, C:69-72).
+ * Tiles are 64 rows, cluster_size 1..16 (fedb_tcx_max_cluster(): 16 where the device can co-schedule a 16-CTA cluster, else
+ * 8).  Same model limits as the bf16 kernel; arguments as fedb_local_round_tc_prof / fedb_round_tc_hostin /
+ * fedb_round_tc_p2p_hostin respectively. */
+int64_t fedb_tcx_smem_bytes(void);
+int32_t fedb_tcx_max_slab(void);
+int32_t fedb_tcx_rows(void);
+int32_t fedb_tcx_max_cluster(void);
+int fedb_local_round_tcx(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
+                         const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                         const int32_t* active, const FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                         float* scratch, int32_t batch, int32_t n_steps, int32_t do_eval, long long* prof, void* stream);
+int fedb_round_tcx(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                   const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v,
+                   int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                   float* scratch, int32_t n_steps, const FedbFed* feds, int32_t n_feds, float* global, float* hist_local,
+                   float* hist_global, int32_t conf_ints, uint32_t* tail_count, FedbFedState* state_mirror, long long* prof,
+                   void* stream);
+int fedb_round_tcx_p2p(const FedbGroup* groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y, const float* x_host,
+                       const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
+                       const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
+                       int32_t n_steps, const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream);
+
 /* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
  * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
 int32_t fedb_gemm_args_size(void);
@@ -363,17 +406,21 @@ int fedb_ipc_close_handle(void* p);
  * library until the process exits.  The call performs no cudaMalloc/cudaFree and uses no allocating
  * library routine.
  *
- * groups_host is a host copy of the table at groups_dev; it is used to check that every group's
- * records (scratch_off + max_tiles * (slab_size + FEDB_LOSS_SLOTS)) fit in the array.  A step that
- * needs more returns FEDB_E_UNSUPPORTED with an explanatory fedb_last_error(); nothing is launched.
+ * groups_host is a host copy of the table at groups_dev and must match it byte for byte (the
+ * kernels index the array from the device table); it is used to check that every group's records
+ * (scratch_off + max_tiles * (slab_size + FEDB_LOSS_SLOTS)) fit in the array, that max_tiles covers
+ * the tiles of one step (ceil(min(batch_size or n_rows, n_rows) / FEDB_TILE_ROWS)) and that n_tiles
+ * does not exceed the records reserved.  A step that needs more room returns FEDB_E_UNSUPPORTED, a
+ * malformed table FEDB_E_ARG, each with an explanatory fedb_last_error(); nothing is launched.
  *
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
  * that device current) and remembers it; make that first call outside any stream capture.
  * All calls on a device share the one array and it keeps whatever the last call left in it.  The
  * step does not rely on its initial contents (every record it reads is written first), but two
  * calls whose kernels can overlap on the GPU — different streams, or different host threads — race
- * on it: serialise them on one stream.  Results are bit-identical to fedb_fwd_bwd + fedb_reduce_opt
- * with a caller-provided buffer (batch_stats is not produced). */
+ * on it: serialise them on one stream.  (Host threads may enter concurrently; only the GPU work
+ * must not overlap.)  Results are bit-identical to fedb_fwd_bwd + fedb_reduce_opt with a
+ * caller-provided buffer (batch_stats is not produced). */
 int64_t fedb_noalloc_scratch_floats(void);
 int fedb_local_step_noalloc(const FedbGroup* groups_host, const FedbGroup* groups_dev, int32_t n_groups,
                             const FedbTile* tiles, int32_t n_tiles, int32_t max_slab, float* params, float* m,

@@ -1,6 +1,6 @@
 """Phase timeline of k_local_round_tc from in-kernel clock64 stamps (CTA 0, thread 0).
 
-    python tools/tc_timeline.py [rows_per_client] [clients]
+    python tools/tc_timeline.py [rows_per_client] [clients] [tc32|bf16]
 """
 import sys
 
@@ -18,14 +18,15 @@ NAMES = ["start", "weights+row loaded", "X stored", "fwd1 mma", "epi1 (H1)", "fw
 if __name__ == "__main__":
     rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
     clients = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    PREC = sys.argv[3] if len(sys.argv) > 3 else "tc32"
     d = prepare()
     shards = [np.arange(c * rows, (c + 1) * rows, dtype=np.int32) % 8000 for c in range(clients)]
-    e = FedEngine([FedProblem.custom(14, 2, shards, patience=0)], d.X_train, d.y_train, device="cuda", max_rounds=8, precision="bf16")
+    e = FedEngine([FedProblem.custom(14, 2, shards, patience=0)], d.X_train, d.y_train, device="cuda", max_rounds=8, precision=PREC)
     prof = torch.zeros(32, dtype=torch.int64, device="cuda")
     for it in range(3):
         prof.zero_()
         tc.local_round_tc(e.tb, e.tc_cluster, e.X, e.y, e.idx, e.params, e.m, e.v, e.step, e.active, e.fed_state, e.loss, e.conf,
-                          e.scratch, 0, 1, True, prof)
+                          e.scratch, 0, 1, True, prof, variant=e.tc_variant)
         torch.cuda.synchronize()
     p = prof.cpu().numpy()
     t0 = p[0]
