@@ -97,6 +97,10 @@ def cmd_custom(args) -> int:
     prob = FedProblem.custom(data.n_features, data.n_classes, shards, hidden=tuple(args.hidden), hyper=hyper, patience=args.patience,
                              atol=args.tolerance, weighting=args.weighting, init_seed=args.seed, init_per_client=not args.shared_init)
     world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    max_rounds = args.rounds
+    if args.resume:                      # --rounds counts the rounds still to run: make room for the history so far
+        from .models.checkpoint import load_checkpoint
+        max_rounds += int(load_checkpoint(args.resume)[3].get("round", 0))
     if world > 1:
         import torch
         from .parallel.dist_engine import DistFedEngine, GlooFedEngine, init_distributed
@@ -104,9 +108,9 @@ def cmd_custom(args) -> int:
         init_distributed("nccl" if on_gpu else "gloo")
         Engine = DistFedEngine if on_gpu else GlooFedEngine       # NVLink kernels / CPU plumbing (BASELINE config 1)
         eng = Engine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
-                     max_rounds=args.rounds, seed=args.seed, precision=args.precision)
+                     max_rounds=max_rounds, seed=args.seed, precision=args.precision)
     else:
-        eng = FedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, device=args.device, max_rounds=args.rounds,
+        eng = FedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, device=args.device, max_rounds=max_rounds,
                         seed=args.seed, precision=args.precision)
     if args.resume:
         eng.load_checkpoint(args.resume)

@@ -4,6 +4,7 @@ import json
 import os
 
 import numpy as np
+import torch
 import pytest
 
 from fedb200 import FedEngine, FedProblem, make_shards
@@ -78,11 +79,36 @@ def test_cli_custom_checkpoint_and_resume(tmp_path, capsys):
     out = capsys.readouterr().out
     assert "Global Metrics (Round 3)" in out and "RANK 1 - Local Metrics (Round 1)" in out
     spec, coefs, inter, meta, opt = load_checkpoint(ck)
-    assert spec.dims == (14, 50, 200, 2) and meta["round"] == 3 and set(opt) == {"m", "v", "step", "params"}
+    assert spec.dims == (14, 50, 200, 2) and meta["round"] == 3
+    assert set(opt) == {"m", "v", "step", "params", "hist_global", "hist_local"} and opt["m"].shape[0] == 2
+    assert meta["extras"]["fed_state"]["done"] == 3 and meta["extras"]["fed_state"]["round"] == 3
     recs = [json.loads(l) for l in open(jl)]
     assert len(recs) == 4 and recs[-1]["summary"]
     assert cli_main(["custom", "--clients", "2", "--rounds", "1", "--device", "cpu", "--resume", ck, "--quiet",
                      "--synthetic-rows", "600"]) == 0
+
+
+def test_resume_continues_exactly(tmp_path, income):
+    """3 rounds + checkpoint + 3 more rounds in a fresh engine == 6 rounds in one go: weights, moments, step counts, the
+    early-stop anchor / patience count and the metric history all carry over (resume dropped the federation state)."""
+    from fedb200 import FedEngine, FedProblem, make_shards
+    mk = lambda: FedEngine([FedProblem.custom(14, 2, make_shards("contiguous", 600, 3), hidden=(8, 12), patience=10)],
+                           income.X_train[:600], income.y_train[:600], income.X_test, income.y_test, device="cpu", max_rounds=8)
+    whole, first, second = mk(), mk(), mk()
+    whole.run(6)
+    first.run(3)
+    ck = str(tmp_path / "r.npz")
+    first.save_checkpoint(ck, resume=True)
+    second.load_checkpoint(ck)
+    h = second.run(3)
+    assert int(h["rounds"][0]) == 6
+    for name in ("params", "m", "v", "step", "global_"):
+        assert torch.equal(getattr(second, name), getattr(whole, name)), name
+    a, b = whole.fed_state_host()[0], second.fed_state_host()[0]
+    for k in ("round", "done", "count", "has_anchor", "stop", "stop_pending"):
+        assert a[k] == b[k], k
+    assert np.array_equal(a["anchor"], b["anchor"]) and np.array_equal(whole.history()["global"], h["global"])
+    assert np.array_equal(whole.history()["local"], h["local"])
 
 
 def test_cli_sklearn_and_tune_smoke(capsys):
