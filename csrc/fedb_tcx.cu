@@ -8,7 +8,7 @@
 //     A B  ~=  A_lo B_hi + A_hi B_lo + A_hi B_hi  (the dropped A_lo B_lo term is 2^-22 of the product).
 // The reference trains in fp32 (C:65, C:69-72) and its early-stop rule compares metrics at atol 1e-4 (C:181-192); with
 // bf16 operands the accuracy keeps jittering and the rule fires ~100 rounds late.  tests/test_gpu_tcx.py bounds this
-// kernel's gradients against the fp32 SIMT kernels at 1e-5 of each layer's scale.
+// kernel's gradients against float64 and the fp32 SIMT kernels at 1e-5 of each layer's scale (measured: 2e-6).
 //
 // Range management (fp16 has 5 exponent bits): weights are held scaled by WS = 16 and the accumulators descaled on
 // read-out; the loss gradient travels through the backward GEMMs multiplied by DZS = 32 and WITHOUT the 1/n factor
@@ -19,8 +19,22 @@
 // 0..63; the MMAs still run at M = 128 and the upper 64 accumulator lanes hold don't-care values computed from
 // whatever follows the 64-row panel in shared memory), a cluster of up to 16 CTAs (non-portable size, one GPC) owns a
 // client.  Panels are [64 rows][64 fp16] with the hardware 128-byte swizzle (csrc/tc_common.cuh); hi and lo panels of
-// an operand are separate, except where an operand is <= 16 columns wide and both fit one panel side by side (X, W1,
-// dZ3) — there a single MMA with N = 32 (or 16) against the [hi | lo] panel yields both products at once.
+// an operand are separate, except where an operand is <= 16 columns wide and both halves fit one panel side by side
+// (X, W1, dZ3 — the last one shares X's panel) — there a single MMA with N = 32 (or 16) yields both products at once.
+// 16 warps: warp w reaches TMEM lanes 32 (w % 4) .. +31, so the data rows (lanes 0..63) are served by the eight warps
+// with w % 4 < 2, four per row ("parts": each takes a quarter of the columns of every epilogue).
+//
+// Cross-CTA exchange (per optimizer step), all by bulk asynchronous copies between the CTAs' shared memories
+// (cp.async.bulk.shared::cluster.shared::cta, completion counted on the RECEIVER's mbarrier) — no cluster barrier:
+//   reduce-scatter  every CTA drains its weight-gradient accumulators from TMEM into a staging area laid out by OWNER
+//                   (CTA o owns W2 rows [o R2, (o+1) R2) with their b2 / W3 entries, W1 rows of block CS-1-o and, for
+//                   o = CS-1, b3 and the loss) and sends block o to CTA o: one copy per peer;
+//   optimizer       the owner adds the CS partials in rank order (bit-reproducible), updates master weights / moments in
+//                   global memory and writes the new values straight into ITS OWN operand panels as split fp16;
+//   all-gather      ... and copies those panel rows (whole 128-byte rows, so the swizzle is irrelevant) into every peer's
+//                   panels at the same offsets.
+// Hazards are excluded by the protocol itself: a CTA sends partials only after its MMAs are done, an owner publishes
+// only after it has every partial, and nobody starts the next step before it has every published row.
 //
 // Shapes: 2 hidden ReLU layers, in <= 15, h1 <= 63, h2 <= 256, out <= 8 (the custom script's 14-50-200-2, C:40).
 #include <cooperative_groups.h>
@@ -36,33 +50,51 @@ namespace cg = cooperative_groups;
 namespace fedb {
 namespace {
 
+constexpr int XT = 512;           // threads per CTA
 constexpr int XR = 64;            // data rows per tile
 constexpr int XP = XR * 128;      // bytes of a [64][64] fp16 panel
 constexpr float WS = 16.f, INV_WS = 1.f / 16.f;   // weight panels hold WS * w
 constexpr float DZS = 32.f;                        // backward operands hold DZS * n * (true gradient)
 constexpr float HMAX = 60000.f;                    // activation clamp (fp16 max 65504)
 // shared-memory map (bytes from the 1024-aligned base)
-constexpr int SX_X = 0;                      // cols 0-15 X hi (col 15 = 1), cols 16-31 X lo
-constexpr int SX_DZ3 = SX_X + XP;            // cols 0-7 dZ3 hi, cols 8-15 dZ3 lo
-constexpr int SX_H1 = SX_DZ3 + XP;           // H1 hi, H1 lo; later dZ1 hi, dZ1 lo
+constexpr int SX_X = 0;                      // cols 0-15 X hi (col 15 = 1), 16-31 X lo, 32-39 dZ3 hi, 40-47 dZ3 lo
+constexpr int SX_H1 = SX_X + XP;             // H1 hi, H1 lo; later dZ1 hi, dZ1 lo
 constexpr int SX_Z = SX_H1 + 2 * XP;         // hi panels 0..3, lo panels 0..3: H2, then dZ2
 constexpr int SX_W1 = SX_Z + 8 * XP;         // [64][64]: cols 0-15 W1 hi (col 15 = b1), cols 16-31 lo
 constexpr int SX_W2 = SX_W1 + 64 * 128;      // hi [256][64] (col 63 = b2)
 constexpr int SX_W2L = SX_W2 + 256 * 128;    // lo
-constexpr int SX_W3 = SX_W2L + 256 * 128;    // fp32 [8][256]
-constexpr int SX_B3 = SX_W3 + 8 * 256 * 4;   // fp32 [8]
+constexpr int SX_W3 = SX_W2L + 256 * 128;    // fp32 [256 units][8 classes]
+constexpr int SX_B3 = SX_W3 + 256 * 8 * 4;   // fp32 [8]
 constexpr int SX_END = SX_B3 + 256;
-constexpr int SX_SLOTS = SX_END;              // [CS][per] float4 partial-gradient slices + CS loss floats
+constexpr int SX_SLOTS = SX_END;              // [CS senders][share] floats: the partials this CTA owns
 constexpr int SX_SLOTS_MAX = 227 * 1024 - 4096 - SX_SLOTS;
-constexpr int SX_STAGE = SX_H1;               // fp32 slab landing zone overlays H1..Z (idle at those points)
+constexpr int SX_STAGE = SX_H1;               // outgoing partials [CS owners][share] (and the fp32 slab at launch) overlay H1..Z
+constexpr int SX_STAGE_MAX = 10 * XP;
+constexpr int DZ3_COL = 32;                   // first column of [dZ3 hi | dZ3 lo] inside the X panel
 // TMEM columns
 constexpr uint32_t TX_D1 = 0, TX_D2 = 64, TX_DW2 = 320, TX_DW1 = 448, TX_DW3 = 480;
-constexpr uint32_t TX_ZX = TX_D1;             // logit exchange between the two column halves (D1 is dead at that point)
+constexpr uint32_t TX_ZX = TX_D1;             // 4 x 8 partial logits per row (D1 is dead at that point)
 
 struct ShapeX {
   int d0, h1, h2, C, N2, MT2;
   int ld0, ld1, ld2;
+  int w_off0, b_off0, w_off1, b_off1, w_off2, b_off2, end;   // slab offsets (floats)
 };
+
+// Who owns what in the cross-CTA exchange, and the layout of one (sender, owner) block:
+//   [R2 records of recf floats: W2 row (ld1) | b2, dW3[0..2] (C <= 3)  or  b2, 0, 0, 0 | dW3[0..7] (C > 3)]
+//   [R1 records of 16 floats: W1 row, column 15 = b1]   [16 floats: db3[0..7], loss sum, 0...]   (only owner CS-1 uses the last)
+struct OwnX {
+  int R2, R1, recf, share;   // share: floats per block (multiple of 4)
+};
+__host__ __device__ inline OwnX own_geometry(int h1, int h2, int C, int CS) {
+  OwnX o;
+  o.R2 = (h2 + CS - 1) / CS;
+  o.R1 = (h1 + CS - 1) / CS;
+  o.recf = ru4(h1) + 4 + (C > 3 ? 8 : 0);
+  o.share = o.R2 * o.recf + o.R1 * 16 + 16;
+  return o;
+}
 
 // kind::f16 instruction descriptor with fp16 (not bf16) operands, fp32 accumulation
 __host__ __device__ constexpr uint32_t idesc_f16(int M, int N, bool a_mn, bool b_mn) {
@@ -91,21 +123,36 @@ __device__ __forceinline__ void st_panel8(uint8_t* hi_panel, uint8_t* lo_panel, 
   *reinterpret_cast<uint4*>(lo_panel + off) = lo;
 }
 
-// distributed shared memory by 32-bit shared::cluster addresses (no 64-bit pointer per peer in registers)
+// ---- distributed shared memory by 32-bit shared::cluster addresses --------------------------------------------
 __device__ __forceinline__ uint32_t mapa(uint32_t saddr, int rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
   return r;
 }
-__device__ __forceinline__ void st_cluster_f4(uint32_t a, const float4 v) {
-  asm volatile("st.shared::cluster.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+// bytes [src, src + n) of THIS CTA's shared memory -> shared::cluster address dst; completion (n bytes) is counted on the
+// mbarrier at shared::cluster address bar (the receiver's).  n: multiple of 16, addresses 16-byte aligned.
+__device__ __forceinline__ void bulk_s2c(uint32_t dst_cluster, uint32_t src_cta, uint32_t n, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
+               "r"(src_cta), "r"(n), "r"(bar_cluster)
+               : "memory");
 }
-__device__ __forceinline__ void st_cluster_u2(uint32_t a, const uint32_t x, const uint32_t y) {
-  asm volatile("st.shared::cluster.v2.u32 [%0], {%1,%2};" ::"r"(a), "r"(x), "r"(y) : "memory");
+__device__ __forceinline__ void mbar_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void st_cluster_f1(uint32_t a, const float x) {
-  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(a), "f"(x) : "memory");
+// wait with cluster-scope acquire: the data counted on the barrier was written by other CTAs' bulk copies
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(done)
+        : "r"(tc::smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
 }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 __device__ __forceinline__ void bulk_load_begin_x(uint8_t* dst, const float* src, uint32_t bytes, uint64_t* wbar) {
   asm volatile("fence.proxy.async;" ::: "memory");
@@ -115,132 +162,120 @@ __device__ __forceinline__ void bulk_load_begin_x(uint8_t* dst, const float* src
                : "memory");
 }
 
-// W1 (+ b1 in column 15) from the fp32 landing zone into the [hi | lo] panel; b2 into column 63 of the W2 panels
-__device__ __forceinline__ void convert_w1_b2(uint8_t* sm, const float* L, const SlabLayout& lay, const ShapeX& s, int tid) {
-  {
-    const int q = tid & 3, nq = s.ld0 >> 2;
-    for (int j = tid >> 2; j < s.h1; j += TC_THREADS / 4) {
-      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (q < nq) w = *reinterpret_cast<const float4*>(L + lay.w_off[0] + j * s.ld0 + 4 * q);
-      if (q == 3) w.w = L[lay.b_off[0] + j];   // column 15 carries the bias (d0 <= 15: the slab has padding there)
-      uint32_t h0, l0, h1, l1;
-      split2(w.x * WS, w.y * WS, h0, l0);
-      split2(w.z * WS, w.w * WS, h1, l1);
-      *reinterpret_cast<uint2*>(sm + SX_W1 + tc::panel_off(j, 4 * q)) = make_uint2(h0, h1);
-      *reinterpret_cast<uint2*>(sm + SX_W1 + tc::panel_off(j, 16 + 4 * q)) = make_uint2(l0, l1);
-    }
-  }
-  for (int j = tid; j < s.h2; j += TC_THREADS) {
-    const float b = L[lay.b_off[1] + j] * WS;
-    const __half h = __float2half_rn(b);
-    *reinterpret_cast<__half*>(sm + SX_W2 + tc::panel_off(j, 63)) = h;
-    *reinterpret_cast<__half*>(sm + SX_W2L + tc::panel_off(j, 63)) = __float2half_rn(b - __half2float(h));
-  }
+// One W2 row segment (4 columns) / one W1 row segment / one b2 entry -> split fp16 in this CTA's panels
+__device__ __forceinline__ void put_w2(uint8_t* sm, int j, int col, const float4 w) {
+  uint32_t h0, l0, h1, l1;
+  split2(w.x * WS, w.y * WS, h0, l0);
+  split2(w.z * WS, w.w * WS, h1, l1);
+  const uint32_t off = tc::panel_off(j, col);
+  *reinterpret_cast<uint2*>(sm + SX_W2 + off) = make_uint2(h0, h1);
+  *reinterpret_cast<uint2*>(sm + SX_W2L + off) = make_uint2(l0, l1);
+}
+__device__ __forceinline__ void put_w1(uint8_t* sm, int i, int col, const float4 w) {   // col in {0, 4, 8, 12}
+  uint32_t h0, l0, h1, l1;
+  split2(w.x * WS, w.y * WS, h0, l0);
+  split2(w.z * WS, w.w * WS, h1, l1);
+  *reinterpret_cast<uint2*>(sm + SX_W1 + tc::panel_off(i, col)) = make_uint2(h0, h1);
+  *reinterpret_cast<uint2*>(sm + SX_W1 + tc::panel_off(i, 16 + col)) = make_uint2(l0, l1);
+}
+__device__ __forceinline__ void put_b2(uint8_t* sm, int j, float b) {
+  b *= WS;
+  const __half h = __float2half_rn(b);
+  *reinterpret_cast<__half*>(sm + SX_W2 + tc::panel_off(j, 63)) = h;
+  *reinterpret_cast<__half*>(sm + SX_W2L + tc::panel_off(j, 63)) = __float2half_rn(b - __half2float(h));
 }
 
 // whole slab (fp32 landing zone) -> operand image; once per launch
-__device__ void convert_weights_x(uint8_t* sm, const float* L, const SlabLayout& lay, const ShapeX& s) {
+__device__ void convert_weights_x(uint8_t* sm, const float* L, const ShapeX& s) {
   const int tid = threadIdx.x;
   {  // W2 [h2][ld1]: 16 lanes walk one row
-    const int q = tid & 15, jr = tid >> 4, nq = s.ld1 >> 2;
-    for (int j = jr; j < s.h2; j += TC_THREADS / 16) {
-      if (q < nq) {
-        const float4 w = *reinterpret_cast<const float4*>(L + lay.w_off[1] + j * s.ld1 + 4 * q);
-        uint32_t h0, l0, h1, l1;
-        split2(w.x * WS, w.y * WS, h0, l0);
-        split2(w.z * WS, w.w * WS, h1, l1);
-        const uint32_t off = tc::panel_off(j, 4 * q);
-        *reinterpret_cast<uint2*>(sm + SX_W2 + off) = make_uint2(h0, h1);
-        *reinterpret_cast<uint2*>(sm + SX_W2L + off) = make_uint2(l0, l1);
-      }
+    const int q = tid & 15, nq = s.ld1 >> 2;
+    for (int j = tid >> 4; j < s.h2; j += XT / 16)
+      if (q < nq) put_w2(sm, j, 4 * q, *reinterpret_cast<const float4*>(L + s.w_off1 + j * s.ld1 + 4 * q));
+  }
+  {  // W1 [h1][ld0] (+ b1 into column 15)
+    const int q = tid & 3, nq = s.ld0 >> 2;
+    for (int i = tid >> 2; i < s.h1; i += XT / 4) {
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (q < nq) w = *reinterpret_cast<const float4*>(L + s.w_off0 + i * s.ld0 + 4 * q);
+      if (q == 3) w.w = L[s.b_off0 + i];   // d0 <= 15: column 15 is free for the bias
+      put_w1(sm, i, 4 * q, w);
     }
   }
-  convert_w1_b2(sm, L, lay, s, tid);
-  {  // W3 [C][ld2] -> fp32 [C][256], b3
-    const int nq = s.ld2 >> 2;
-    for (int k = 0; k < s.C; ++k)
-      for (int q = tid; q < nq; q += TC_THREADS)
-        *reinterpret_cast<float4*>(sm + SX_W3 + (k * 256 + 4 * q) * 4) = *reinterpret_cast<const float4*>(L + lay.w_off[2] + k * s.ld2 + 4 * q);
-    if (tid < s.C) reinterpret_cast<float*>(sm + SX_B3)[tid] = L[lay.b_off[2] + tid];
+  for (int j = tid; j < s.h2; j += XT) {
+    put_b2(sm, j, L[s.b_off1 + j]);
+    float* w3 = reinterpret_cast<float*>(sm + SX_W3) + j * 8;
+    for (int k = 0; k < s.C; ++k) w3[k] = L[s.w_off2 + k * s.ld2 + j];
   }
+  if (tid < s.C) reinterpret_cast<float*>(sm + SX_B3)[tid] = L[s.b_off2 + tid];
   tc::fence_async_smem();
   __syncthreads();
 }
 
+// Row threads: columns 4 part .. 4 part + 3 of data row `pos` (global -> registers; issued early)
 struct RowRegsX {
-  float4 q[2];
+  float4 q;
   int label;
 };
-// Row threads: column half h of data row `pos` (global -> registers; issued early so the latency overlaps other work)
-__device__ __forceinline__ RowRegsX fetch_row_x(const TcArgs& a, int64_t pos, bool valid, int half) {
+__device__ __forceinline__ RowRegsX fetch_row_x(const TcArgs& a, int64_t pos, bool valid, int part) {
   RowRegsX r;
   r.label = 0;
-  r.q[0] = r.q[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.q = make_float4(0.f, 0.f, 0.f, 0.f);
   if (valid) {
     const int row = __ldg(a.idx + pos);
-    const float4* src = reinterpret_cast<const float4*>(a.X + (size_t)row * a.ldx) + 2 * half;
-    r.q[0] = __ldg(src);
-    r.q[1] = __ldg(src + 1);
+    r.q = __ldg(reinterpret_cast<const float4*>(a.X + (size_t)row * a.ldx) + part);
     r.label = __ldg(a.y + row);
   }
   return r;
 }
-// Host-input mode (TcArgs::x_host): four lanes fetch one whole 64-byte row from pinned host memory with one instruction
-// (tools/host_pull_bench.cu: the request size is what matters over the host link); 64 rows x 4 lanes = the whole CTA.
-struct HostRegsX {
-  float4 v;
-  int grow, label;
-};
-__device__ __forceinline__ HostRegsX host_fetch_x(const TcArgs& a, int64_t pos0, int nvalid, int tid) {
-  HostRegsX h;
-  const int rl = tid >> 2, c = tid & 3;
-  h.v = make_float4(0.f, 0.f, 0.f, 0.f);
-  h.grow = -1;
-  h.label = 0;
-  if (rl < nvalid) {
-    const int row = __ldg(a.idx + pos0 + rl);
-    h.grow = row;
-    h.v = __ldcv(reinterpret_cast<const float4*>(a.x_host + (size_t)row * a.ldx) + c);
-    if (c == 0) h.label = __ldcv(a.y_host + row);
-  }
-  return h;
-}
-// ... handed to the row threads through shared memory (the H1 panels, idle at that point) and written through to X / y
-__device__ __forceinline__ RowRegsX host_deliver_x(uint8_t* sm, const TcArgs& a, const HostRegsX& h, int tid, int row, int half, bool rowt) {
+// Host-input mode (TcArgs::x_host): the tile's rows come from pinned host memory, 64 bytes per row in one request by four
+// neighbouring lanes (tools/host_pull_bench.cu: the request size is what matters over the host link), written through
+// to the device-resident X / y.  Threads 0..255 fetch (row t / 4, chunk t % 4) — which is exactly what row thread
+// (row, part) needs, so the hand-over goes through shared memory (the H1 panel, idle at that point).
+__device__ __forceinline__ RowRegsX host_rows_x(uint8_t* sm, const TcArgs& a, int64_t pos0, int nvalid, int tid, int row, int part, bool rowt) {
   float* stage = reinterpret_cast<float*>(sm + SX_H1);           // 64 rows x 16 floats, then 64 labels
   int* stage_lab = reinterpret_cast<int*>(sm + SX_H1 + XR * 64);
-  const int rl = tid >> 2, c = tid & 3;
-  *reinterpret_cast<float4*>(stage + rl * 16 + 4 * c) = h.v;
-  if (c == 0) stage_lab[rl] = h.label;
-  if (h.grow >= 0) {
-    *(reinterpret_cast<float4*>(const_cast<float*>(a.X) + (size_t)h.grow * a.ldx) + c) = h.v;
-    if (c == 0) const_cast<int32_t*>(a.y)[h.grow] = h.label;
+  if (tid < 4 * XR) {
+    const int rl = tid >> 2, c = tid & 3;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    int label = 0;
+    if (rl < nvalid) {
+      const int grow = __ldg(a.idx + pos0 + rl);
+      v = __ldcv(reinterpret_cast<const float4*>(a.x_host + (size_t)grow * a.ldx) + c);
+      *(reinterpret_cast<float4*>(const_cast<float*>(a.X) + (size_t)grow * a.ldx) + c) = v;
+      if (c == 0) {
+        label = __ldcv(a.y_host + grow);
+        const_cast<int32_t*>(a.y)[grow] = label;
+      }
+    }
+    *reinterpret_cast<float4*>(stage + rl * 16 + 4 * c) = v;
+    if (c == 0) stage_lab[rl] = label;
   }
   __syncthreads();
   RowRegsX r;
   r.label = 0;
-  r.q[0] = r.q[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.q = make_float4(0.f, 0.f, 0.f, 0.f);
   if (rowt) {
-    r.q[0] = *reinterpret_cast<const float4*>(stage + row * 16 + 8 * half);
-    r.q[1] = *reinterpret_cast<const float4*>(stage + row * 16 + 8 * half + 4);
+    r.q = *reinterpret_cast<const float4*>(stage + row * 16 + 4 * part);
     r.label = stage_lab[row];
   }
   __syncthreads();   // the stage area is the H1 panel: everyone has read before anyone's epilogue writes it
   return r;
 }
-__device__ __forceinline__ int store_row_x(uint8_t* sm, const RowRegsX& r, bool valid, const ShapeX& s, int row, int half) {
-  float f[8] = {r.q[0].x, r.q[0].y, r.q[0].z, r.q[0].w, r.q[1].x, r.q[1].y, r.q[1].z, r.q[1].w};
+__device__ __forceinline__ void store_row_x(uint8_t* sm, const RowRegsX& r, bool valid, const ShapeX& s, int row, int part) {
+  float f[4] = {r.q.x, r.q.y, r.q.z, r.q.w};
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
-    if (8 * half + i >= s.d0) f[i] = 0.f;
-  if (half == 1) f[7] = valid ? 1.f : 0.f;   // column 15: the bias input
-  uint4 hi, lo;
-  split8(f, hi, lo);
-  *reinterpret_cast<uint4*>(sm + SX_X + tc::panel_off(row, 8 * half)) = hi;
-  *reinterpret_cast<uint4*>(sm + SX_X + tc::panel_off(row, 16 + 8 * half)) = lo;
-  return r.label;
+  for (int i = 0; i < 4; ++i)
+    if (4 * part + i >= s.d0) f[i] = 0.f;
+  if (part == 3) f[3] = valid ? 1.f : 0.f;   // column 15: the bias input
+  uint32_t h0, l0, h1, l1;
+  split2(f[0], f[1], h0, l0);
+  split2(f[2], f[3], h1, l1);
+  *reinterpret_cast<uint2*>(sm + SX_X + tc::panel_off(row, 4 * part)) = make_uint2(h0, h1);
+  *reinterpret_cast<uint2*>(sm + SX_X + tc::panel_off(row, 16 + 4 * part)) = make_uint2(l0, l1);
 }
 
+// epilogue -> next MMA hand-off: my TMEM reads are done, my smem writes are visible to the tensor core
 __device__ __forceinline__ void handoff_x() {
   tc::tmem_ld_wait();
   tc::tc_fence_before();
@@ -271,40 +306,35 @@ struct IssuerX {
   }
   __device__ __forceinline__ void wgrad3(const ShapeX& s, bool acc) const {   // DW3[j][0..7 | 8..15] = H2^T [dZ3 hi | dZ3 lo]
     const uint32_t id = idesc_f16(128, 16, true, true);
+#pragma unroll 1
+    for (int mt = 0; mt < s.MT2; ++mt) {
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
-      if (mt < s.MT2) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          tc::mma_bf16(tmem + TX_DW3 + 16 * mt, md(SX_Z + (4 + 2 * mt) * XP + 2048 * k), md(SX_DZ3 + 2048 * k), id, acc || k > 0);
-          tc::mma_bf16(tmem + TX_DW3 + 16 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), md(SX_DZ3 + 2048 * k), id, true);
-        }
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t b = md(SX_X + 2 * DZ3_COL + 2048 * k);
+        tc::mma_bf16(tmem + TX_DW3 + 16 * mt, md(SX_Z + (4 + 2 * mt) * XP + 2048 * k), b, id, acc || k > 0);
+        tc::mma_bf16(tmem + TX_DW3 + 16 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), b, id, true);
       }
+    }
   }
   __device__ __forceinline__ void dgrad2_wgrad2(const ShapeX& s, bool acc) const {
     const uint32_t id4 = idesc_f16(128, 64, false, true);   // dH1 = dZ2 W2
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (64 * p + 16 * k < s.N2) {   // never feed unwritten pad columns of the last panel
-          const int wrow = (p * 64 + 16 * k) * 128;
-          tc::mma_bf16(tmem + TX_D1, kd(SX_Z + (4 + p) * XP + 32 * k), md(SX_W2 + wrow), id4, (p | k) > 0);
-          tc::mma_bf16(tmem + TX_D1, kd(SX_Z + p * XP + 32 * k), md(SX_W2L + wrow), id4, true);
-          tc::mma_bf16(tmem + TX_D1, kd(SX_Z + p * XP + 32 * k), md(SX_W2 + wrow), id4, true);
-        }
+#pragma unroll 1
+    for (int c = 0; c < (s.N2 >> 4); ++c) {   // 16 columns of dZ2 per step; never feeds unwritten pad columns
+      const int p = c >> 2, k = c & 3, wrow = c * 16 * 128;
+      tc::mma_bf16(tmem + TX_D1, kd(SX_Z + (4 + p) * XP + 32 * k), md(SX_W2 + wrow), id4, c > 0);
+      tc::mma_bf16(tmem + TX_D1, kd(SX_Z + p * XP + 32 * k), md(SX_W2L + wrow), id4, true);
+      tc::mma_bf16(tmem + TX_D1, kd(SX_Z + p * XP + 32 * k), md(SX_W2 + wrow), id4, true);
     }
     const uint32_t id5 = idesc_f16(128, 64, true, true);    // dW2 += dZ2^T H1
+#pragma unroll 1
+    for (int mt = 0; mt < s.MT2; ++mt) {
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
-      if (mt < s.MT2) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + (4 + 2 * mt) * XP + 2048 * k), md(SX_H1 + 2048 * k), id5, acc || k > 0);
-          tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), md(SX_H1 + XP + 2048 * k), id5, true);
-          tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), md(SX_H1 + 2048 * k), id5, true);
-        }
+      for (int k = 0; k < 4; ++k) {
+        tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + (4 + 2 * mt) * XP + 2048 * k), md(SX_H1 + 2048 * k), id5, acc || k > 0);
+        tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), md(SX_H1 + XP + 2048 * k), id5, true);
+        tc::mma_bf16(tmem + TX_DW2 + 64 * mt, md(SX_Z + 2 * mt * XP + 2048 * k), md(SX_H1 + 2048 * k), id5, true);
       }
+    }
   }
   __device__ __forceinline__ void wgrad1(bool acc) const {   // DW1[i][0..15 | 16..31] = dZ1^T [X hi | X lo]
     const uint32_t id = idesc_f16(128, 32, true, true);
@@ -316,32 +346,39 @@ struct IssuerX {
   }
 };
 
+// One float4 "unit" of an owner's share: which four slab entries it updates and where the new values go in the operand image.
+struct UnitX {
+  int kind;     // 0 nothing | 1 W2 row segment | 2 [b2, W3[0..2]] | 3 W3[k0..k0+3] | 4 W1 row segment (column 15 = b1) | 5 b3 | 6 loss
+  int r, c;     // row (j or i) and column / class offset
+  int e[4];     // slab indices (-1: lane unused); kind 1: e[0] is the float4-aligned start
+  int wmask;    // lanes that are weights (L2 applies)
+};
+
 }  // namespace
 
-// Thread mapping: 8 warps.  Warp w reaches TMEM lanes 32 (w % 4) .. +31.  Data rows live in lanes 0..63, so the "row
-// threads" of the forward / backward epilogues are warps 0, 1 (column half 0) and 4, 5 (column half 1); all eight warps
-// take part in the weight-gradient read-out (lanes = output features), the optimizer and the weight conversion.
-__device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw) {
-  __shared__ uint64_t bar, wbar;
+// Returns true when the optimizer phase has already produced the FedAvg result (single-client federation on one GPU:
+// global = (w n) / n written by the owners, C:110-115), so the tail only scores the round.
+__device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw) {
+  __shared__ uint64_t bar, wbar, gbar, pbar;   // MMA done | slab landed | partials in | published rows in
   __shared__ uint32_t tmem_slot;
   __shared__ float red_f[2][9];   // per-warp partial sums: loss + db3[8]
   __shared__ int cnt[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
   __shared__ StepScalars sc_s;
+  __shared__ FedbGroup Gs;
 
   cg::cluster_group cluster = cg::this_cluster();
   const int CS = (int)cluster.num_blocks(), q = (int)cluster.block_rank();
   const int g = blockIdx.x / CS;
-  __shared__ FedbGroup Gs;
   if (threadIdx.x < sizeof(FedbGroup) / 4)
     reinterpret_cast<int32_t*>(&Gs)[threadIdx.x] = reinterpret_cast<const int32_t*>(a.groups + g)[threadIdx.x];
   __syncthreads();
   const FedbGroup& G = Gs;
-  if (a.active && !a.active[g]) return;                     // cluster-uniform exits
-  if (a.fed_state && a.fed_state[G.fed].stop) return;
+  if (a.active && !a.active[g]) return false;                     // cluster-uniform exits
+  if (a.fed_state && a.fed_state[G.fed].stop) return false;
   const int n = G.n_rows;
   const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
   const int b0 = a.batch * bs;
-  if (b0 >= n) return;
+  if (b0 >= n) return false;
   const int nb = min(bs, n - b0);
   const int ntiles = (nb + XR - 1) / XR;
 
@@ -353,95 +390,70 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
   s.d0 = G.dims[0]; s.h1 = G.dims[1]; s.h2 = G.dims[2]; s.C = G.dims[3];
   s.N2 = (s.h2 + 15) & ~15; s.MT2 = (s.N2 + 127) >> 7;
   s.ld0 = ru4(s.d0); s.ld1 = ru4(s.h1); s.ld2 = ru4(s.h2);
-  const SlabLayout lay = slab_layout(G.dims, 3);
+  {
+    const SlabLayout lay = slab_layout(G.dims, 3);
+    s.w_off0 = lay.w_off[0]; s.b_off0 = lay.b_off[0]; s.w_off1 = lay.w_off[1]; s.b_off1 = lay.b_off[1];
+    s.w_off2 = lay.w_off[2]; s.b_off2 = lay.b_off[2]; s.end = lay.end;
+  }
+  const OwnX own = own_geometry(s.h1, s.h2, s.C, CS);
+  const int share4 = own.share >> 2;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lane128 = (warp & 3) * 32 + lane;   // this thread's TMEM lane
-  const int half = warp >> 2;
+  const int part = warp >> 2;                   // column quarter
   const bool rowt = (warp & 2) == 0;            // owns data row `lane128` (< 64) in the forward / backward epilogues
   const int row = lane128;
   const int step0 = a.step[g];
   float* Pg = a.params + G.slab_off;
-  // gradient exchange geometry: CTA o owns float4 indices [o*per, (o+1)*per) of the slab
-  const int n4 = lay.end >> 2, per = (n4 + CS - 1) / CS;
-  const uint32_t inv_per = 0xFFFFFFFFu / (uint32_t)per + 1u;   // e4 / per == __umulhi(e4, inv_per) for e4 < 2^16
-  const int lo = q * per, hi = min(n4, lo + per);
 
+  // single-GPU, single-client federation: the owners write the FedAvg result themselves
+  const bool inline_avg = a.tail_mode == 1 && gridDim.x == (unsigned)CS && a.n_feds == 1 && a.feds[0].n_clients == 1;
   uint64_t p2p_seq = 0;
-  float* p2p_partial = nullptr;
+  float* avg_out = nullptr;    // where (w n_k) / N goes on the last step: the peers' fetch area, or the global arena
   if (a.tail_mode == 2) {
     p2p_seq = *reinterpret_cast<volatile uint64_t*>(a.p2p->seq);
-    p2p_partial = reinterpret_cast<float*>(a.p2p->sym[a.p2p->rank] + a.p2p->sym_partial_off) + (p2p_seq & 1) * a.p2p->global_total;
+    avg_out = reinterpret_cast<float*>(a.p2p->sym[a.p2p->rank] + a.p2p->sym_partial_off) + (p2p_seq & 1) * a.p2p->global_total;
+  } else if (inline_avg) {
+    avg_out = a.global + a.feds[0].global_off;
   }
-  float* landing = reinterpret_cast<float*>(sm + SX_STAGE);
-  float4* slots = reinterpret_cast<float4*>(sm + SX_SLOTS);
-  const uint32_t slots_u = sm_u + SX_SLOTS;
+  float* landing = reinterpret_cast<float*>(sm + SX_STAGE);   // fp32 slab at launch; outgoing partials later
+  const float* slots = reinterpret_cast<const float*>(sm + SX_SLOTS);
   if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
   if (tid == 0) {
     tc::mbar_init(&bar, 1);
     tc::mbar_init(&wbar, 1);
+    tc::mbar_init(&gbar, 1);
+    tc::mbar_init(&pbar, 1);
     tc::fence_mbar_init();
-    bulk_load_begin_x(reinterpret_cast<uint8_t*>(landing), Pg, (uint32_t)lay.end * 4u, &wbar);
+    bulk_load_begin_x(reinterpret_cast<uint8_t*>(landing), Pg, (uint32_t)s.end * 4u, &wbar);
   }
-  for (int i = tid; i < (SX_B3 + 64 - SX_W1) / 16; i += TC_THREADS) *reinterpret_cast<uint4*>(sm + SX_W1 + i * 16) = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < (SX_B3 + 64 - SX_W1) / 16; i += XT) *reinterpret_cast<uint4*>(sm + SX_W1 + i * 16) = make_uint4(0, 0, 0, 0);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  // every CTA's mbarriers exist before any peer's copy can name them: arrive now, wait before the first send
+  if (CS > 1) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  bool cluster_waited = CS == 1;
   const uint32_t tmem = tmem_slot;
   const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const IssuerX mma{tc::make_desc(sm_u, 0, 1024), tc::make_desc(sm_u, XP, 1024), tmem};
-  uint32_t ph = 0, wph = 0;
-  const float* W3s = reinterpret_cast<const float*>(sm + SX_W3);
-  const float* b3s = reinterpret_cast<const float*>(sm + SX_B3);
+  uint32_t ph = 0, gph = 0, pph = 0;
+  float* W3s = reinterpret_cast<float*>(sm + SX_W3);
+  float* b3s = reinterpret_cast<float*>(sm + SX_B3);
   const float inv_n = 1.f / (float)nb;
   const float gscale = inv_n * (1.f / DZS);
-
-  // One updated float4 of the slab (element index e) -> the operand image of every CTA of the cluster: W2 as split fp16
-  // into the hi / lo panels, the head as fp32, W1 / b1 / b2 as fp32 into the landing zone (converted locally afterwards).
-  auto publish_weights = [&](int e, const float4 w) {
-    if (e >= lay.w_off[1] && e < lay.b_off[1]) {
-      const int r = e - lay.w_off[1];
-      const int j = r / s.ld1, i = r - j * s.ld1;
-      const uint32_t off = tc::panel_off(j, i);
-      uint32_t h0, l0, h1, l1;
-      split2(w.x * WS, w.y * WS, h0, l0);
-      split2(w.z * WS, w.w * WS, h1, l1);
-#pragma unroll 4
-      for (int rk = 0; rk < CS; ++rk) {
-        const uint32_t base = mapa(sm_u, rk);
-        st_cluster_u2(base + SX_W2 + off, h0, h1);
-        st_cluster_u2(base + SX_W2L + off, l0, l1);
-      }
-      return;
-    }
-    int off;
-    if (e >= lay.w_off[2] && e < lay.b_off[2]) {          // W3 [C][ld2] -> fp32 [C][256]
-      const int r = e - lay.w_off[2];
-      const int k = r / s.ld2, c = r - k * s.ld2;
-      off = SX_W3 + (k * 256 + c) * 4;
-    } else if (e >= lay.b_off[2]) {                       // b3
-      off = SX_B3 + (e - lay.b_off[2]) * 4;
-    } else {                                              // W1, b1, b2
-      off = SX_STAGE + e * 4;
-    }
-#pragma unroll 4
-    for (int rk = 0; rk < CS; ++rk) st_cluster_f4(mapa(sm_u, rk) + off, w);
-  };
-  // one gradient float4 (slab index e4) -> the owner CTA's slot for this CTA
-  auto send_grad = [&](int e4, const float4 v) {
-    const int o = (int)__umulhi((uint32_t)e4, inv_per);
-    st_cluster_f4(mapa(slots_u + (uint32_t)(q * per + (e4 - o * per)) * 16u, o), v);
-  };
+  // bytes this CTA receives per step from the other owners' publications
+  const int my_j0 = q * own.R2, my_n2 = max(0, min(own.R2, s.h2 - my_j0));
+  const int my_i0 = (CS - 1 - q) * own.R1, my_n1 = max(0, min(own.R1, s.h1 - my_i0));
+  const uint32_t pub_in = (uint32_t)(s.h2 * 288 + s.h1 * 128 + 32) - (uint32_t)(my_n2 * 288 + my_n1 * 128 + (q == CS - 1 ? 32 : 0));
 
 #define STAMP(i) do { if (a.prof && blockIdx.x == 0 && tid == 0) a.prof[i] = clock64(); } while (0)
   STAMP(0);
   RowRegsX rr;
-  HostRegsX hr;
   rr.label = 0;
-  rr.q[0] = rr.q[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (a.x_host) hr = host_fetch_x(a, G.idx_off + b0 + q * XR, q < ntiles ? min(XR, nb - q * XR) : 0, tid);
-  else if (rowt) rr = fetch_row_x(a, G.idx_off + b0 + q * XR + row, q < ntiles && q * XR + row < nb, half);
-  tc::mbar_wait(&wbar, wph); wph ^= 1;
-  convert_weights_x(sm, landing, lay, s);
+  rr.q = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (!a.x_host && rowt) rr = fetch_row_x(a, G.idx_off + b0 + q * XR + row, q < ntiles && q * XR + row < nb, part);
+  tc::mbar_wait(&wbar, 0);
+  convert_weights_x(sm, landing, s);
   STAMP(1);
 
 #define FEDB_MMA_PHASE(ISSUE)            \
@@ -456,12 +468,19 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
     tc::tc_fence_after();                \
   } while (0)
 
-  // split of the layer-2 columns between the two halves (in 16-column chunks)
-  const int nch2 = s.N2 >> 4, ch_lo = half ? (nch2 + 1) >> 1 : 0, ch_hi = half ? nch2 : (nch2 + 1) >> 1;
+  // split of the layer-2 columns between the four parts (in 16-column chunks)
+  const int nch2 = s.N2 >> 4;
+  const int ch_lo = part * (nch2 >> 2) + min(part, nch2 & 3), ch_hi = ch_lo + (nch2 >> 2) + (part < (nch2 & 3) ? 1 : 0);
   uint8_t* const h1_hi = sm + SX_H1;
   uint8_t* const h1_lo = sm + SX_H1 + XP;
+  const int c1 = 16 * part;   // this part's 16 columns of the 64-wide layer-1 accumulators
+  bool first_fetch = true;
 
   for (int st = 0; st < a.n_steps; ++st) {
+    if (tid == 0 && CS > 1) {   // arm this step's two exchange barriers (a peer's bytes may arrive first: the count goes negative)
+      mbar_expect(&gbar, (uint32_t)(CS * own.share * 4));
+      if (pub_in) mbar_expect(&pbar, pub_in);
+    }
     float loss_acc = 0.f, db3_acc[FEDB_MAX_CLASSES];
 #pragma unroll
     for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] = 0.f;
@@ -471,35 +490,28 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
       const bool acc = my_tiles > 0;
       const int r = tile * XR + row;
       const bool valid = rowt && r < nb;
-      if (a.x_host) {
-        if (my_tiles > 0 || st > 0) hr = host_fetch_x(a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid);
-        rr = host_deliver_x(sm, a, hr, tid, row, half, rowt);
-      } else if (rowt && (my_tiles > 0 || st > 0)) {
-        rr = fetch_row_x(a, G.idx_off + b0 + r, valid, half);
-      }
-      int label = 0;
-      if (rowt) label = store_row_x(sm, rr, valid, s, row, half);
+      if (a.x_host) rr = host_rows_x(sm, a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid, row, part, rowt);
+      else if (rowt && !first_fetch) rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+      first_fetch = false;
+      const int label = rr.label;
+      if (rowt) store_row_x(sm, rr, valid, s, row, part);
       handoff_x();
       STAMP(2);
       // ---- layer 1 -----------------------------------------------------------------------
       FEDB_MMA_PHASE(mma.fwd1());
       STAMP(3);
-      uint32_t mask1 = 0;   // ReLU mask of this half's 32 columns of H1
+      uint32_t mask1 = 0;   // ReLU mask of this part's 16 columns of H1
       if (rowt) {
         float v[16];
+        tc::tmem_ld16(tl + TX_D1 + c1, v);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c0 = 32 * half + 16 * cc;
-          tc::tmem_ld16(tl + TX_D1 + c0, v);
-          tc::tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            if (v[i] > 0.f) { mask1 |= 1u << (16 * cc + i); v[i] = fminf(v[i] * INV_WS, HMAX); } else v[i] = 0.f;
-          }
-          if (c0 == 48) { v[15] = valid ? 1.f : 0.f; mask1 &= ~(1u << 31); }
-          st_panel8(h1_hi, h1_lo, row, c0, v);
-          st_panel8(h1_hi, h1_lo, row, c0 + 8, v + 8);
+        for (int i = 0; i < 16; ++i) {
+          if (v[i] > 0.f) { mask1 |= 1u << i; v[i] = fminf(v[i] * INV_WS, HMAX); } else v[i] = 0.f;
         }
+        if (part == 3) { v[15] = valid ? 1.f : 0.f; mask1 &= ~(1u << 15); }   // column 63: the bias input of layer 2
+        st_panel8(h1_hi, h1_lo, row, c1, v);
+        st_panel8(h1_hi, h1_lo, row, c1 + 8, v + 8);
       }
       handoff_x();
       STAMP(4);
@@ -510,6 +522,7 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
 #pragma unroll
       for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = dz3[k] = 0.f;
       if (rowt) {
+#pragma unroll 1
         for (int ch = ch_lo; ch < ch_hi; ++ch) {
           const int c0 = ch << 4;
           float v[16];
@@ -517,18 +530,27 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
           tc::tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX);
+          if (s.C <= 2) {
 #pragma unroll
-          for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-            if (k < s.C) {
-#pragma unroll
-              for (int i = 0; i < 16; ++i) z[k] = fmaf(v[i], W3s[k * 256 + c0 + i], z[k]);
+            for (int i = 0; i < 16; ++i) {
+              const float2 w = *reinterpret_cast<const float2*>(W3s + (c0 + i) * 8);
+              z[0] = fmaf(v[i], w.x, z[0]);
+              z[1] = fmaf(v[i], w.y, z[1]);
             }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float4 w0 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8), w1 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8 + 4);
+              z[0] = fmaf(v[i], w0.x, z[0]); z[1] = fmaf(v[i], w0.y, z[1]); z[2] = fmaf(v[i], w0.z, z[2]); z[3] = fmaf(v[i], w0.w, z[3]);
+              z[4] = fmaf(v[i], w1.x, z[4]); z[5] = fmaf(v[i], w1.y, z[5]); z[6] = fmaf(v[i], w1.z, z[6]); z[7] = fmaf(v[i], w1.w, z[7]);
+            }
+          }
           uint8_t* pz = sm + SX_Z + (c0 >> 6) * XP;
           st_panel8(pz, pz + 4 * XP, row, c0 & 63, v);
           st_panel8(pz, pz + 4 * XP, row, (c0 & 63) + 8, v + 8);
         }
-        // the two halves swap their partial logits through 16 spare TMEM columns of the row's lane
-        tc::tmem_st8(tl + TX_ZX + 8 * half, z);
+        // the four parts swap their partial logits through 32 spare TMEM columns of the row's lane
+        tc::tmem_st8(tl + TX_ZX + 8 * part, z);
         tc::tmem_st_wait();
       }
       tc::tc_fence_before();
@@ -536,11 +558,12 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
       tc::tc_fence_after();
       if (rowt) {
         {
-          float zo[8];
-          tc::tmem_ld8(tl + TX_ZX + 8 * (half ^ 1), zo);
+          float z0[16], z1[16];
+          tc::tmem_ld16(tl + TX_ZX, z0);
+          tc::tmem_ld16(tl + TX_ZX + 16, z1);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = (half ? zo[k] + z[k] : z[k] + zo[k]) + (k < s.C ? b3s[k] : 0.f);
+          for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = ((z0[k] + z0[8 + k]) + (z1[k] + z1[8 + k])) + (k < s.C ? b3s[k] : 0.f);
         }
         float loss = 0.f;
         if (valid) {
@@ -566,14 +589,14 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
             dz3[0] = (p - yt) * DZS;
           }
         }
-        if (half == 0) {   // one thread per row books the loss / db3 and publishes dZ3 as [hi | lo]
+        if (part == 0) {   // one thread per row books the loss / db3 and publishes dZ3 as [hi | lo] next to X
           loss_acc += loss;
 #pragma unroll
           for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] += dz3[k];
           uint4 dh, dl;
           split8(dz3, dh, dl);
-          *reinterpret_cast<uint4*>(sm + SX_DZ3 + tc::panel_off(row, 0)) = dh;
-          *reinterpret_cast<uint4*>(sm + SX_DZ3 + tc::panel_off(row, 8)) = dl;
+          *reinterpret_cast<uint4*>(sm + SX_X + tc::panel_off(row, DZ3_COL)) = dh;
+          *reinterpret_cast<uint4*>(sm + SX_X + tc::panel_off(row, DZ3_COL + 8)) = dl;
         }
       }
       handoff_x();
@@ -582,19 +605,25 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
       FEDB_MMA_PHASE(mma.wgrad3(s, acc));
       STAMP(7);
       if (rowt) {
+#pragma unroll 1
         for (int ch = ch_lo; ch < ch_hi; ++ch) {
           const int c0 = ch << 4;
           float v[16], d[16];
           tc::tmem_ld16(tl + TX_D2 + c0, v);
           tc::tmem_ld_wait();
+          if (s.C <= 2) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) d[i] = 0.f;
-#pragma unroll
-          for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-            if (k < s.C) {
-#pragma unroll
-              for (int i = 0; i < 16; ++i) d[i] = fmaf(dz3[k], W3s[k * 256 + c0 + i], d[i]);
+            for (int i = 0; i < 16; ++i) {
+              const float2 w = *reinterpret_cast<const float2*>(W3s + (c0 + i) * 8);
+              d[i] = fmaf(dz3[1], w.y, dz3[0] * w.x);
             }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float4 w0 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8), w1 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8 + 4);
+              d[i] = dz3[0] * w0.x + dz3[1] * w0.y + dz3[2] * w0.z + dz3[3] * w0.w + dz3[4] * w1.x + dz3[5] * w1.y + dz3[6] * w1.z + dz3[7] * w1.w;
+            }
+          }
 #pragma unroll
           for (int i = 0; i < 16; ++i) d[i] = v[i] > 0.f ? d[i] : 0.f;
           uint8_t* pz = sm + SX_Z + (c0 >> 6) * XP;
@@ -609,16 +638,12 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
       STAMP(9);
       if (rowt) {
         float v[16];
+        tc::tmem_ld16(tl + TX_D1 + c1, v);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c0 = 32 * half + 16 * cc;
-          tc::tmem_ld16(tl + TX_D1 + c0, v);
-          tc::tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = ((mask1 >> (16 * cc + i)) & 1u) ? v[i] * INV_WS : 0.f;
-          st_panel8(h1_hi, h1_lo, row, c0, v);        // dZ1 takes H1's place
-          st_panel8(h1_hi, h1_lo, row, c0 + 8, v + 8);
-        }
+        for (int i = 0; i < 16; ++i) v[i] = ((mask1 >> i) & 1u) ? v[i] * INV_WS : 0.f;
+        st_panel8(h1_hi, h1_lo, row, c1, v);        // dZ1 takes H1's place
+        st_panel8(h1_hi, h1_lo, row, c1 + 8, v + 8);
       }
       handoff_x();
       STAMP(10);
@@ -627,56 +652,46 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
       STAMP(11);
     }  // tiles
 
-    // ---- send this CTA's partial gradients, slice by slice, straight from TMEM into the owning CTA's shared memory
-    // (a reduce-scatter over distributed shared memory).  Every slab position below lay.end is sent (padding as 0).
+    // ---- reduce-scatter, sender side: weight-gradient accumulators (TMEM) -> staging blocks by owner -> one bulk copy per owner
+    float* stage = landing;
     {
       const bool have = my_tiles > 0;
       float v[16];
+#pragma unroll 1
       for (int mt = 0; mt < s.MT2; ++mt) {
         const int j = 128 * mt + lane128;
+        const int o = j / own.R2;
+        float* rec = stage + o * own.share + (j - o * own.R2) * own.recf;
+        if (have) { tc::tmem_ld16(tl + TX_DW2 + 64 * mt + c1, v); tc::tmem_ld_wait(); }
+        else {
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c0 = 32 * half + 16 * cc;
-          if (have) { tc::tmem_ld16(tl + TX_DW2 + 64 * mt + c0, v); tc::tmem_ld_wait(); }
-          else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = 0.f;
-          }
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] *= gscale;
-          if (j < s.h2) {
-#pragma unroll
-            for (int i4 = 0; i4 < 4; ++i4) {
-              const int col = c0 + 4 * i4;
-              if (col < s.ld1)
-                send_grad((lay.w_off[1] + j * s.ld1 + col) >> 2,
-                          make_float4(col < s.h1 ? v[4 * i4] : 0.f, col + 1 < s.h1 ? v[4 * i4 + 1] : 0.f,
-                                      col + 2 < s.h1 ? v[4 * i4 + 2] : 0.f, col + 3 < s.h1 ? v[4 * i4 + 3] : 0.f));
-            }
-          }
-          if (c0 == 48) {   // bias gradients sit in column 63: gathered four rows at a time by the lane that owns the aligned group
-            const float b0v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 0), b1v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 1);
-            const float b2v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 2), b3v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 3);
-            if ((lane & 3) == 0 && j < ru4(s.h2))
-              send_grad((lay.b_off[1] + j) >> 2, make_float4(j < s.h2 ? b0v : 0.f, j + 1 < s.h2 ? b1v : 0.f, j + 2 < s.h2 ? b2v : 0.f,
-                                                             j + 3 < s.h2 ? b3v : 0.f));
-          }
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
         }
-        if (half == 0) {   // head weights: dW3[k][j] = DW3[j][k] + DW3[j][8 + k]
-          if (have) { tc::tmem_ld16(tl + TX_DW3 + 16 * mt, v); tc::tmem_ld_wait(); }
+        if (j < s.h2) {
 #pragma unroll
-          for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-            if (k < s.C) {
-              const float x = (v[k] + v[8 + k]) * gscale;
-              const float x0 = __shfl_sync(0xffffffffu, x, (lane & ~3) + 0), x1 = __shfl_sync(0xffffffffu, x, (lane & ~3) + 1);
-              const float x2 = __shfl_sync(0xffffffffu, x, (lane & ~3) + 2), x3 = __shfl_sync(0xffffffffu, x, (lane & ~3) + 3);
-              if ((lane & 3) == 0 && j < s.ld2)
-                send_grad((lay.w_off[2] + k * s.ld2 + j) >> 2, make_float4(j < s.h2 ? x0 : 0.f, j + 1 < s.h2 ? x1 : 0.f,
-                                                                           j + 2 < s.h2 ? x2 : 0.f, j + 3 < s.h2 ? x3 : 0.f));
+          for (int i4 = 0; i4 < 4; ++i4)
+            if (c1 + 4 * i4 < s.ld1)   // columns h1 .. ld1-1 of the accumulator are exact zeros (H1's pad columns are)
+              *reinterpret_cast<float4*>(rec + c1 + 4 * i4) =
+                  make_float4(v[4 * i4] * gscale, v[4 * i4 + 1] * gscale, v[4 * i4 + 2] * gscale, v[4 * i4 + 3] * gscale);
+          if (part == 3) rec[s.ld1] = v[15] * gscale;   // column 63 multiplied the constant-1 input: db2
+        }
+        if (part == 0) {   // head weights: dW3[k][j] = DW3[j][k] + DW3[j][8 + k]
+          if (have) { tc::tmem_ld16(tl + TX_DW3 + 16 * mt, v); tc::tmem_ld_wait(); }
+          if (j < s.h2) {
+            float g3[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g3[k] = (v[k] + v[8 + k]) * gscale;
+            if (s.C <= 3) {
+              rec[s.ld1 + 1] = g3[0]; rec[s.ld1 + 2] = g3[1]; rec[s.ld1 + 3] = g3[2];
+            } else {
+              rec[s.ld1 + 1] = 0.f; rec[s.ld1 + 2] = 0.f; rec[s.ld1 + 3] = 0.f;
+              *reinterpret_cast<float4*>(rec + s.ld1 + 4) = make_float4(g3[0], g3[1], g3[2], g3[3]);
+              *reinterpret_cast<float4*>(rec + s.ld1 + 8) = make_float4(g3[4], g3[5], g3[6], g3[7]);
             }
+          }
         }
       }
-      if (half == 0) {     // layer 1: dW1[i][c] = DW1[i][c] + DW1[i][16 + c] (+ db1 in column 15)
+      if (part == 1) {     // layer 1: dW1[i][c] = DW1[i][c] + DW1[i][16 + c] (column 15: db1)
         float w[16];
         if (have) {
           tc::tmem_ld16(tl + TX_DW1, v);
@@ -686,29 +701,17 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = w[i] = 0.f;
         }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = (v[i] + w[i]) * gscale;
         if (lane128 < s.h1) {
+          const int blk = lane128 / own.R1;
+          float* rec = stage + (CS - 1 - blk) * own.share + own.R2 * own.recf + (lane128 - blk * own.R1) * 16;
 #pragma unroll
-          for (int i4 = 0; i4 < 4; ++i4) {
-            const int col = 4 * i4;
-            if (col < s.ld0)
-              send_grad((lay.w_off[0] + lane128 * s.ld0 + col) >> 2,
-                        make_float4(col < s.d0 ? v[col] : 0.f, col + 1 < s.d0 ? v[col + 1] : 0.f, col + 2 < s.d0 ? v[col + 2] : 0.f,
-                                    col + 3 < s.d0 ? v[col + 3] : 0.f));
-          }
+          for (int i4 = 0; i4 < 4; ++i4)
+            *reinterpret_cast<float4*>(rec + 4 * i4) = make_float4((v[4 * i4] + w[4 * i4]) * gscale, (v[4 * i4 + 1] + w[4 * i4 + 1]) * gscale,
+                                                                   (v[4 * i4 + 2] + w[4 * i4 + 2]) * gscale, (v[4 * i4 + 3] + w[4 * i4 + 3]) * gscale);
         }
-        const float b0v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 0), b1v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 1);
-        const float b2v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 2), b3v = __shfl_sync(0xffffffffu, v[15], (lane & ~3) + 3);
-        if ((lane & 3) == 0 && lane128 < ru4(s.h1))
-          send_grad((lay.b_off[0] + lane128) >> 2, make_float4(lane128 < s.h1 ? b0v : 0.f, lane128 + 1 < s.h1 ? b1v : 0.f,
-                                                               lane128 + 2 < s.h1 ? b2v : 0.f, lane128 + 3 < s.h1 ? b3v : 0.f));
       }
-    }
-    STAMP(12);
-    // loss and db3: warp shuffle, then the 2 row-warps of half 0 in a fixed order; sent like any other gradient
-    {
-      if (rowt && half == 0) {
+      // loss and db3: warp shuffle, then the two row warps of part 0 in a fixed order
+      if (rowt && part == 0) {
         float vals[9];
         vals[0] = loss_acc;
 #pragma unroll
@@ -721,97 +724,192 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
           if (lane == 0) red_f[warp][i] = x;
         }
       }
-      __syncthreads();
-      if (tid == 0) {
-        float t[9];
-#pragma unroll
-        for (int i = 0; i < 9; ++i) t[i] = red_f[0][i] + red_f[1][i];
-        send_grad(lay.b_off[2] >> 2, make_float4(0 < s.C ? t[1] : 0.f, 1 < s.C ? t[2] : 0.f, 2 < s.C ? t[3] : 0.f, 3 < s.C ? t[4] : 0.f));
-        if (s.C > 4) send_grad((lay.b_off[2] >> 2) + 1, make_float4(t[5], 5 < s.C ? t[6] : 0.f, 6 < s.C ? t[7] : 0.f, 7 < s.C ? t[8] : 0.f));
-        // loss partial: float q of the extra row behind rank 0's slots
-        st_cluster_f1(mapa(slots_u + (uint32_t)(CS * per) * 16u + 4u * (uint32_t)q, 0), t[0]);
-        sc_s = step_scalars_fast(G, step0 + st + 1);
-      }
     }
-    // my slice of the slab and its moments do not depend on the peers: fetch them before the barrier
-    constexpr int PF = 2;
-    const bool use_v = a.v && G.opt != FEDB_OPT_SGD;
-    float4 w_pf[PF], m_pf[PF], v_pf[PF];
-#pragma unroll
-    for (int it = 0; it < PF; ++it) {
-      const int e4 = lo + tid + it * TC_THREADS;
-      w_pf[it] = m_pf[it] = v_pf[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (e4 < hi) {
-        w_pf[it] = *reinterpret_cast<float4*>(Pg + 4 * e4);
-        if (a.m) m_pf[it] = *reinterpret_cast<float4*>(a.m + G.slab_off + 4 * e4);
-        if (use_v) v_pf[it] = *reinterpret_cast<float4*>(a.v + G.slab_off + 4 * e4);
+    STAMP(12);
+    // ---- owner, before the partials arrive: classify my unit and fetch its weights / moments (they do not depend on the peers)
+    const int nrec4 = own.recf >> 2, w2u = own.R2 * nrec4, w1u = own.R1 * 4, ld1q = s.ld1 >> 2;
+    const bool use_m = a.m != nullptr, use_v = a.v && G.opt != FEDB_OPT_SGD;
+    const float* Mg = a.m + G.slab_off;
+    const float* Vg = a.v + G.slab_off;
+    auto plan_unit = [&](int u) -> UnitX {
+      UnitX p;
+      p.kind = 0; p.r = p.c = 0; p.wmask = 0;
+      p.e[0] = p.e[1] = p.e[2] = p.e[3] = -1;
+      if (u < w2u) {
+        const int jr = u / nrec4, c4 = u - jr * nrec4, j = my_j0 + jr;
+        if (j >= s.h2) return p;
+        p.r = j;
+        if (c4 < ld1q) {
+          p.kind = 1; p.c = 4 * c4; p.wmask = 15;
+          const int e = s.w_off1 + j * s.ld1 + 4 * c4;
+          p.e[0] = e; p.e[1] = e + 1; p.e[2] = e + 2; p.e[3] = e + 3;
+        } else if (c4 == ld1q) {
+          p.kind = 2; p.wmask = 14;
+          p.e[0] = s.b_off1 + j;
+          if (s.C <= 3)
+            for (int k = 0; k < 3; ++k) if (k < s.C) p.e[1 + k] = s.w_off2 + k * s.ld2 + j;
+        } else {
+          p.kind = 3; p.c = 4 * (c4 - ld1q - 1); p.wmask = 15;
+          for (int l = 0; l < 4; ++l) if (p.c + l < s.C) p.e[l] = s.w_off2 + (p.c + l) * s.ld2 + j;
+        }
+      } else if (u < w2u + w1u) {
+        const int ir = (u - w2u) >> 2, c4 = (u - w2u) & 3, i = my_i0 + ir;
+        if (i >= s.h1) return p;
+        p.kind = 4; p.r = i; p.c = 4 * c4;
+        for (int l = 0; l < 4; ++l) {
+          const int col = 4 * c4 + l;
+          if (col < s.d0) { p.e[l] = s.w_off0 + i * s.ld0 + col; p.wmask |= 1 << l; }
+          else if (col == 15) p.e[l] = s.b_off0 + i;
+        }
+      } else if (q == CS - 1) {
+        const int t = u - w2u - w1u;
+        if (t < 2) {
+          p.kind = 5; p.c = 4 * t;
+          for (int l = 0; l < 4; ++l) if (4 * t + l < s.C) p.e[l] = s.b_off2 + 4 * t + l;
+        } else if (t == 2) {
+          p.kind = 6;
+        }
       }
-    }
+      return p;
+    };
+    auto load_unit = [&](const UnitX& p, float* w, float* mm, float* vv) {
+#pragma unroll
+      for (int l = 0; l < 4; ++l) w[l] = mm[l] = vv[l] = 0.f;
+      if (p.kind == 1) {
+        const float4 t = *reinterpret_cast<const float4*>(Pg + p.e[0]);
+        w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
+        if (use_m) { const float4 x = *reinterpret_cast<const float4*>(Mg + p.e[0]); mm[0] = x.x; mm[1] = x.y; mm[2] = x.z; mm[3] = x.w; }
+        if (use_v) { const float4 x = *reinterpret_cast<const float4*>(Vg + p.e[0]); vv[0] = x.x; vv[1] = x.y; vv[2] = x.z; vv[3] = x.w; }
+      } else {
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+          if (p.e[l] >= 0) {
+            w[l] = Pg[p.e[l]];
+            if (use_m) mm[l] = Mg[p.e[l]];
+            if (use_v) vv[l] = Vg[p.e[l]];
+          }
+      }
+    };
+    UnitX up = plan_unit(tid);
+    float uw[4], um[4], uv[4];
+    load_unit(up, uw, um, uv);
     tc::tc_fence_before();
-    cluster.sync();     // every partial slice has landed in its owner's shared memory
+    tc::fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      float* misc = stage + (CS - 1) * own.share + own.R2 * own.recf + own.R1 * 16;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) misc[i == 0 ? 8 : i - 1] = red_f[0][i] + red_f[1][i];   // [db3[0..7], loss]
+      sc_s = step_scalars_fast(G, step0 + st + 1);
+      tc::fence_async_smem();
+    }
+    if (!cluster_waited) {
+      asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+      cluster_waited = true;
+    }
+    __syncthreads();
+    if (CS > 1) {
+      if (tid < CS)   // block `tid` of my staging area -> slot `q` of owner `tid`
+        bulk_s2c(mapa(sm_u + SX_SLOTS + (uint32_t)(q * own.share) * 4u, tid), sm_u + SX_STAGE + (uint32_t)(tid * own.share) * 4u,
+                 (uint32_t)own.share * 4u, mapa(tc::smem_u32(&gbar), tid));
+      mbar_wait_cluster(&gbar, gph);
+      gph ^= 1;
+    }
     STAMP(13);
 
-    // ---- owner: fixed-order sum of the CS partials (local shared memory), optimizer, then all-gather + conversion of the
-    // updated slice into every CTA's operand image (distributed shared memory) ------
+    // ---- owner: fixed-order sum of the CS partials, optimizer, new values into my own operand panels ------------------
     {
       const StepScalars sc = sc_s;
-      int it = 0;
-      for (int e4 = lo + tid; e4 < hi; e4 += TC_THREADS, ++it) {
-        const int e = e4 * 4, i = e4 - lo;
-        float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float* parts = CS > 1 ? slots : stage;
+      const bool emit_avg = avg_out != nullptr && st == a.n_steps - 1;
+      const float al = G.alpha * inv_n;
+#pragma unroll 1
+      for (int u = tid; u < share4; u += XT) {
+        if (u != tid) { up = plan_unit(u); load_unit(up, uw, um, uv); }
+        if (up.kind == 0) continue;
+        float gs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
-        for (int rk = 0; rk < CS; ++rk) { const float4 p = slots[rk * per + i]; gsum.x += p.x; gsum.y += p.y; gsum.z += p.z; gsum.w += p.w; }
-        float4 w, mm, vv;
-        if (it < PF) {
-          w = it == 0 ? w_pf[0] : w_pf[1];
-          mm = it == 0 ? m_pf[0] : m_pf[1];
-          vv = it == 0 ? v_pf[0] : v_pf[1];
+        for (int rk = 0; rk < CS; ++rk) {
+          const float4 p = *reinterpret_cast<const float4*>(parts + rk * own.share + 4 * u);
+          gs[0] += p.x; gs[1] += p.y; gs[2] += p.z; gs[3] += p.w;
+        }
+        if (up.kind == 6) {
+          if (a.loss_out) a.loss_out[g] = gs[0] * inv_n;
+          continue;
+        }
+        float av[4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          av[l] = 0.f;
+          if (up.e[l] >= 0) {
+            const float gr = ((up.wmask >> l) & 1) ? fmaf(al, uw[l], gs[l]) : gs[l];
+            uw[l] = opt_update(G, sc, uw[l], gr, um[l], uv[l]);
+            av[l] = __fdiv_rn(__fmul_rn(uw[l], G.agg_num), G.agg_den);   // this client's FedAvg term (C:110-115)
+          }
+        }
+        float* Mw = a.m + G.slab_off;
+        float* Vw = a.v + G.slab_off;
+        if (up.kind == 1) {
+          const int e = up.e[0];
+          if (use_m) *reinterpret_cast<float4*>(Mw + e) = make_float4(um[0], um[1], um[2], um[3]);
+          if (use_v) *reinterpret_cast<float4*>(Vw + e) = make_float4(uv[0], uv[1], uv[2], uv[3]);
+          const float4 wv = make_float4(uw[0], uw[1], uw[2], uw[3]), avv = make_float4(av[0], av[1], av[2], av[3]);
+          if (emit_avg) *reinterpret_cast<float4*>(avg_out + e) = avv;
+          *reinterpret_cast<float4*>(Pg + e) = (emit_avg && inline_avg) ? avv : wv;
+          put_w2(sm, up.r, up.c, wv);
         } else {
-          w = *reinterpret_cast<float4*>(Pg + e);
-          mm = vv = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (a.m) mm = *reinterpret_cast<float4*>(a.m + G.slab_off + e);
-          if (use_v) vv = *reinterpret_cast<float4*>(a.v + G.slab_off + e);
+#pragma unroll
+          for (int l = 0; l < 4; ++l)
+            if (up.e[l] >= 0) {
+              const int e = up.e[l];
+              if (use_m) Mw[e] = um[l];
+              if (use_v) Vw[e] = uv[l];
+              if (emit_avg) avg_out[e] = av[l];
+              Pg[e] = (emit_avg && inline_avg) ? av[l] : uw[l];
+            }
+          if (up.kind == 2) {
+            put_b2(sm, up.r, uw[0]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) if (up.e[1 + k] >= 0) W3s[up.r * 8 + k] = uw[1 + k];
+          } else if (up.kind == 3) {
+#pragma unroll
+            for (int l = 0; l < 4; ++l) if (up.e[l] >= 0) W3s[up.r * 8 + up.c + l] = uw[l];
+          } else if (up.kind == 4) {
+            put_w1(sm, up.r, up.c, make_float4(uw[0], uw[1], uw[2], uw[3]));
+          } else {
+#pragma unroll
+            for (int l = 0; l < 4; ++l) if (up.e[l] >= 0) b3s[up.c + l] = uw[l];
+          }
         }
-        const bool is_w = (e < lay.b_off[0]) || (e >= lay.w_off[1] && e < lay.b_off[1]) || (e >= lay.w_off[2] && e < lay.b_off[2]);
-        if (is_w && G.alpha != 0.f) {
-          const float al = G.alpha * inv_n;
-          gsum.x = fmaf(al, w.x, gsum.x); gsum.y = fmaf(al, w.y, gsum.y);
-          gsum.z = fmaf(al, w.z, gsum.z); gsum.w = fmaf(al, w.w, gsum.w);
-        }
-        w.x = opt_update(G, sc, w.x, gsum.x, mm.x, vv.x);
-        w.y = opt_update(G, sc, w.y, gsum.y, mm.y, vv.y);
-        w.z = opt_update(G, sc, w.z, gsum.z, mm.z, vv.z);
-        w.w = opt_update(G, sc, w.w, gsum.w, mm.w, vv.w);
-        publish_weights(e, w);
-        if (p2p_partial && st == a.n_steps - 1)          // this rank's FedAvg term, (w * n_k) / N, for the peers to fetch (C:110-115)
-          reinterpret_cast<float4*>(p2p_partial)[e4] =
-              make_float4(__fdiv_rn(__fmul_rn(w.x, G.agg_num), G.agg_den), __fdiv_rn(__fmul_rn(w.y, G.agg_num), G.agg_den),
-                          __fdiv_rn(__fmul_rn(w.z, G.agg_num), G.agg_den), __fdiv_rn(__fmul_rn(w.w, G.agg_num), G.agg_den));
-        *reinterpret_cast<float4*>(Pg + e) = w;          // master copy (off the critical path)
-        if (a.m) *reinterpret_cast<float4*>(a.m + G.slab_off + e) = mm;
-        if (use_v) *reinterpret_cast<float4*>(a.v + G.slab_off + e) = vv;
-      }
-      if (q == 0 && tid == 32 && a.loss_out) {
-        const float* lp = reinterpret_cast<const float*>(slots + CS * per);
-        float ls = 0.f;
-        for (int rk = 0; rk < CS; ++rk) ls += lp[rk];
-        a.loss_out[g] = ls * inv_n;
       }
     }
     STAMP(14);
-    cluster.sync();   // every CTA holds the complete updated operand image
-    if (p2p_partial && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
-      // arrival flag A ("my partial is complete") into every peer's buffer; the local evaluation below overlaps its flight.
-      // The cluster barrier ordered every CTA's partial stores before this thread; fence + release make them visible to
-      // whoever acquires the flag.
+    // ---- all-gather: my rows (already in panel format) -> the same offsets of every peer's panels ------------------------
+    tc::fence_async_smem();
+    __syncthreads();
+    if (CS > 1) {
+      if (tid < CS && tid != q) {
+        if (avg_out && st == a.n_steps - 1) __threadfence_system();   // my partial's stores precede the signal the peers' flag rests on
+        const uint32_t base = mapa(sm_u, tid), pb = mapa(tc::smem_u32(&pbar), tid);
+        if (my_n2 > 0) {
+          bulk_s2c(base + SX_W2 + my_j0 * 128, sm_u + SX_W2 + my_j0 * 128, (uint32_t)my_n2 * 128u, pb);
+          bulk_s2c(base + SX_W2L + my_j0 * 128, sm_u + SX_W2L + my_j0 * 128, (uint32_t)my_n2 * 128u, pb);
+          bulk_s2c(base + SX_W3 + my_j0 * 32, sm_u + SX_W3 + my_j0 * 32, (uint32_t)my_n2 * 32u, pb);
+        }
+        if (my_n1 > 0) bulk_s2c(base + SX_W1 + my_i0 * 128, sm_u + SX_W1 + my_i0 * 128, (uint32_t)my_n1 * 128u, pb);
+        if (q == CS - 1) bulk_s2c(base + SX_B3, sm_u + SX_B3, 32u, pb);
+      }
+      if (pub_in) { mbar_wait_cluster(&pbar, pph); pph ^= 1; }
+    }
+    if (a.tail_mode == 2 && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
+      // arrival flag A ("my partial is complete") into every peer GPU's buffer; the local evaluation below overlaps its
+      // flight.  Every owner fenced its partial stores at system scope before publishing, and this CTA has received
+      // every publication: fence + release make them visible to whoever acquires the flag.
       __threadfence_system();
       uint64_t* pf = reinterpret_cast<uint64_t*>(a.p2p->sym[tid] + a.p2p->sym_flag_off);
       st_release_sys_u64(pf + a.p2p->rank, p2p_seq + 1);
     }
     STAMP(15);
-    convert_w1_b2(sm, landing, lay, s, tid);
-    tc::fence_async_smem();
-    __syncthreads();
     STAMP(16);
   }  // steps
 
@@ -822,33 +920,24 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
     for (int tile = q; tile < ntiles; tile += CS) {
       const int r = tile * XR + row;
       const bool valid = rowt && r < nb;
-      int label = 0;
-      if (ntiles <= CS && a.n_steps > 0) {
-        label = rr.label;   // single tile per CTA: the X panel from the training step is still in place
-      } else {
-        if (a.x_host) {
-          hr = host_fetch_x(a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid);
-          rr = host_deliver_x(sm, a, hr, tid, row, half, rowt);
-        } else if (rowt) {
-          rr = fetch_row_x(a, G.idx_off + b0 + r, valid, half);
-        }
-        if (rowt) label = store_row_x(sm, rr, valid, s, row, half);
+      if (!(ntiles <= CS && a.n_steps > 0)) {   // (single tile per CTA: the X panel from the training step is still in place)
+        if (a.x_host) rr = host_rows_x(sm, a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid, row, part, rowt);
+        else if (rowt && !first_fetch) rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+        first_fetch = false;
+        if (rowt) store_row_x(sm, rr, valid, s, row, part);
       }
+      const int label = rr.label;
       handoff_x();
       FEDB_MMA_PHASE(mma.fwd1());
       if (rowt) {
         float v[16];
+        tc::tmem_ld16(tl + TX_D1 + c1, v);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c0 = 32 * half + 16 * cc;
-          tc::tmem_ld16(tl + TX_D1 + c0, v);
-          tc::tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX);
-          if (c0 == 48) v[15] = valid ? 1.f : 0.f;
-          st_panel8(h1_hi, h1_lo, row, c0, v);
-          st_panel8(h1_hi, h1_lo, row, c0 + 8, v + 8);
-        }
+        for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX);
+        if (part == 3) v[15] = valid ? 1.f : 0.f;
+        st_panel8(h1_hi, h1_lo, row, c1, v);
+        st_panel8(h1_hi, h1_lo, row, c1 + 8, v + 8);
       }
       handoff_x();
       FEDB_MMA_PHASE(mma.fwd2(s));
@@ -856,30 +945,43 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
 #pragma unroll
       for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = 0.f;
       if (rowt) {
+#pragma unroll 1
         for (int ch = ch_lo; ch < ch_hi; ++ch) {
           const int c0 = ch << 4;
           float v[16];
           tc::tmem_ld16(tl + TX_D2 + c0, v);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-            if (k < s.C) {
+          for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX);
+          if (s.C <= 2) {
 #pragma unroll
-              for (int i = 0; i < 16; ++i) z[k] = fmaf(fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX), W3s[k * 256 + c0 + i], z[k]);
+            for (int i = 0; i < 16; ++i) {
+              const float2 w = *reinterpret_cast<const float2*>(W3s + (c0 + i) * 8);
+              z[0] = fmaf(v[i], w.x, z[0]);
+              z[1] = fmaf(v[i], w.y, z[1]);
             }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float4 w0 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8), w1 = *reinterpret_cast<const float4*>(W3s + (c0 + i) * 8 + 4);
+              z[0] = fmaf(v[i], w0.x, z[0]); z[1] = fmaf(v[i], w0.y, z[1]); z[2] = fmaf(v[i], w0.z, z[2]); z[3] = fmaf(v[i], w0.w, z[3]);
+              z[4] = fmaf(v[i], w1.x, z[4]); z[5] = fmaf(v[i], w1.y, z[5]); z[6] = fmaf(v[i], w1.z, z[6]); z[7] = fmaf(v[i], w1.w, z[7]);
+            }
+          }
         }
-        tc::tmem_st8(tl + TX_ZX + 8 * half, z);
+        tc::tmem_st8(tl + TX_ZX + 8 * part, z);
         tc::tmem_st_wait();
       }
       tc::tc_fence_before();
       __syncthreads();
       tc::tc_fence_after();
-      if (rowt && half == 0) {
-        float zo[8];
-        tc::tmem_ld8(tl + TX_ZX + 8, zo);
+      if (rowt && part == 0) {
+        float z0[16], z1[16];
+        tc::tmem_ld16(tl + TX_ZX, z0);
+        tc::tmem_ld16(tl + TX_ZX + 16, z1);
         tc::tmem_ld_wait();
 #pragma unroll
-        for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = z[k] + zo[k] + (k < s.C ? b3s[k] : 0.f);
+        for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = ((z0[k] + z0[8 + k]) + (z1[k] + z1[8 + k])) + (k < s.C ? b3s[k] : 0.f);
         int pred = 0;
         if (G.head == FEDB_HEAD_SOFTMAX_CE) {
           float best = z[0];
@@ -902,14 +1004,19 @@ __device__ __forceinline__ void round_body_x(const TcArgs& a, uint8_t* smem_raw)
 #undef STAMP
 
   if (q == 0 && tid == 0) a.step[g] = step0 + a.n_steps;
+  if (!cluster_waited) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // (n_steps == 0: complete the pending phase)
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc<512>(tmem);
+  // a CTA's shared memory is the source of its outgoing copies and the target of its peers': nobody leaves before all have
+  // received everything (the tails synchronise the cluster themselves)
+  if (a.tail_mode == 0 && CS > 1) cluster.sync();
+  return inline_avg && a.n_steps > 0;
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) k_round_tcx(TcArgs a) {
+__global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  round_body_x(a, smem_raw);
+  const bool avg_done = round_body_x(a, smem_raw);
   if (a.tail_mode == 0) return;
   if (a.tail_mode == 2) { p2p_tail(a); return; }
   // the cluster that observes the last check-in runs the single-GPU aggregation tail (see k_local_round_tc)
@@ -917,7 +1024,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_round_tcx(TcArgs a) {
   __shared__ unsigned char s_stop[TAIL_MAX_FEDS];
   cg::cluster_group cluster = cg::this_cluster();
   const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
-  for (int f = threadIdx.x; f < a.n_feds; f += TC_THREADS) s_stop[f] = a.fed_state_rw[f].stop ? 1 : 0;
+  for (int f = threadIdx.x; f < a.n_feds; f += XT) s_stop[f] = a.fed_state_rw[f].stop ? 1 : 0;
   __threadfence();
   cluster.sync();
   const unsigned int n_clusters = gridDim.x / CS;
@@ -931,7 +1038,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_round_tcx(TcArgs a) {
     __threadfence();
   }
   if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[18] = clock64();
-  round_tail(a, crank, CS, s_stop);
+  round_tail(a, crank, CS, s_stop, avg_done);
   if (a.prof && crank == CS - 1 && threadIdx.x == 0) a.prof[19] = clock64();
 }
 
@@ -939,10 +1046,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_round_tcx(TcArgs a) {
 
 using namespace fedb;
 
-extern "C" int64_t fedb_tcx_smem_bytes(void) { return SX_SLOTS + SX_SLOTS_MAX + 1024; }
-// largest slab (floats) whose gradient slices (rounded up to a multiple of 16 CTAs) fit the per-CTA exchange area
-extern "C" int32_t fedb_tcx_max_slab(void) { return (SX_SLOTS_MAX - 64 - 16 * 16) / 4; }
+static constexpr int kTcxSmem = SX_SLOTS + SX_SLOTS_MAX + 1024;
+
+extern "C" int64_t fedb_tcx_smem_bytes(void) { return kTcxSmem; }
 extern "C" int32_t fedb_tcx_rows(void) { return XR; }
+// 1 if a model with these layer sizes runs with `cluster` CTAs per client: shape limits, and the exchange blocks of all
+// senders / owners must fit the receive area and the staging area.
+extern "C" int32_t fedb_tcx_fits(int32_t d0, int32_t h1, int32_t h2, int32_t C, int32_t cluster) {
+  if (cluster < 1 || cluster > 16 || d0 < 1 || d0 > 15 || h1 < 1 || h1 > 63 || h2 < 1 || h2 > 256 || C < 1 || C > 8) return 0;
+  const OwnX o = own_geometry(h1, h2, C, cluster);
+  const int64_t bytes = (int64_t)cluster * o.share * 4;
+  int32_t dims[4] = {d0, h1, h2, C};
+  const SlabLayout lay = slab_layout(dims, 3);
+  if ((int64_t)lay.end * 4 > SX_STAGE_MAX) return 0;                         // the fp32 slab lands in the staging area at launch
+  return bytes <= SX_STAGE_MAX && (cluster == 1 || bytes <= SX_SLOTS_MAX) ? 1 : 0;
+}
 
 // Largest cluster size (<= 16) the device can co-schedule for this kernel; 16 needs the non-portable opt-in and a GPC
 // with 16 free SMs.  Cached per device.
@@ -951,16 +1069,15 @@ extern "C" int32_t fedb_tcx_max_cluster(void) {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 8;
   if (cached[dev]) return cached[dev];
-  const int smem = SX_SLOTS + SX_SLOTS_MAX + 1024;
-  if (cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+  if (cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcxSmem) != cudaSuccess ||
       cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
     cudaGetLastError();
     return cached[dev] = 8;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(16);
-  cfg.blockDim = dim3(TC_THREADS);
-  cfg.dynamicSmemBytes = smem;
+  cfg.blockDim = dim3(XT);
+  cfg.dynamicSmemBytes = kTcxSmem;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 16;
@@ -976,14 +1093,13 @@ extern "C" int32_t fedb_tcx_max_cluster(void) {
 static int launch_tcx(TcArgs a, int32_t n_groups, int32_t cluster_size, void* stream) {
   FEDB_REQUIRE(n_groups > 0 && cluster_size >= 1 && cluster_size <= 16, "bad grid");
   FEDB_REQUIRE(a.ldx >= 16 && a.ldx % 4 == 0, "feature rows must be padded to >= 16 floats");
-  const int smem = SX_SLOTS + SX_SLOTS_MAX + 1024;
   // per-device attributes: cheap, legal during stream capture, and correct for a process that drives several GPUs
-  FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcxSmem));
   if (cluster_size > 8) FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_round_tcx, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(n_groups * cluster_size);
-  cfg.blockDim = dim3(TC_THREADS);
-  cfg.dynamicSmemBytes = smem;
+  cfg.blockDim = dim3(XT);
+  cfg.dynamicSmemBytes = kTcxSmem;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
@@ -998,6 +1114,7 @@ static int launch_tcx(TcArgs a, int32_t n_groups, int32_t cluster_size, void* st
 
 // The three general entry points of the split-fp16 round kernel; arguments exactly as for the bf16 kernel's
 // fedb_local_round_tc_prof / fedb_round_tc_hostin / fedb_round_tc_p2p_hostin (include/fedb200.h), cluster_size 1..16.
+// The caller checks the model against fedb_tcx_fits (the kernel reads shapes from the device table).
 extern "C" int fedb_local_round_tcx(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
                                     const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                                     const int32_t* active, const FedbFedState* fed_state, float* loss_out, int32_t* conf,

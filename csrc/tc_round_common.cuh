@@ -10,7 +10,7 @@
 
 namespace fedb {
 
-constexpr int TC_THREADS = 256;   // both round kernels run 8 warps per CTA
+constexpr int TC_THREADS = 256;   // threads per CTA of the bf16 round kernel (the tails below take the count from blockDim.x)
 
 struct TcArgs {
   const FedbGroup* groups;
@@ -45,20 +45,30 @@ struct TcArgs {
   FedbFedState* state_mirror;   // optional: mapped pinned host copy of the federation state, written by the tail
 };
 
+// One copy of the metrics / early-stop code for both tails (it runs once per round on one warp; inlined twice it is ~4000
+// instructions of mostly double-precision code that a cache-cold round has to fetch).
+static __device__ __noinline__ void round_metrics_ni(const FedbFed* F, FedbFedState* S, int f, int n_groups, const int32_t* conf,
+                                                     float* hist_local, float* hist_global, int* pool, FedbFedState* host_mirror,
+                                                     void* host_result) {
+  round_metrics_warp(*F, *S, f, n_groups, conf, hist_local, hist_global, pool, true, host_mirror, host_result);
+}
+
 // K1 + K5 for small problems, executed by the last cluster to finish: FedAvg of every federation in
 // client order with the reference's arithmetic (C:108-116), write-back (C:119-120), metrics and early
 // stop (C:165-192), then the next round's begin bookkeeping — same results as k_fedavg.
 constexpr int TAIL_MAX_FEDS = 256, TAIL_MAX_CLIENTS = 32;
 
-static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop) {
-  const int tid = threadIdx.x;
+// skip_avg: the caller's optimizer phase has already written the FedAvg result into the global arena and the slabs (the
+// single-client federation of the split-operand kernel); only metrics / early stop / bookkeeping are left.
+static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop, bool skip_avg = false) {
+  const int tid = threadIdx.x, NT = (int)blockDim.x;
   __shared__ long long t_off[TAIL_MAX_CLIENTS];
   __shared__ float t_num[TAIL_MAX_CLIENTS], t_den[TAIL_MAX_CLIENTS];
   // the last CTA of the cluster scores the round (metrics need only the confusion counts) while the
   // others average; with a single CTA it does both
   const int mrank = csize - 1, workers = csize > 1 ? csize - 1 : 1;
-  const int nthr = workers * TC_THREADS, gt = crank * TC_THREADS + tid;
-  for (int f = 0; f < a.n_feds && (csize == 1 || crank != mrank); ++f) {
+  const int nthr = workers * NT, gt = crank * NT + tid;
+  for (int f = 0; f < a.n_feds && !skip_avg && (csize == 1 || crank != mrank); ++f) {
     if (s_stop[f]) continue;
     const FedbFed F = a.feds[f];
     __syncthreads();
@@ -105,13 +115,13 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
     if (tid < 32)
       for (int f = 0; f < a.n_feds; ++f) {
         if (s_stop[f]) continue;
-        round_metrics_warp(a.feds[f], a.fed_state_rw[f], f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool, true,
+        round_metrics_ni(a.feds + f, a.fed_state_rw + f, f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool,
                            a.state_mirror ? a.state_mirror + f : nullptr,
                            a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
       }
     __syncthreads();
     if (a.prof && tid == 0) a.prof[21] = clock64();
-    for (int i = tid; i < a.n_conf; i += TC_THREADS) a.conf[i] = 0;
+    for (int i = tid; i < a.n_conf; i += NT) a.conf[i] = 0;
   }
 }
 
@@ -123,9 +133,9 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
 // and the last CTA scores the round from all ranks' counts and does the next round's bookkeeping.
 static __device__ void p2p_tail(const TcArgs& a) {
   cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
-  const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x;
+  const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x, NT = (int)blockDim.x;
   __shared__ FedbP2PRank R;
-  for (int i = tid; i < (int)(sizeof(FedbP2PRank) / 4); i += TC_THREADS)
+  for (int i = tid; i < (int)(sizeof(FedbP2PRank) / 4); i += NT)
     reinterpret_cast<int32_t*>(&R)[i] = reinterpret_cast<const int32_t*>(a.p2p)[i];
   __shared__ int s_timeout;
   if (tid == 0) s_timeout = 0;
@@ -141,7 +151,7 @@ static __device__ void p2p_tail(const TcArgs& a) {
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
   if (crank == 0) {   // PUSH this rank's confusion counts into every peer's area (parity, my rank), then flag B
     const int nconf = R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
-    for (int i = tid; i < nconf * R.world; i += TC_THREADS) {
+    for (int i = tid; i < nconf * R.world; i += NT) {
       const int qq = i / nconf, w = i - qq * nconf;
       reinterpret_cast<int32_t*>(R.sym[qq] + R.sym_conf_off)[(par * 8 + R.rank) * conf_stride + w] = __ldcg(a.conf + w);
     }
@@ -162,7 +172,7 @@ static __device__ void p2p_tail(const TcArgs& a) {
     float4* slab = reinterpret_cast<float4*>(R.params + G->slab_off);
     float4* glob = reinterpret_cast<float4*>(R.global + F.global_off);
     const int n4 = F.slab_size >> 2;
-    for (int e4 = crank * TC_THREADS + tid; e4 < n4; e4 += workers * TC_THREADS) {
+    for (int e4 = crank * NT + tid; e4 < n4; e4 += workers * NT) {
       float4 pr[8];
 #pragma unroll
       for (int qq = 0; qq < 8; ++qq)
@@ -181,7 +191,7 @@ static __device__ void p2p_tail(const TcArgs& a) {
       while (ld_acquire_sys_u64(my_flags + 8 + tid) < seq + 1)
         if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
     __syncthreads();
-    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) {
+    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += NT) {
       const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
       const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
       // the counts were pushed into THIS rank's buffer by their owners: a local read, no NVLink round trip
@@ -191,10 +201,10 @@ static __device__ void p2p_tail(const TcArgs& a) {
     __syncthreads();
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32 && R.do_metrics)
-      round_metrics_warp(R.feds_global[0], R.fed_state[0], 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool, true,
+      round_metrics_ni(R.feds_global, R.fed_state, 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool,
                          a.state_mirror, a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) + 15) & ~size_t(15)) : nullptr);
     __syncthreads();
-    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += TC_THREADS) a.conf[i] = 0;
+    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += NT) a.conf[i] = 0;
     if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
   }
   __syncthreads();

@@ -238,7 +238,7 @@ OPTIONAL_SIGS = {
     "fedb_round_tc": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P, _P], _I32),
     "fedb_local_round_tc_prof": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),
     "fedb_tcx_smem_bytes": ([], _I64),
-    "fedb_tcx_max_slab": ([], _I32),
+    "fedb_tcx_fits": ([_I32, _I32, _I32, _I32, _I32], _I32),
     "fedb_tcx_rows": ([], _I32),
     "fedb_tcx_max_cluster": ([], _I32),
     "fedb_local_round_tcx": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),

@@ -78,40 +78,46 @@ def probe(a_img: torch.Tensor, b_img: torch.Tensor, N: int, a_steps: Sequence[in
 TC_ROWS = 128
 TC_MAX_SLAB = 11920   # floats; fedb_tc_max_slab(): the gradient slices of all 8 CTAs must fit one CTA's exchange area
 TCX_ROWS = 64
-TCX_MAX_SLAB = 11888  # fedb_tcx_max_slab()
 
 
 def tc_eligible(groups: np.ndarray, variant: str = "bf16") -> bool:
-    """True when every group fits the fused tcgen05 kernel: 2 hidden ReLU layers,
-    in <= 15, h1 <= 63, h2 <= 256, out <= 8, slab small enough for the smem staging area."""
-    max_slab = TCX_MAX_SLAB if variant == "x2" else TC_MAX_SLAB
+    """True when every group fits the fused tcgen05 kernel: 2 hidden ReLU layers, in <= 15, h1 <= 63, h2 <= 256, out <= 8,
+    and the cross-CTA exchange areas hold the model (bf16: slab size; x2: fedb_tcx_fits at the planned cluster size)."""
     for g in groups:
         d = g["dims"]
         if int(g["n_layers"]) != 3 or int(g["act"]) != nat.ACT_IDS["relu"]:
             return False
         if not (d[0] <= 15 and d[1] <= 63 and d[2] <= 256 and d[3] <= 8):
             return False
-        if int(g["slab_size"]) > max_slab:
+        if variant != "x2" and int(g["slab_size"]) > TC_MAX_SLAB:
             return False
-    return True
+    return variant != "x2" or tc_cluster_size(groups, "x2") > 0
 
 
-def tc_cluster_size(groups: np.ndarray, variant: str = "bf16") -> int:
-    """CTAs per client: one per row tile, up to the largest cluster the kernel runs with (x2: 16 where the device can
-    co-schedule it and the grid then still fits the GPU in one wave, else 8)."""
+def _rows_per_step(groups: np.ndarray) -> int:
     rows = 1
     for g in groups:
         n = int(g["n_rows"])
         rows = max(rows, min(int(g["batch_size"]), n) if int(g["batch_size"]) > 0 else n)
+    return rows
+
+
+def tc_cluster_size(groups: np.ndarray, variant: str = "bf16") -> int:
+    """CTAs per client: one per row tile, up to the largest cluster the kernel runs with.  x2: 16 where the device can
+    co-schedule it and the grid then still fits the GPU in one wave, else <= 8; the largest size <= that at which every
+    model's exchange blocks fit (0: none does)."""
+    rows = _rows_per_step(groups)
     if variant != "x2":
         return int(min(8, max(1, (rows + TC_ROWS - 1) // TC_ROWS)))
+    lib = nat.lib(required=True)
     want = max(1, (rows + TCX_ROWS - 1) // TCX_ROWS)
-    if want <= 8:
-        return int(want)
-    cap = int(nat.lib(required=True).fedb_tcx_max_cluster())
-    if cap >= 16 and len(groups) * 16 <= 128:
-        return int(min(16, want))
-    return 8
+    if want > 8:
+        want = 16 if (int(lib.fedb_tcx_max_cluster()) >= 16 and len(groups) * 16 <= 128) else 8
+    shapes = {tuple(int(x) for x in g["dims"][:4]) for g in groups}
+    for cs in range(want, 0, -1):
+        if all(lib.fedb_tcx_fits(d0, h1, h2, c, cs) for d0, h1, h2, c in shapes):
+            return cs
+    return 0
 
 
 def local_round_tc(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch,

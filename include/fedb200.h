@@ -299,9 +299,11 @@ int fedb_tc_probe_args_size(void);
  * 8).  Same model limits as the bf16 kernel; arguments as fedb_local_round_tc_prof / fedb_round_tc_hostin /
  * fedb_round_tc_p2p_hostin respectively. */
 int64_t fedb_tcx_smem_bytes(void);
-int32_t fedb_tcx_max_slab(void);
 int32_t fedb_tcx_rows(void);
 int32_t fedb_tcx_max_cluster(void);
+/* 1 if a model in-h1-h2-out runs with `cluster` CTAs per client (the per-owner gradient blocks of all CTAs must fit the
+ * receive and staging areas in shared memory); the kernel itself trusts the device table, so check before launching. */
+int32_t fedb_tcx_fits(int32_t d0, int32_t h1, int32_t h2, int32_t n_out, int32_t cluster);
 int fedb_local_round_tcx(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, const float* X, int32_t ldx,
                          const int32_t* y, const int32_t* idx, float* params, float* m, float* v, int32_t* step,
                          const int32_t* active, const FedbFedState* fed_state, float* loss_out, int32_t* conf,
