@@ -24,17 +24,19 @@
 // 16 warps: warp w reaches TMEM lanes 32 (w % 4) .. +31, so the data rows (lanes 0..63) are served by the eight warps
 // with w % 4 < 2, four per row ("parts": each takes a quarter of the columns of every epilogue).
 //
-// Cross-CTA exchange (per optimizer step), all by bulk asynchronous copies between the CTAs' shared memories
-// (cp.async.bulk.shared::cluster.shared::cta, completion counted on the RECEIVER's mbarrier) — no cluster barrier:
+// Cross-CTA exchange (per optimizer step):
 //   reduce-scatter  every CTA drains its weight-gradient accumulators from TMEM into a staging area laid out by OWNER
 //                   (CTA o owns W2 rows [o R2, (o+1) R2) with their b2 / W3 entries, W1 rows of block CS-1-o and, for
-//                   o = CS-1, b3 and the loss) and sends block o to CTA o: one copy per peer;
-//   optimizer       the owner adds the CS partials in rank order (bit-reproducible), updates master weights / moments in
-//                   global memory and writes the new values straight into ITS OWN operand panels as split fp16;
-//   all-gather      ... and copies those panel rows (whole 128-byte rows, so the swizzle is irrelevant) into every peer's
-//                   panels at the same offsets.
-// Hazards are excluded by the protocol itself: a CTA sends partials only after its MMAs are done, an owner publishes
-// only after it has every partial, and nobody starts the next step before it has every published row.
+//                   o = CS-1, b3 and the loss) and sends block o to CTA o with ONE bulk asynchronous copy between the two
+//                   shared memories (cp.async.bulk.shared::cluster.shared::cta, completion counted on the receiver's
+//                   mbarrier, receivers visited in a rotated order); no cluster barrier;
+//   optimizer       the owner adds the CS partials in rank order (bit-reproducible) and updates master weights / moments
+//                   in global memory, one scalar per thread and pass;
+//   all-gather      through L2: one cluster barrier, then every CTA bulk-loads the whole fp32 slab (cp.async.bulk, the TMA
+//                   engine's 1-D mode) and rebuilds its split-fp16 operand image.  Measured on B200 the SM-to-SM fabric
+//                   moves ~6-20 B/clk per SM, so pushing 16 copies of the weights through it cost twice what L2 does.
+// Hazards are excluded by the protocol itself: a CTA sends partials only after its MMAs are done, and nobody reuses the
+// staging area before the barrier that follows every owner's wait.
 //
 // Shapes: 2 hidden ReLU layers, in <= 15, h1 <= 63, h2 <= 256, out <= 8 (the custom script's 14-50-200-2, C:40).
 #include <cooperative_groups.h>
@@ -346,20 +348,12 @@ struct IssuerX {
   }
 };
 
-// One float4 "unit" of an owner's share: which four slab entries it updates and where the new values go in the operand image.
-struct UnitX {
-  int kind;     // 0 nothing | 1 W2 row segment | 2 [b2, W3[0..2]] | 3 W3[k0..k0+3] | 4 W1 row segment (column 15 = b1) | 5 b3 | 6 loss
-  int r, c;     // row (j or i) and column / class offset
-  int e[4];     // slab indices (-1: lane unused); kind 1: e[0] is the float4-aligned start
-  int wmask;    // lanes that are weights (L2 applies)
-};
-
 }  // namespace
 
 // Returns true when the optimizer phase has already produced the FedAvg result (single-client federation on one GPU:
 // global = (w n) / n written by the owners, C:110-115), so the tail only scores the round.
 __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw) {
-  __shared__ uint64_t bar, wbar, gbar, pbar;   // MMA done | slab landed | partials in | published rows in
+  __shared__ uint64_t bar, wbar, gbar;   // MMA phase done | fp32 slab landed | every sender's partials for my rows are in
   __shared__ uint32_t tmem_slot;
   __shared__ float red_f[2][9];   // per-warp partial sums: loss + db3[8]
   __shared__ int cnt[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
@@ -415,14 +409,14 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
   } else if (inline_avg) {
     avg_out = a.global + a.feds[0].global_off;
   }
-  float* landing = reinterpret_cast<float*>(sm + SX_STAGE);   // fp32 slab at launch; outgoing partials later
+  float* landing = reinterpret_cast<float*>(sm + SX_STAGE);   // fp32 slab (at launch and after every step); outgoing partials in between
+  float* stage = landing;
   const float* slots = reinterpret_cast<const float*>(sm + SX_SLOTS);
   if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
   if (tid == 0) {
     tc::mbar_init(&bar, 1);
     tc::mbar_init(&wbar, 1);
     tc::mbar_init(&gbar, 1);
-    tc::mbar_init(&pbar, 1);
     tc::fence_mbar_init();
     bulk_load_begin_x(reinterpret_cast<uint8_t*>(landing), Pg, (uint32_t)s.end * 4u, &wbar);
   }
@@ -436,23 +430,20 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
   const uint32_t tmem = tmem_slot;
   const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const IssuerX mma{tc::make_desc(sm_u, 0, 1024), tc::make_desc(sm_u, XP, 1024), tmem};
-  uint32_t ph = 0, gph = 0, pph = 0;
+  uint32_t ph = 0, gph = 0, wph = 0;
   float* W3s = reinterpret_cast<float*>(sm + SX_W3);
   float* b3s = reinterpret_cast<float*>(sm + SX_B3);
   const float inv_n = 1.f / (float)nb;
   const float gscale = inv_n * (1.f / DZS);
-  // bytes this CTA receives per step from the other owners' publications
-  const int my_j0 = q * own.R2, my_n2 = max(0, min(own.R2, s.h2 - my_j0));
-  const int my_i0 = (CS - 1 - q) * own.R1, my_n1 = max(0, min(own.R1, s.h1 - my_i0));
-  const uint32_t pub_in = (uint32_t)(s.h2 * 288 + s.h1 * 128 + 32) - (uint32_t)(my_n2 * 288 + my_n1 * 128 + (q == CS - 1 ? 32 : 0));
+  const int my_j0 = q * own.R2, my_i0 = (CS - 1 - q) * own.R1;   // first W2 row / W1 row this CTA owns
 
-#define STAMP(i) do { if (a.prof && blockIdx.x == 0 && tid == 0) a.prof[i] = clock64(); } while (0)
+#define STAMP(i) do { if (a.prof && g == 0 && tid == 0) tc_stamp(a, q, i); } while (0)
   STAMP(0);
   RowRegsX rr;
   rr.label = 0;
   rr.q = make_float4(0.f, 0.f, 0.f, 0.f);
   if (!a.x_host && rowt) rr = fetch_row_x(a, G.idx_off + b0 + q * XR + row, q < ntiles && q * XR + row < nb, part);
-  tc::mbar_wait(&wbar, 0);
+  tc::mbar_wait(&wbar, wph); wph ^= 1;
   convert_weights_x(sm, landing, s);
   STAMP(1);
 
@@ -477,10 +468,7 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
   bool first_fetch = true;
 
   for (int st = 0; st < a.n_steps; ++st) {
-    if (tid == 0 && CS > 1) {   // arm this step's two exchange barriers (a peer's bytes may arrive first: the count goes negative)
-      mbar_expect(&gbar, (uint32_t)(CS * own.share * 4));
-      if (pub_in) mbar_expect(&pbar, pub_in);
-    }
+    if (tid == 0 && CS > 1) mbar_expect(&gbar, (uint32_t)(CS * own.share * 4));   // (a peer's bytes may arrive first: the count goes negative)
     float loss_acc = 0.f, db3_acc[FEDB_MAX_CLASSES];
 #pragma unroll
     for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] = 0.f;
@@ -653,7 +641,6 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
     }  // tiles
 
     // ---- reduce-scatter, sender side: weight-gradient accumulators (TMEM) -> staging blocks by owner -> one bulk copy per owner
-    float* stage = landing;
     {
       const bool have = my_tiles > 0;
       float v[16];
@@ -726,78 +713,54 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
       }
     }
     STAMP(12);
-    // ---- owner, before the partials arrive: classify my unit and fetch its weights / moments (they do not depend on the peers)
-    const int nrec4 = own.recf >> 2, w2u = own.R2 * nrec4, w1u = own.R1 * 4, ld1q = s.ld1 >> 2;
+    // ---- owner, before the partials arrive: the floats of my share that are parameters, and their weights / moments (these
+    // do not depend on the peers).  One scalar per task, TK tasks per thread and pass, so every thread of the CTA takes part.
+    constexpr int TK = 2;
+    const int w2f = own.R2 * own.recf, w1f = own.R1 * 16;
     const bool use_m = a.m != nullptr, use_v = a.v && G.opt != FEDB_OPT_SGD;
-    const float* Mg = a.m + G.slab_off;
-    const float* Vg = a.v + G.slab_off;
-    auto plan_unit = [&](int u) -> UnitX {
-      UnitX p;
-      p.kind = 0; p.r = p.c = 0; p.wmask = 0;
-      p.e[0] = p.e[1] = p.e[2] = p.e[3] = -1;
-      if (u < w2u) {
-        const int jr = u / nrec4, c4 = u - jr * nrec4, j = my_j0 + jr;
-        if (j >= s.h2) return p;
-        p.r = j;
-        if (c4 < ld1q) {
-          p.kind = 1; p.c = 4 * c4; p.wmask = 15;
-          const int e = s.w_off1 + j * s.ld1 + 4 * c4;
-          p.e[0] = e; p.e[1] = e + 1; p.e[2] = e + 2; p.e[3] = e + 3;
-        } else if (c4 == ld1q) {
-          p.kind = 2; p.wmask = 14;
-          p.e[0] = s.b_off1 + j;
-          if (s.C <= 3)
-            for (int k = 0; k < 3; ++k) if (k < s.C) p.e[1 + k] = s.w_off2 + k * s.ld2 + j;
-        } else {
-          p.kind = 3; p.c = 4 * (c4 - ld1q - 1); p.wmask = 15;
-          for (int l = 0; l < 4; ++l) if (p.c + l < s.C) p.e[l] = s.w_off2 + (p.c + l) * s.ld2 + j;
-        }
-      } else if (u < w2u + w1u) {
-        const int ir = (u - w2u) >> 2, c4 = (u - w2u) & 3, i = my_i0 + ir;
-        if (i >= s.h1) return p;
-        p.kind = 4; p.r = i; p.c = 4 * c4;
-        for (int l = 0; l < 4; ++l) {
-          const int col = 4 * c4 + l;
-          if (col < s.d0) { p.e[l] = s.w_off0 + i * s.ld0 + col; p.wmask |= 1 << l; }
-          else if (col == 15) p.e[l] = s.b_off0 + i;
-        }
-      } else if (q == CS - 1) {
-        const int t = u - w2u - w1u;
-        if (t < 2) {
-          p.kind = 5; p.c = 4 * t;
-          for (int l = 0; l < 4; ++l) if (4 * t + l < s.C) p.e[l] = s.b_off2 + 4 * t + l;
-        } else if (t == 2) {
-          p.kind = 6;
+    float* Mw = a.m + G.slab_off;
+    float* Vw = a.v + G.slab_off;
+    // float f of my share -> slab index (-1: padding / not mine; -2: the loss sum); bit 30 marks a weight (L2 applies)
+    auto plan = [&](int f) -> int {
+      if (f < w2f) {
+        const int jr = f / own.recf, c = f - jr * own.recf, j = my_j0 + jr;
+        if (j >= s.h2) return -1;
+        if (c < s.h1) return (s.w_off1 + j * s.ld1 + c) | (1 << 30);
+        if (c == s.ld1) return s.b_off1 + j;
+        const int k = c - s.ld1 - (s.C > 3 ? 4 : 1);
+        return (c > s.ld1 && k >= 0 && k < s.C) ? ((s.w_off2 + k * s.ld2 + j) | (1 << 30)) : -1;
+      }
+      if (f < w2f + w1f) {
+        const int t = f - w2f, i = my_i0 + (t >> 4), col = t & 15;
+        if (i >= s.h1) return -1;
+        if (col < s.d0) return (s.w_off0 + i * s.ld0 + col) | (1 << 30);
+        return col == 15 ? s.b_off0 + i : -1;
+      }
+      if (q != CS - 1 || f >= own.share) return -1;
+      const int t = f - w2f - w1f;
+      return t < s.C ? s.b_off2 + t : (t == 8 ? -2 : -1);
+    };
+    int te[TK];
+    float uw[TK], um[TK], uv[TK];
+    auto fetch = [&](int f0) {
+#pragma unroll
+      for (int i = 0; i < TK; ++i) {
+        te[i] = plan(f0 + i * XT);
+        uw[i] = um[i] = uv[i] = 0.f;
+        if (te[i] >= 0) {
+          const int e = te[i] & ~(1 << 30);
+          uw[i] = __ldcg(Pg + e);
+          if (use_m) um[i] = __ldcg(Mw + e);
+          if (use_v) uv[i] = __ldcg(Vw + e);
         }
       }
-      return p;
     };
-    auto load_unit = [&](const UnitX& p, float* w, float* mm, float* vv) {
-#pragma unroll
-      for (int l = 0; l < 4; ++l) w[l] = mm[l] = vv[l] = 0.f;
-      if (p.kind == 1) {
-        const float4 t = *reinterpret_cast<const float4*>(Pg + p.e[0]);
-        w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
-        if (use_m) { const float4 x = *reinterpret_cast<const float4*>(Mg + p.e[0]); mm[0] = x.x; mm[1] = x.y; mm[2] = x.z; mm[3] = x.w; }
-        if (use_v) { const float4 x = *reinterpret_cast<const float4*>(Vg + p.e[0]); vv[0] = x.x; vv[1] = x.y; vv[2] = x.z; vv[3] = x.w; }
-      } else {
-#pragma unroll
-        for (int l = 0; l < 4; ++l)
-          if (p.e[l] >= 0) {
-            w[l] = Pg[p.e[l]];
-            if (use_m) mm[l] = Mg[p.e[l]];
-            if (use_v) vv[l] = Vg[p.e[l]];
-          }
-      }
-    };
-    UnitX up = plan_unit(tid);
-    float uw[4], um[4], uv[4];
-    load_unit(up, uw, um, uv);
+    fetch(tid);
     tc::tc_fence_before();
     tc::fence_async_smem();
     __syncthreads();
     if (tid == 0) {
-      float* misc = stage + (CS - 1) * own.share + own.R2 * own.recf + own.R1 * 16;
+      float* misc = stage + (CS - 1) * own.share + w2f + w1f;
 #pragma unroll
       for (int i = 0; i < 9; ++i) misc[i == 0 ? 8 : i - 1] = red_f[0][i] + red_f[1][i];   // [db3[0..7], loss]
       sc_s = step_scalars_fast(G, step0 + st + 1);
@@ -809,107 +772,69 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
     }
     __syncthreads();
     if (CS > 1) {
-      if (tid < CS)   // block `tid` of my staging area -> slot `q` of owner `tid`
-        bulk_s2c(mapa(sm_u + SX_SLOTS + (uint32_t)(q * own.share) * 4u, tid), sm_u + SX_STAGE + (uint32_t)(tid * own.share) * 4u,
-                 (uint32_t)own.share * 4u, mapa(tc::smem_u32(&gbar), tid));
+      if (tid < CS) {   // my staging block for owner o -> slot `q` of owner o; the owners are visited in a rotated order so that
+                        // no receiver is the target of all senders at once
+        const int o = (q + 1 + tid) % CS;
+        bulk_s2c(mapa(sm_u + SX_SLOTS + (uint32_t)(q * own.share) * 4u, o), sm_u + SX_STAGE + (uint32_t)(o * own.share) * 4u,
+                 (uint32_t)own.share * 4u, mapa(tc::smem_u32(&gbar), o));
+      }
       mbar_wait_cluster(&gbar, gph);
       gph ^= 1;
     }
     STAMP(13);
 
-    // ---- owner: fixed-order sum of the CS partials, optimizer, new values into my own operand panels ------------------
+    // ---- owner: fixed-order sum of the CS partials, optimizer; master weights / moments (and, on the last step, this client's
+    // FedAvg term) go to global memory, from where every CTA rebuilds its operand image after the cluster barrier below
     {
       const StepScalars sc = sc_s;
       const float* parts = CS > 1 ? slots : stage;
       const bool emit_avg = avg_out != nullptr && st == a.n_steps - 1;
       const float al = G.alpha * inv_n;
 #pragma unroll 1
-      for (int u = tid; u < share4; u += XT) {
-        if (u != tid) { up = plan_unit(u); load_unit(up, uw, um, uv); }
-        if (up.kind == 0) continue;
-        float gs[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
-        for (int rk = 0; rk < CS; ++rk) {
-          const float4 p = *reinterpret_cast<const float4*>(parts + rk * own.share + 4 * u);
-          gs[0] += p.x; gs[1] += p.y; gs[2] += p.z; gs[3] += p.w;
-        }
-        if (up.kind == 6) {
-          if (a.loss_out) a.loss_out[g] = gs[0] * inv_n;
-          continue;
-        }
-        float av[4];
+      for (int f0 = tid; f0 < own.share; f0 += TK * XT) {
+        if (f0 != tid) fetch(f0);
+        float gs[TK];
 #pragma unroll
-        for (int l = 0; l < 4; ++l) {
-          av[l] = 0.f;
-          if (up.e[l] >= 0) {
-            const float gr = ((up.wmask >> l) & 1) ? fmaf(al, uw[l], gs[l]) : gs[l];
-            uw[l] = opt_update(G, sc, uw[l], gr, um[l], uv[l]);
-            av[l] = __fdiv_rn(__fmul_rn(uw[l], G.agg_num), G.agg_den);   // this client's FedAvg term (C:110-115)
+        for (int i = 0; i < TK; ++i) {
+          gs[i] = 0.f;
+          if (te[i] != -1) {
+#pragma unroll 4
+            for (int rk = 0; rk < CS; ++rk) gs[i] += parts[rk * own.share + f0 + i * XT];
           }
         }
-        float* Mw = a.m + G.slab_off;
-        float* Vw = a.v + G.slab_off;
-        if (up.kind == 1) {
-          const int e = up.e[0];
-          if (use_m) *reinterpret_cast<float4*>(Mw + e) = make_float4(um[0], um[1], um[2], um[3]);
-          if (use_v) *reinterpret_cast<float4*>(Vw + e) = make_float4(uv[0], uv[1], uv[2], uv[3]);
-          const float4 wv = make_float4(uw[0], uw[1], uw[2], uw[3]), avv = make_float4(av[0], av[1], av[2], av[3]);
-          if (emit_avg) *reinterpret_cast<float4*>(avg_out + e) = avv;
-          *reinterpret_cast<float4*>(Pg + e) = (emit_avg && inline_avg) ? avv : wv;
-          put_w2(sm, up.r, up.c, wv);
-        } else {
 #pragma unroll
-          for (int l = 0; l < 4; ++l)
-            if (up.e[l] >= 0) {
-              const int e = up.e[l];
-              if (use_m) Mw[e] = um[l];
-              if (use_v) Vw[e] = uv[l];
-              if (emit_avg) avg_out[e] = av[l];
-              Pg[e] = (emit_avg && inline_avg) ? av[l] : uw[l];
-            }
-          if (up.kind == 2) {
-            put_b2(sm, up.r, uw[0]);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) if (up.e[1 + k] >= 0) W3s[up.r * 8 + k] = uw[1 + k];
-          } else if (up.kind == 3) {
-#pragma unroll
-            for (int l = 0; l < 4; ++l) if (up.e[l] >= 0) W3s[up.r * 8 + up.c + l] = uw[l];
-          } else if (up.kind == 4) {
-            put_w1(sm, up.r, up.c, make_float4(uw[0], uw[1], uw[2], uw[3]));
-          } else {
-#pragma unroll
-            for (int l = 0; l < 4; ++l) if (up.e[l] >= 0) b3s[up.c + l] = uw[l];
+        for (int i = 0; i < TK; ++i) {
+          if (te[i] == -2) {
+            if (a.loss_out) a.loss_out[g] = gs[i] * inv_n;
+          } else if (te[i] >= 0) {
+            const int e = te[i] & ~(1 << 30);
+            const float gr = (te[i] >> 30) ? fmaf(al, uw[i], gs[i]) : gs[i];
+            const float w = opt_update(G, sc, uw[i], gr, um[i], uv[i]);
+            if (use_m) Mw[e] = um[i];
+            if (use_v) Vw[e] = uv[i];
+            Pg[e] = w;
+            if (emit_avg) avg_out[e] = __fdiv_rn(__fmul_rn(w, G.agg_num), G.agg_den);   // (w n_k) / N, C:110-115
           }
         }
       }
     }
     STAMP(14);
-    // ---- all-gather: my rows (already in panel format) -> the same offsets of every peer's panels ------------------------
-    tc::fence_async_smem();
-    __syncthreads();
-    if (CS > 1) {
-      if (tid < CS && tid != q) {
-        if (avg_out && st == a.n_steps - 1) __threadfence_system();   // my partial's stores precede the signal the peers' flag rests on
-        const uint32_t base = mapa(sm_u, tid), pb = mapa(tc::smem_u32(&pbar), tid);
-        if (my_n2 > 0) {
-          bulk_s2c(base + SX_W2 + my_j0 * 128, sm_u + SX_W2 + my_j0 * 128, (uint32_t)my_n2 * 128u, pb);
-          bulk_s2c(base + SX_W2L + my_j0 * 128, sm_u + SX_W2L + my_j0 * 128, (uint32_t)my_n2 * 128u, pb);
-          bulk_s2c(base + SX_W3 + my_j0 * 32, sm_u + SX_W3 + my_j0 * 32, (uint32_t)my_n2 * 32u, pb);
-        }
-        if (my_n1 > 0) bulk_s2c(base + SX_W1 + my_i0 * 128, sm_u + SX_W1 + my_i0 * 128, (uint32_t)my_n1 * 128u, pb);
-        if (q == CS - 1) bulk_s2c(base + SX_B3, sm_u + SX_B3, 32u, pb);
-      }
-      if (pub_in) { mbar_wait_cluster(&pbar, pph); pph ^= 1; }
-    }
+    // ---- all-gather through L2 (its path into an SM is several times wider than the SM-to-SM fabric): every owner's stores
+    // are ordered before the barrier, the bulk load of the whole slab after it; the staging area is free again by then (all
+    // owners have passed their wait, so every outgoing copy has completed)
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    if (tid == 0) bulk_load_begin_x(reinterpret_cast<uint8_t*>(landing), Pg, (uint32_t)s.end * 4u, &wbar);
     if (a.tail_mode == 2 && st == a.n_steps - 1 && q == 0 && tid < a.p2p->world) {
       // arrival flag A ("my partial is complete") into every peer GPU's buffer; the local evaluation below overlaps its
-      // flight.  Every owner fenced its partial stores at system scope before publishing, and this CTA has received
-      // every publication: fence + release make them visible to whoever acquires the flag.
+      // flight.  The cluster barrier ordered every owner's stores before this thread: fence + release make them visible
+      // to whoever acquires the flag.
       __threadfence_system();
       uint64_t* pf = reinterpret_cast<uint64_t*>(a.p2p->sym[tid] + a.p2p->sym_flag_off);
       st_release_sys_u64(pf + a.p2p->rank, p2p_seq + 1);
     }
     STAMP(15);
+    tc::mbar_wait(&wbar, wph); wph ^= 1;
+    convert_weights_x(sm, landing, s);
     STAMP(16);
   }  // steps
 
@@ -1037,9 +962,9 @@ __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
     if (!s_last) return;
     __threadfence();
   }
-  if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[18] = clock64();
+  if (a.prof && threadIdx.x == 0) tc_stamp(a, crank, 18);
   round_tail(a, crank, CS, s_stop, avg_done);
-  if (a.prof && crank == CS - 1 && threadIdx.x == 0) a.prof[19] = clock64();
+  if (a.prof && threadIdx.x == 0) tc_stamp(a, crank, 19);
 }
 
 }  // namespace fedb
@@ -1122,7 +1047,7 @@ extern "C" int fedb_local_round_tcx(const FedbGroup* groups, int32_t n_groups, i
   TcArgs a{};
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
   a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = batch;
-  a.n_steps = n_steps; a.do_eval = do_eval; a.prof = prof; a.tail_mode = 0;
+  a.n_steps = n_steps; a.do_eval = do_eval; a.prof = prof; a.prof_stride = 32; a.tail_mode = 0;
   return launch_tcx(a, n_groups, cluster_size, stream);
 }
 
@@ -1138,7 +1063,7 @@ extern "C" int fedb_round_tcx(const FedbGroup* groups, int32_t n_groups, int32_t
   a.x_host = x_host; a.y_host = y_host;
   a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
   a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
-  a.n_steps = n_steps; a.do_eval = 1; a.prof = prof;
+  a.n_steps = n_steps; a.do_eval = 1; a.prof = prof; a.prof_stride = 32;
   a.tail_mode = 1; a.n_groups = n_groups; a.n_feds = n_feds; a.n_conf = conf_ints; a.feds = feds; a.fed_state_rw = fed_state;
   a.global = global; a.hist_local = hist_local; a.hist_global = hist_global; a.tail_count = tail_count;
   a.state_mirror = state_mirror;

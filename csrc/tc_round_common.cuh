@@ -32,6 +32,7 @@ struct TcArgs {
   float* scratch;   // per-group gradient records (FedbGroup::scratch_off; >= cluster_size records each)
   int ldx, batch, n_steps, do_eval;
   long long* prof;  // optional: clock64 stamps of CTA 0 / thread 0 (debug, tools/tc_timeline.py)
+  int prof_stride;  // 0: as above; n > 0: globaltimer nanoseconds, CTA r of the first cluster writes prof[r * n + i]
   // ---- fused round tail (tail_mode 1): the last cluster to finish aggregates every federation ----
   int tail_mode, n_groups, n_feds, n_conf;
   const FedbFed* feds;
@@ -44,6 +45,13 @@ struct TcArgs {
   const FedbP2PRank* p2p;
   FedbFedState* state_mirror;   // optional: mapped pinned host copy of the federation state, written by the tail
 };
+
+__device__ __forceinline__ void tc_stamp(const TcArgs& a, int crank, int i) {
+  long long t;
+  if (a.prof_stride) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  else t = clock64();
+  a.prof[crank * a.prof_stride + i] = t;
+}
 
 // One copy of the metrics / early-stop code for both tails (it runs once per round on one warp; inlined twice it is ~4000
 // instructions of mostly double-precision code that a cache-cold round has to fetch).
@@ -58,8 +66,9 @@ static __device__ __noinline__ void round_metrics_ni(const FedbFed* F, FedbFedSt
 // stop (C:165-192), then the next round's begin bookkeeping — same results as k_fedavg.
 constexpr int TAIL_MAX_FEDS = 256, TAIL_MAX_CLIENTS = 32;
 
-// skip_avg: the caller's optimizer phase has already written the FedAvg result into the global arena and the slabs (the
-// single-client federation of the split-operand kernel); only metrics / early stop / bookkeeping are left.
+// skip_avg: the caller's optimizer phase has already written the FedAvg result into the global arena (the single-client
+// federation of the split-operand kernel); what is left is the write-back into the client's slab (C:119-120), metrics, early
+// stop and bookkeeping.
 static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop, bool skip_avg = false) {
   const int tid = threadIdx.x, NT = (int)blockDim.x;
   __shared__ long long t_off[TAIL_MAX_CLIENTS];
@@ -68,6 +77,17 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
   // others average; with a single CTA it does both
   const int mrank = csize - 1, workers = csize > 1 ? csize - 1 : 1;
   const int nthr = workers * NT, gt = crank * NT + tid;
+  if (skip_avg && (csize == 1 || crank != mrank)) {
+    for (int f = 0; f < a.n_feds; ++f) {
+      if (s_stop[f]) continue;
+      const FedbFed F = a.feds[f];
+      const float4* src = reinterpret_cast<const float4*>(a.global + F.global_off);
+      for (int k = 0; k < F.n_clients; ++k) {
+        float4* dst = reinterpret_cast<float4*>(a.params + a.groups[F.first_group + k].slab_off);
+        for (int e4 = gt; e4 < (F.slab_size >> 2); e4 += nthr) dst[e4] = __ldcg(src + e4);
+      }
+    }
+  }
   for (int f = 0; f < a.n_feds && !skip_avg && (csize == 1 || crank != mrank); ++f) {
     if (s_stop[f]) continue;
     const FedbFed F = a.feds[f];
@@ -109,7 +129,7 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
       }
     }
   }
-  if (a.prof && crank == 0 && tid == 0) a.prof[20] = clock64();
+  if (a.prof && crank == 0 && tid == 0) tc_stamp(a, crank, 20);
   if (crank == mrank) {
     __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
     if (tid < 32)
@@ -120,7 +140,7 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
                            a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
       }
     __syncthreads();
-    if (a.prof && tid == 0) a.prof[21] = clock64();
+    if (a.prof && tid == 0) tc_stamp(a, crank, 21);
     for (int i = tid; i < a.n_conf; i += NT) a.conf[i] = 0;
   }
 }
