@@ -20,6 +20,42 @@ def _bench(port, env_extra=None):
     return json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
 
 
+def _dist_run(tmp_path, name, port, n_clients, rows, rounds, precision, env_extra=None, nproc=2):
+    out = str(tmp_path / f"{name}.npz")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "_dist_worker.py"), out, str(n_clients), str(rows), str(rounds), precision]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, **(env_extra or {})))
+    assert r.returncode == 0, r.stderr[-3000:]
+    import numpy as np
+    return np.load(out)
+
+
+@pytest.mark.parametrize("precision", ["tc32", "bf16"])
+def test_two_gpu_global_model_is_bitwise_the_single_gpu_one(tmp_path, precision):
+    """Two clients on two GPUs (one launch per rank per round, aggregation inside the round kernel over NVLink peer memory)
+    against the same two clients on ONE GPU: the global model after 12 rounds, the metric history, and every rank's copy
+    of the global model are bit-identical.  Also with the stand-alone aggregation kernel."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, ROOT)
+    from fedb200 import FedEngine, FedProblem, prepare
+    rows, rounds = 1000, 12
+    data = prepare(with_mean=True)
+    shards = [np.arange(c * rows, (c + 1) * rows, dtype=np.int32) for c in range(2)]
+    one = FedEngine([FedProblem.custom(data.n_features, data.n_classes, shards, patience=0)], data.X_train, data.y_train,
+                    data.X_test, data.y_test, device="cuda", max_rounds=rounds + 4, precision=precision)
+    h = one.run(rounds)
+    want = one.global_.cpu().numpy()
+    fused = _dist_run(tmp_path, "fused", 29551, 2, rows, rounds, precision)
+    assert int(fused["launches"]) == 1 and "p2p-fedavg" in str(fused["kernels"][0]) and str(fused["precision"]) == precision
+    assert np.array_equal(fused["global_"], want)
+    assert np.array_equal(fused["globals_all"][0], fused["globals_all"][1])
+    assert np.array_equal(fused["hist"], h["global"]) and np.array_equal(fused["local"], h["local"])
+    sep = _dist_run(tmp_path, "sep", 29552, 2, rows, rounds, precision, {"FEDB200_NO_FUSED_P2P": "1"})
+    assert int(sep["launches"]) > 1
+    assert np.array_equal(sep["global_"], want) and np.array_equal(sep["hist"], h["global"])
+
+
 def test_two_gpu_bench_fused_and_standalone_aggregation_agree():
     fused = _bench(29541)
     assert fused["n_gpus"] == 2 and fused["value"] > 0 and any("p2p-fedavg" in k for k in fused["kernels"])
