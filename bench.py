@@ -137,7 +137,11 @@ def run_ours(args):
             eng.step_graph()
             e.record()
         barrier()
-        ms_flushed = sum(s.elapsed_time(e) for s, e in ev)
+        step_ms = sorted(s.elapsed_time(e) for s, e in ev)
+        ms_flushed = sum(step_ms)
+        # the metric both arms report at the same round index: after exactly warmup + steps rounds (the timing loops below train on)
+        acc_round = W + K
+        acc_at_round = float(eng.history()["global"][0][acc_round - 1][0])
         # steady state, back to back, no flush (reported separately, never as `value`)
         s0, e0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
@@ -188,8 +192,12 @@ def run_ours(args):
                        "{round counter, stop flag, metric}; the host polls the chunks and reads the result"},
         "gpu_launches": K * eng.launches_per_round, "launches_per_step": eng.launches_per_round,
         "kernels": eng.kernel_names, "clocks": clk.summary(),
+        "step_ms": {"min": step_ms[0], "median": step_ms[len(step_ms) // 2], "max": step_ms[-1],
+                    "p90": step_ms[min(len(step_ms) - 1, (9 * len(step_ms)) // 10)]},
+        "global_accuracy_train_shards": {"round": acc_round, "value": acc_at_round},
         "final_global_accuracy_train_shards": float(hist["last"][0][0]), "rounds_run": int(hist["rounds"][0]),
     })
+    eng.check_errors()    # a timed-out peer or a stalled GEMM pipeline raises here instead of passing silently
     if rank == 0:
         print(json.dumps(rec))
     if world > 1:
@@ -246,8 +254,8 @@ def run_reference(args):
         rec = base_record(args, world, "reference")
         samples = world * ROWS_PER_CLIENT
         value = samples * K / dt
-        rec["config"]["l2"] = "n/a (stock reference path; wall clock around train_and_evaluate, max over ranks)"
-        rec["config"]["parallelism"] = f"{world} ranks = {world} clients over an mpi4py stand-in (gloo), device={'cuda' if cuda else 'cpu'}"
+        rec["arm_notes"] = {"timing": "stock reference path: wall clock around train_and_evaluate, max over ranks; no L2 flush",
+                            "transport": f"{world} ranks = {world} clients over an mpi4py stand-in (gloo), device={'cuda' if cuda else 'cpu'}"}
         rec.update({
             "value": value, "ms_per_step": dt * 1e3 / K, "vs_baseline": value / BASELINE_SAMPLES_PER_SEC, "dtype": "fp32",
             "rounds_per_sec": K / dt,
@@ -256,6 +264,7 @@ def run_reference(args):
                     "h2d_bytes_per_step": 2 * (ROWS_PER_CLIENT * 14 * 4 + ROWS_PER_CLIENT * 8) + 11352 * 4,
                     "d2h_bytes_per_step": ROWS_PER_CLIENT * 8 + 11352 * 4},
             "gpu_launches": None, "clocks": clk.summary(),
+            "global_accuracy_train_shards": {"round": W + K, "value": float(hist["accuracy"][-1]) if hist["accuracy"] else None},
             "final_global_accuracy_train_shards": float(hist["accuracy"][-1]) if hist["accuracy"] else None,
         })
         print(json.dumps(rec))
@@ -306,7 +315,7 @@ def run_nccl(args):
         rec = base_record(args, world, "nccl_cublas_baseline")
         samples = world * cpg * ROWS_PER_CLIENT
         value = samples * K / (ms / 1e3)
-        rec["config"]["parallelism"] = f"{world} ranks, torch.nn + torch.optim + NCCL all_reduce FedAvg"
+        rec["arm_notes"] = {"transport": f"{world} ranks, torch.nn + torch.optim + NCCL all_reduce FedAvg"}
         rec.update({"value": value, "ms_per_step": ms / K, "vs_baseline": value / BASELINE_SAMPLES_PER_SEC, "dtype": "fp32",
                     "rounds_per_sec": K / (ms / 1e3), "gpu_launches": None, "clocks": clk.summary(),
                     "final_global_accuracy_train_shards": float(fed.last_metrics[0])})

@@ -276,8 +276,10 @@ __device__ inline void begin_next_round(FedbFedState& S) {
 // (F is taken BY VALUE: through a pointer every field access may be re-fetched from L2 after each store)
 __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int f, int n_groups, const int32_t* conf,
                                           float* hist_local, float* hist_global, int* pool, bool begin_next = false,
-                                          FedbFedState* host_mirror = nullptr, void* host_result = nullptr) {
+                                          FedbFedState* host_mirror = nullptr, void* host_result = nullptr, long long* stamps = nullptr) {
   const int lane = threadIdx.x & 31;
+#define FEDB_MSTAMP(i) do { if (stamps && lane == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); stamps[i] = t_; } } while (0)
+  FEDB_MSTAMP(0);
   const int C = F.n_classes;
   const int r = S.round - 1;  // 0-based index of the round in progress
   const bool pooled = F.metric_mode == FEDB_METRIC_POOLED;
@@ -298,11 +300,13 @@ __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int 
       for (int i = 0; i < C; ++i)
         for (int j = 0; j < C; ++j) atomicAdd(&pool[i * FEDB_MAX_CLASSES + j], cm[i * FEDB_MAX_CLASSES + j]);
   }
+  FEDB_MSTAMP(1);
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
   __syncwarp();
+  FEDB_MSTAMP(2);
   if (lane == 0) {
     double glob[4];
     if (pooled) metrics_from_conf(pool, C, glob);
@@ -331,6 +335,8 @@ __device__ inline void round_metrics_warp(const FedbFed F, FedbFedState& S, int 
       }
     }
   }
+  FEDB_MSTAMP(3);
+#undef FEDB_MSTAMP
   __syncwarp();
 }
 

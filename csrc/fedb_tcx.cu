@@ -69,7 +69,7 @@ constexpr int SX_W3 = SX_W2L + 256 * 128;    // fp32 [256 units][8 classes]
 constexpr int SX_B3 = SX_W3 + 256 * 8 * 4;   // fp32 [8]
 constexpr int SX_END = SX_B3 + 256;
 constexpr int SX_SLOTS = SX_END;              // [CS senders][share] floats: the partials this CTA owns
-constexpr int SX_SLOTS_MAX = 227 * 1024 - 4096 - SX_SLOTS;
+constexpr int SX_SLOTS_MAX = 227 * 1024 - 6144 - SX_SLOTS;   // (static shared memory of the kernel and its tails: < 5 KB, + 1 KB alignment)
 constexpr int SX_STAGE = SX_H1;               // outgoing partials [CS owners][share] (and the fp32 slab at launch) overlay H1..Z
 constexpr int SX_STAGE_MAX = 10 * XP;
 constexpr int DZ3_COL = 32;                   // first column of [dZ3 hi | dZ3 lo] inside the X panel
@@ -352,7 +352,7 @@ struct IssuerX {
 
 // Returns true when the optimizer phase has already produced the FedAvg result (single-client federation on one GPU:
 // global = (w n) / n written by the owners, C:110-115), so the tail only scores the round.
-__device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw) {
+__device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw, TailPre* pre) {
   __shared__ uint64_t bar, wbar, gbar;   // MMA phase done | fp32 slab landed | every sender's partials for my rows are in
   __shared__ uint32_t tmem_slot;
   __shared__ float red_f[2][9];   // per-warp partial sums: loss + db3[8]
@@ -921,8 +921,16 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
     }
     tc::tmem_ld_wait();
     __syncthreads();
-    if (tid < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES && cnt[tid] != 0)
-      atomicAdd(a.conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + tid, cnt[tid]);
+    if (!cluster_waited) {   // (evaluation-only launch: the peers' shared memory is initialised once this completes)
+      asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+      cluster_waited = true;
+    }
+    if (tid < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES && cnt[tid] != 0) {
+      if (a.tail_mode != 0 && gridDim.x == (unsigned)CS)   // single cluster: straight into the scoring CTA's shared memory
+        asm volatile("red.relaxed.cluster.shared::cluster.add.u32 [%0], %1;" ::"r"(mapa(tc::smem_u32(&pre->cnt[tid]), CS - 1)), "r"((uint32_t)cnt[tid]) : "memory");
+      else
+        atomicAdd(a.conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + tid, cnt[tid]);
+    }
     STAMP(17);
   }
 #undef FEDB_MMA_PHASE
@@ -941,9 +949,19 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw)
 
 __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  const bool avg_done = round_body_x(a, smem_raw);
+  __shared__ TailPre pre;
+  {
+    cg::cluster_group cl = cg::this_cluster();
+    const bool single = gridDim.x == cl.num_blocks();
+    if (threadIdx.x < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES) pre.cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { pre.have_fs = 0; pre.have_cnt = (a.tail_mode != 0 && single) ? 1 : 0; }
+    __syncthreads();
+    // the scoring CTA's last warp (idle in every epilogue) fetches the federation record / state while the round runs
+    if (a.tail_mode != 0 && cl.block_rank() == cl.num_blocks() - 1 && (threadIdx.x >> 5) == XT / 32 - 1) tail_prefetch(a, &pre);
+  }
+  const bool avg_done = round_body_x(a, smem_raw, &pre);
   if (a.tail_mode == 0) return;
-  if (a.tail_mode == 2) { p2p_tail(a); return; }
+  if (a.tail_mode == 2) { p2p_tail(a, &pre); return; }
   // the cluster that observes the last check-in runs the single-GPU aggregation tail (see k_local_round_tc)
   __shared__ unsigned int s_last;
   __shared__ unsigned char s_stop[TAIL_MAX_FEDS];
@@ -963,7 +981,7 @@ __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
     __threadfence();
   }
   if (a.prof && threadIdx.x == 0) tc_stamp(a, crank, 18);
-  round_tail(a, crank, CS, s_stop, avg_done);
+  round_tail(a, crank, CS, s_stop, avg_done, &pre);
   if (a.prof && threadIdx.x == 0) tc_stamp(a, crank, 19);
 }
 

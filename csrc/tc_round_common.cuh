@@ -46,6 +46,34 @@ struct TcArgs {
   FedbFedState* state_mirror;   // optional: mapped pinned host copy of the federation state, written by the tail
 };
 
+// What a round kernel can hand its tail in shared memory of the cluster's LAST CTA (the one that scores the round):
+// the federation record and state fetched at kernel start (they change only when the tail itself writes them), and — when the
+// grid is a single cluster — the confusion counts of the local evaluation, added up over distributed shared memory, so the
+// tail starts computing without a chain of L2 round trips.
+struct TailPre {
+  FedbFed F;
+  FedbFedState S;
+  int32_t cnt[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
+  int32_t conf_all[8 * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];   // cross-GPU tail: every rank's counts (one client per rank, <= 8 ranks)
+  int32_t have_fs, have_cnt;
+};
+// (whole warp) fetch F / S of the only federation into *pre
+__device__ __forceinline__ void tail_prefetch(const TcArgs& a, TailPre* pre) {
+  const int lane = threadIdx.x & 31;
+  const FedbFed* F = nullptr;
+  const FedbFedState* S = nullptr;
+  if (a.tail_mode == 1 && a.n_feds == 1) { F = a.feds; S = a.fed_state_rw; }
+  if (a.tail_mode == 2) { F = a.p2p->feds_global; S = a.p2p->fed_state; }
+  if (!F) return;
+  for (int i = lane; i < (int)(sizeof(FedbFed) / 4); i += 32) reinterpret_cast<int32_t*>(&pre->F)[i] = reinterpret_cast<const int32_t*>(F)[i];
+  for (int i = lane; i < (int)(sizeof(FedbFedState) / 4); i += 32) reinterpret_cast<int32_t*>(&pre->S)[i] = reinterpret_cast<const int32_t*>(S)[i];
+  __syncwarp();
+  if (lane == 0) pre->have_fs = 1;
+}
+__device__ __forceinline__ void st_relaxed_sys_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ void tc_stamp(const TcArgs& a, int crank, int i) {
   long long t;
   if (a.prof_stride) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -55,10 +83,12 @@ __device__ __forceinline__ void tc_stamp(const TcArgs& a, int crank, int i) {
 
 // One copy of the metrics / early-stop code for both tails (it runs once per round on one warp; inlined twice it is ~4000
 // instructions of mostly double-precision code that a cache-cold round has to fetch).
+// S_out (optional): S is a shared-memory copy fetched early; the updated state is stored to *S_out as well.
 static __device__ __noinline__ void round_metrics_ni(const FedbFed* F, FedbFedState* S, int f, int n_groups, const int32_t* conf,
                                                      float* hist_local, float* hist_global, int* pool, FedbFedState* host_mirror,
-                                                     void* host_result) {
-  round_metrics_warp(*F, *S, f, n_groups, conf, hist_local, hist_global, pool, true, host_mirror, host_result);
+                                                     void* host_result, FedbFedState* S_out = nullptr, long long* stamps = nullptr) {
+  round_metrics_warp(*F, *S, f, n_groups, conf, hist_local, hist_global, pool, true, host_mirror, host_result, stamps);
+  if (S_out && (threadIdx.x & 31) == 0) *S_out = *S;
 }
 
 // K1 + K5 for small problems, executed by the last cluster to finish: FedAvg of every federation in
@@ -69,7 +99,8 @@ constexpr int TAIL_MAX_FEDS = 256, TAIL_MAX_CLIENTS = 32;
 // skip_avg: the caller's optimizer phase has already written the FedAvg result into the global arena (the single-client
 // federation of the split-operand kernel); what is left is the write-back into the client's slab (C:119-120), metrics, early
 // stop and bookkeeping.
-static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop, bool skip_avg = false) {
+static __device__ void round_tail(const TcArgs& a, int crank, int csize, const unsigned char* s_stop, bool skip_avg = false,
+                                  TailPre* pre = nullptr) {
   const int tid = threadIdx.x, NT = (int)blockDim.x;
   __shared__ long long t_off[TAIL_MAX_CLIENTS];
   __shared__ float t_num[TAIL_MAX_CLIENTS], t_den[TAIL_MAX_CLIENTS];
@@ -135,9 +166,12 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
     if (tid < 32)
       for (int f = 0; f < a.n_feds; ++f) {
         if (s_stop[f]) continue;
-        round_metrics_ni(a.feds + f, a.fed_state_rw + f, f, a.n_groups, a.conf, a.hist_local, a.hist_global, pool,
+        const bool fs = pre && pre->have_fs && a.n_feds == 1;
+        round_metrics_ni(fs ? &pre->F : a.feds + f, fs ? &pre->S : a.fed_state_rw + f, f, a.n_groups,
+                           (pre && pre->have_cnt) ? pre->cnt : a.conf, a.hist_local, a.hist_global, pool,
                            a.state_mirror ? a.state_mirror + f : nullptr,
-                           a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
+                           a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * a.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr,
+                           fs ? a.fed_state_rw + f : nullptr, (a.prof && a.prof_stride) ? a.prof + crank * a.prof_stride + 22 : nullptr);
       }
     __syncthreads();
     if (a.prof && tid == 0) tc_stamp(a, crank, 21);
@@ -145,13 +179,15 @@ static __device__ void round_tail(const TcArgs& a, int crank, int csize, const u
   }
 }
 
-// Cross-GPU FedAvg fused into the round kernel (one federation, one resident client per rank): the
-// protocol of k_fedavg_p2p (csrc/fedb_p2p.cu) executed by the client's own cluster.  The partial
-// (w * n_k) / N was published by the optimizer phase and flag A raised BEFORE the local evaluation, so
-// the NVLink latency hides behind it; here the confusion counts follow (flag B), every CTA but the last
-// sums the R partials in rank order with peer loads and writes the global model + the client's slab,
-// and the last CTA scores the round from all ranks' counts and does the next round's bookkeeping.
-static __device__ void p2p_tail(const TcArgs& a) {
+// Cross-GPU FedAvg fused into the round kernel (one federation, one resident client per rank): the protocol of k_fedavg_p2p
+// (csrc/fedb_p2p.cu) executed by the client's own cluster.  The partial (w * n_k) / N was published by the optimizer phase
+// and flag A raised BEFORE the local evaluation, so that NVLink flight hides behind it.  After the evaluation the last CTA
+// pushes this rank's confusion counts into every peer's buffer as SELF-VALIDATING words — the count in the low 24 bits, the
+// low 8 bits of the round's sequence number above them — so the receiver polls the words themselves: one one-way NVLink
+// flight on the critical path, no flag, no system-scope fence (the area is double-buffered by round parity; a shard has
+// fewer than 2^24 rows).  Meanwhile every other CTA sums the R partials in rank order with peer loads and writes the global
+// model + the client's slab; the last CTA scores the round from all ranks' counts and does the next round's bookkeeping.
+static __device__ void p2p_tail(const TcArgs& a, TailPre* pre = nullptr) {
   cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
   const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x, NT = (int)blockDim.x;
   __shared__ FedbP2PRank R;
@@ -162,26 +198,25 @@ static __device__ void p2p_tail(const TcArgs& a) {
   __syncthreads();
   const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
   const int par = (int)(seq & 1);
+  const uint32_t tag = (uint32_t)((seq + 1) & 0xFF) << 24;
   const bool stopped = R.fed_state[0].stop != 0;   // as it stands for THIS round
   __threadfence();
-  cluster.sync();                                   // all CTAs: evaluation counts are in a.conf; seq / stop have been read
+  cluster.sync();                                   // all CTAs: evaluation counts are complete; seq / stop have been read
   if (stopped) return;
   const long long t0 = clock64();
-  const int64_t conf_stride = (int64_t)R.conf_slots * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  constexpr int C2 = FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  const int64_t conf_stride = (int64_t)R.conf_slots * C2;
   uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
-  if (crank == 0) {   // PUSH this rank's confusion counts into every peer's area (parity, my rank), then flag B
-    const int nconf = R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
+  const bool smem_cnt = pre && pre->have_cnt;
+  if (crank == mrank) {   // PUSH this rank's tagged confusion counts into every peer's area (parity, my rank)
+    const int nconf = R.n_groups_local * C2;
     for (int i = tid; i < nconf * R.world; i += NT) {
       const int qq = i / nconf, w = i - qq * nconf;
-      reinterpret_cast<int32_t*>(R.sym[qq] + R.sym_conf_off)[(par * 8 + R.rank) * conf_stride + w] = __ldcg(a.conf + w);
-    }
-    __syncthreads();
-    if (tid < R.world) {
-      __threadfence_system();
-      st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + 8 + R.rank, seq + 1);
+      const uint32_t c = (uint32_t)(smem_cnt ? pre->cnt[w] : __ldcg(a.conf + w));
+      st_relaxed_sys_u32(reinterpret_cast<uint32_t*>(R.sym[qq] + R.sym_conf_off) + (par * 8 + R.rank) * conf_stride + w, (c & 0xFFFFFFu) | tag);
     }
   }
-  const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
   if (CS == 1 || crank != mrank) {   // ---- aggregation: wait for every peer's partial (flag A), sum in rank order
     if (tid < R.world)
       while (ld_acquire_sys_u64(my_flags + tid) < seq + 1)
@@ -206,25 +241,31 @@ static __device__ void p2p_tail(const TcArgs& a) {
       if (R.write_back) slab[e4] = acc;
     }
   }
-  if (crank == mrank) {              // ---- metrics from every rank's counts (flag B), early stop, next round's begin
-    if (tid < R.world)
-      while (ld_acquire_sys_u64(my_flags + 8 + tid) < seq + 1)
-        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
-    __syncthreads();
-    for (int i = tid; i < R.n_groups_total * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += NT) {
-      const int slot = i / (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES), w = i - slot * (FEDB_MAX_CLASSES * FEDB_MAX_CLASSES);
+  if (crank == mrank) {              // ---- metrics from every rank's counts, early stop, next round's begin
+    __shared__ int pool[C2];
+    int* conf_all = (pre && R.n_groups_total <= 8) ? pre->conf_all : R.conf_all;
+    for (int i = tid; i < R.n_groups_total * C2; i += NT) {
+      const int slot = i / C2, w = i - slot * C2;
       const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
-      // the counts were pushed into THIS rank's buffer by their owners: a local read, no NVLink round trip
-      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + qq) * conf_stride;
-      R.conf_all[i] = ld_relaxed_sys_i32(cq + ls * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + w);
+      // pushed into THIS rank's buffer by their owners: poll the local word until it carries this round's tag
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + qq) * conf_stride + ls * C2 + w;
+      uint32_t v = (uint32_t)ld_relaxed_sys_i32(cq);
+      while ((v & 0xFF000000u) != tag) {
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+        v = (uint32_t)ld_relaxed_sys_i32(cq);
+      }
+      conf_all[i] = (int32_t)(v & 0xFFFFFFu);
     }
     __syncthreads();
-    __shared__ int pool[FEDB_MAX_CLASSES * FEDB_MAX_CLASSES];
-    if (tid < 32 && R.do_metrics)
-      round_metrics_ni(R.feds_global, R.fed_state, 0, R.n_groups_total, R.conf_all, R.hist_local, R.hist_global, pool,
-                         a.state_mirror, a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) + 15) & ~size_t(15)) : nullptr);
+    if (tid < 32 && R.do_metrics) {
+      const bool fs = pre && pre->have_fs;
+      round_metrics_ni(fs ? &pre->F : R.feds_global, fs ? &pre->S : R.fed_state, 0, R.n_groups_total, conf_all, R.hist_local, R.hist_global,
+                       pool, a.state_mirror, a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) + 15) & ~size_t(15)) : nullptr,
+                       fs ? R.fed_state : nullptr);
+    }
     __syncthreads();
-    for (int i = tid; i < R.n_groups_local * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES; i += NT) a.conf[i] = 0;
+    if (!smem_cnt)
+      for (int i = tid; i < R.n_groups_local * C2; i += NT) a.conf[i] = 0;
     if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
   }
   __syncthreads();

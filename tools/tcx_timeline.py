@@ -13,8 +13,9 @@ from fedb200.ops import tc  # noqa: E402
 
 NAMES = {0: "start", 1: "weights converted", 2: "X stored", 3: "fwd1 mma", 4: "epi1", 5: "fwd2 mma", 6: "epi2a", 7: "wgrad3 mma", 8: "epi2b",
          9: "dgrad2+wgrad2 mma", 10: "epi3", 11: "wgrad1 mma", 12: "grads staged", 13: "partials in", 14: "optimizer done", 15: "barrier",
-         16: "weights converted", 17: "eval done", 18: "tail begins", 20: "write-back done", 21: "metrics done", 19: "end"}
-ORDER = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 20, 21, 19]
+         16: "weights converted", 17: "eval done", 18: "tail begins", 20: "write-back done", 21: "metrics done", 19: "end",
+         22: "metrics: entry", 23: "metrics: per-client done", 24: "metrics: reduced", 25: "metrics: state written"}
+ORDER = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 20, 22, 23, 24, 25, 21, 19]
 
 if __name__ == "__main__":
     rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
