@@ -303,7 +303,9 @@ __global__ void k_shuffle(const FedbGroup* __restrict__ groups, const int32_t* _
   int bits = 1;
   while ((1u << bits) < n) ++bits;
   const int half = (bits + 1) >> 1;
-  const uint32_t ka = s0 ^ (uint32_t)(g * 0x9E3779B1u), kb = s1 + (uint32_t)epoch[g];
+  // keyed by the client's index inside its federation, not by its position in the packed table: a federation shuffles
+  // the same way whichever other federations share the launch (or the GPU)
+  const uint32_t ka = s0 ^ (uint32_t)(G.client * 0x9E3779B1u), kb = s1 + (uint32_t)epoch[g];
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     idx_out[G.idx_off + i] = idx_in[G.idx_off + feistel_perm(i, n, half, ka, kb)];
 }
@@ -588,7 +590,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) k_fit_cluster(const FitArgs a
   for (int ep = 0; ep < a.max_epochs; ++ep) {
     if (!__ldcg(a.active + g)) break;                       // same value in every CTA: written before the last cluster barrier
     if (a.shuffle) {
-      const uint32_t ka = a.s0 ^ (uint32_t)(g * 0x9E3779B1u), kb = a.s1 + (uint32_t)__ldcg(a.epoch + g);
+      const uint32_t ka = a.s0 ^ (uint32_t)(G.client * 0x9E3779B1u), kb = a.s1 + (uint32_t)__ldcg(a.epoch + g);
       for (uint32_t i = q * blockDim.x + threadIdx.x; i < (uint32_t)n; i += CS * blockDim.x)
         a.idx_epoch[G.idx_off + i] = a.idx_in[G.idx_off + feistel_perm(i, n, half, ka, kb)];
       __threadfence();

@@ -68,12 +68,16 @@ def build_parser() -> argparse.ArgumentParser:
     s.add_argument("--max-iter", type=int, default=300)                      # S:81
     s.add_argument("--policy", default="warm_start", choices=["warm_start", "reference_faithful", "sklearn_literal"])
     s.add_argument("--reference-faithful", action="store_const", const="reference_faithful", dest="policy")
+    s.add_argument("--shuffle", default="feistel", choices=["feistel", "mt19937"],
+                   help="per-epoch reshuffle: device-side keyed bijection, or sklearn's MT19937 stream (parity runs)")
 
     t = sub.add_parser("tune", help="hidden sizes x learning rates (x max_iter) grid as packed federations (H:)")
     _common(t)
     t.add_argument("--clients", type=int, default=4)
     t.add_argument("--max-iter", type=int, nargs="+", default=[400])         # H:90
     t.add_argument("--small", action="store_true", help="3 x 3 corner of the grid (smoke runs)")
+    t.add_argument("--shuffle", default="feistel", choices=["feistel", "mt19937"],
+                   help="per-epoch reshuffle: device-side keyed bijection, or sklearn's MT19937 stream (parity runs)")
     return ap
 
 
@@ -135,6 +139,10 @@ def cmd_custom(args) -> int:
     return 0
 
 
+def _world():
+    return int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+
+
 def cmd_sklearn(args) -> int:
     from .data.partition import contiguous
     from .fed import logging as flog
@@ -144,17 +152,32 @@ def cmd_sklearn(args) -> int:
     data = _load(args, with_mean=False)                                      # S:184 StandardScaler(with_mean=False)
     shards = contiguous(len(data.X_train), args.clients)                     # S:17-22
     prob = FedProblem.sklearn_like(data.n_features, shards, hidden=tuple(args.hidden), lr=args.lr, max_iter=args.max_iter)
-    eng = FedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, device=args.device, max_rounds=args.rounds,
-                    seed=args.seed)
-    log = flog.RunLog(args.jsonl, quiet=args.quiet)
+    prob = prob.with_hyper(shuffle_stream=args.shuffle)
+    world, rank = _world()
+    if world > 1:
+        # client-parallel over the GPUs: every rank fits its own clients, the coefficient mean (S:108-122) and the pooled
+        # counts (S:126-134) cross NVLink inside the aggregation kernel
+        import torch
+        from .parallel.dist_engine import DistFedEngine, GlooFedEngine, init_distributed
+        on_gpu = torch.cuda.is_available() and args.device != "cpu"
+        init_distributed("nccl" if on_gpu else "gloo")
+        Engine = DistFedEngine if on_gpu else GlooFedEngine
+        # (a local fit runs for up to max_iter epochs before a rank reaches the aggregation: generous barrier timeout)
+        eng = Engine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world, max_rounds=args.rounds,
+                     seed=args.seed, timeout_s=60.0)
+    else:
+        eng = FedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, device=args.device, max_rounds=args.rounds,
+                        seed=args.seed)
+    log = flog.RunLog(args.jsonl if rank == 0 else None, quiet=args.quiet or rank != 0)
     t0 = time.perf_counter()
     h = run_sklearn_rounds(eng, args.rounds, args.policy, log)
     dt = time.perf_counter() - t0
     test = eng.evaluate_global("test")[0]
-    print(f"\n[fedb200] {args.rounds} rounds in {dt:.3f} s, policy={args.policy}; epochs per round and client:\n{h['n_iter']}\n"
-          f"held-out accuracy of the averaged model: {test['accuracy']:.4f}", flush=True)
-    if args.checkpoint:
-        eng.save_checkpoint(args.checkpoint)
+    if rank == 0:
+        print(f"\n[fedb200] {args.rounds} rounds in {dt:.3f} s, policy={args.policy}; epochs per round and client"
+              f"{' (this rank)' if world > 1 else ''}:\n{h['n_iter']}\nheld-out accuracy of the averaged model: {test['accuracy']:.4f}", flush=True)
+        if args.checkpoint:
+            eng.save_checkpoint(args.checkpoint)
     log.close()
     return 0
 
@@ -166,22 +189,32 @@ def cmd_tune(args) -> int:
     import torch
     data = _load(args, with_mean=False)                                      # H:164
     hg, lg = (HIDDEN_GRID[:3], LR_GRID[:3]) if args.small else (HIDDEN_GRID, LR_GRID)
-    log = flog.RunLog(args.jsonl, quiet=args.quiet)
-    if not args.quiet:
+    world, rank = _world()
+    if world > 1:
+        from .parallel.dist_engine import init_distributed
+        on_gpu = torch.cuda.is_available() and args.device != "cpu"
+        init_distributed("nccl" if on_gpu else "gloo")
+    log = flog.RunLog(args.jsonl if rank == 0 else None, quiet=args.quiet or rank != 0)
+    if not args.quiet and rank == 0:
         print(f"Training Round 1...\n{'-' * 50}")
     t0 = time.perf_counter()
-    out = run_grid(data, args.clients, hg, lg, tuple(args.max_iter), device=args.device, log=log, seed=args.seed)
+    out = run_grid(data, args.clients, hg, lg, tuple(args.max_iter), device=args.device, log=log, seed=args.seed, rank=rank, world=world,
+                   shuffle_stream=args.shuffle)
     dt = time.perf_counter() - t0
-    print(f"\n[fedb200] {len(out['results'])} federations in {dt:.2f} s; best {out['best_params']} -> {out['best_metrics']}", flush=True)
-    if len(args.max_iter) == 1:
-        np.set_printoptions(precision=3, suppress=True, linewidth=160)
-        print(accuracy_table(out["results"], hg, lg))
-    if args.checkpoint:
-        spec = out["best"]["spec"]
-        slab = torch.zeros(spec.slab_size)
-        spec.from_coefs_intercepts(*out["best"]["weights"], slab)
-        save_checkpoint(args.checkpoint, spec, slab, extras=out["best_params"] | {"metrics": out["best_metrics"]})
+    if rank == 0:
+        print(f"\n[fedb200] {len(out['results'])} federations in {dt:.2f} s on {world} GPU(s); best {out['best_params']} -> "
+              f"{out['best_metrics']}", flush=True)
+        if len(args.max_iter) == 1:
+            np.set_printoptions(precision=3, suppress=True, linewidth=160)
+            print(accuracy_table(out["results"], hg, lg))
+        if args.checkpoint:
+            spec = out["best"]["spec"]
+            slab = torch.zeros(spec.slab_size)
+            spec.from_coefs_intercepts(*out["best"]["weights"], slab)
+            save_checkpoint(args.checkpoint, spec, slab, extras=out["best_params"] | {"metrics": out["best_metrics"]})
     log.close()
+    if world > 1:
+        torch.distributed.barrier()
     return 0
 
 

@@ -149,7 +149,7 @@ class FedEngine:
                     r["agg_num"], r["agg_den"] = float(len(sh)), total
                 else:
                     r["agg_num"], r["agg_den"] = 1.0, float(p.n_clients if p.total_weight is None else p.total_weight)
-                r["scratch_off"], r["max_tiles"], r["client"] = scratch_off, max_tiles, k
+                r["scratch_off"], r["max_tiles"], r["client"] = scratch_off, max_tiles, k + p.client_offset   # GLOBAL client index
                 slab_off += P
                 idx_off += len(sh)
                 scratch_off += max_tiles * (P + nat.LOSS_SLOTS)
@@ -441,8 +441,36 @@ class FedEngine:
             self.no_improve.zero_()
             self.best_loss.fill_(float("inf"))
 
+    def _uses_shuffle_table(self) -> bool:
+        kinds = {p.hyper.shuffle_stream for p in self.problems}
+        if kinds - {"feistel", "mt19937"} or len(kinds) > 1:
+            raise ValueError(f"shuffle_stream must be 'feistel' or 'mt19937', the same for every federation of an engine: {kinds}")
+        return kinds == {"mt19937"}
+
+    def _shuffle_table(self) -> torch.Tensor:
+        """int32 [T, rows of all shards]: row e = the index array of epoch e (sklearn's MT19937 order, models/init.py)."""
+        if getattr(self, "_shuffle_tab", None) is None:
+            T = max(max(p.hyper.max_iter, 1) for p in self.problems)
+            tab = np.empty((T, self.test_idx_off), dtype=np.int32)
+            cache = {}
+            for f, p in enumerate(self.problems):
+                for k, gi in enumerate(self.group_of[f]):
+                    g = self.tb.groups[gi]
+                    n, off = int(g["n_rows"]), int(g["idx_off"])
+                    key = (p.spec.dims, p.init_seed, n, T)
+                    if key not in cache:
+                        cache[key] = minit.sklearn_shuffle_table(p.spec, p.init_seed, n, T)
+                    tab[:, off: off + n] = self.idx_host[off: off + n][cache[key]]
+            self._shuffle_tab = torch.from_numpy(tab).to(self.device)
+        return self._shuffle_tab
+
     def enqueue_epoch(self, shuffle: bool = True) -> None:
-        if shuffle:
+        if shuffle and self._uses_shuffle_table():
+            # every client still active is in the same epoch (they all started at 0); a few small torch ops, graph-capturable
+            tab = self._shuffle_table()
+            ep = self.epoch.max().clamp(max=tab.shape[0] - 1).to(torch.int64).view(1)
+            self.idx_epoch[: tab.shape[1]].copy_(tab.index_select(0, ep).view(-1))
+        elif shuffle:
             K.shuffle(self.tb, self.idx, self.idx_epoch, self.epoch, self.active, self.seed + 0x5EED)
         src = self.idx_epoch if shuffle else self.idx
         for b in range(self.n_batches):
@@ -457,7 +485,7 @@ class FedEngine:
         bit-identical, but measured on B200 the graph of per-step launches is faster (4-client sklearn script 0.53 s against
         0.59 s, 90-federation grid 4.0 s against 4.9 s): its reduction + optimizer step spreads over 88 CTAs instead of the
         client's 7, and short graph nodes cost less than the three cluster barriers per mini-batch."""
-        if self.device.type != "cuda" or self.tb.smem_bytes <= 0:
+        if self.device.type != "cuda" or self.tb.smem_bytes <= 0 or self._uses_shuffle_table():
             return False
         return os.environ.get("FEDB200_FIT", "launches") == "cluster"
 

@@ -38,6 +38,10 @@ class TrainHyper:
     max_iter: int = 0
     tol: float = 1e-4
     n_iter_no_change: int = 10
+    # per-epoch reshuffle of the shard (SK:704-718): 'feistel' = a keyed bijection evaluated on the device (default);
+    # 'mt19937' = sklearn's own stream for random_state = the federation's init_seed, from a host-generated table
+    # (parity runs against the reference: same mini-batches, epoch for epoch)
+    shuffle_stream: str = "feistel"
 
 
 @dataclass

@@ -38,17 +38,23 @@ def run_sklearn_rounds(engine: FedEngine, rounds: int = 5, policy: str = "warm_s
         if policy == "reference_faithful" or r == 0:
             engine.init_params()
         engine.reset_fit_state(keep_no_improvement=(policy == "sklearn_literal" and r > 0))
-        engine.enqueue_round_begin()
+        if engine._begin_is_fused():
+            engine.prime()                      # multi-GPU: the aggregation kernel begins the next round itself
+        else:
+            engine.enqueue_round_begin()
         n_iter = engine.fit_local(shuffle=shuffle)
         engine.enqueue_eval_local()
         engine.enqueue_aggregate()
         n_iter_hist.append(n_iter)
         if log is not None:
             h = engine.history()
-            for f in range(engine.n_feds):
-                gs = engine.group_of[f]
-                log.lines(flog.sklearn_round_lines(r + 1, h["local"][r][gs], h["global"][f, r]))
+            g0 = 0
+            for f in range(engine.n_feds):          # history rows hold ALL clients of the federation, also under torchrun
+                nk = len(getattr(engine, "global_problems", engine.problems)[f].shards)
+                log.lines(flog.sklearn_round_lines(r + 1, h["local"][r][g0: g0 + nk], h["global"][f, r]))
+                g0 += nk
             log.record(round=r + 1, global_metrics=h["global"][:, r], local_metrics=h["local"][r], n_iter=n_iter)
+    engine.check_errors()
     h = engine.history()
     h["n_iter"] = np.asarray(n_iter_hist)
     if log is not None:

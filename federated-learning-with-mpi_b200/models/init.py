@@ -102,3 +102,24 @@ def init_slab(spec: MLPSpec, kind: str, seed: int, stream: int = 0) -> np.ndarra
     if kind == "sklearn_exact":
         return init_slab_sklearn_exact(spec, seed)
     return init_slab_philox(spec, kind, seed, stream)
+
+
+def sklearn_shuffle_table(spec: MLPSpec, seed: int, n_rows: int, n_epochs: int) -> np.ndarray:
+    """int32[n_epochs, n_rows]: the order in which ``MLPClassifier(random_state=seed, shuffle=True).fit`` visits its
+    ``n_rows`` samples in each epoch, draw for draw: the model's MT19937 stream first serves the Glorot initialisation
+    (as in :func:`init_slab_sklearn_exact`), then every epoch applies ``sklearn.utils.shuffle`` to the index vector left
+    by the previous one (SK:704-718: ``sample_idx = shuffle(sample_idx, random_state=self._random_state)``, which is
+    ``sample_idx[perm]`` with ``perm`` = an in-place ``RandomState.shuffle`` of ``arange(n)``)."""
+    rs = np.random.RandomState(seed)
+    for l in range(spec.n_layers):
+        s_ = layer_bound(spec, l, "sklearn_exact")
+        rs.uniform(-s_, s_, (spec.dims[l], spec.dims[l + 1]))
+        rs.uniform(-s_, s_, spec.dims[l + 1])
+    cur = np.arange(n_rows)
+    out = np.empty((n_epochs, n_rows), dtype=np.int32)
+    for ep in range(n_epochs):
+        perm = np.arange(n_rows)
+        rs.shuffle(perm)
+        cur = cur[perm]
+        out[ep] = cur
+    return out

@@ -151,7 +151,7 @@ def shuffle(groups, idx_in, idx_out, epoch, active, seed):
         if act is not None and not act[gi]:
             continue
         n, off = int(g["n_rows"]), int(g["idx_off"])
-        ka = (s0 ^ ((gi * 0x9E3779B1) & 0xFFFFFFFF)) & 0xFFFFFFFF
+        ka = (s0 ^ ((int(g["client"]) * 0x9E3779B1) & 0xFFFFFFFF)) & 0xFFFFFFFF   # by client index: independent of the packing
         kb = (s1 + int(ep[gi])) & 0xFFFFFFFF
         i_out[off: off + n] = i_in[off: off + n][_feistel_perm(n, ka, kb)]
 

@@ -58,3 +58,48 @@ def test_client_placement_and_symmetric_layout():
     assert lay.conf_off >= 2 * lay.global_total * 4
     assert lay.flag_off >= lay.conf_off + 2 * 8 * lay.conf_slots * C2 * 4
     assert lay.nbytes >= lay.flag_off + 24 * 8          # flag words A, B (fused tail) and C (NVLS), one per source rank
+
+
+def test_grid_placement_is_balanced_and_complete():
+    """Longest-processing-time placement of the 90 grid federations over the ranks (fed/tune.py)."""
+    from fedb200.fed.tune import place_federations
+    costs = [float(c) for c in ([700] * 9 + [1500] * 9 + [3300] * 9 + [6500] * 9 + [6600] * 9 + [11600] * 9 + [21500] * 9 +
+                                 [42000] * 9 + [86400] * 9 + [84000] * 9)]
+    for world in (1, 2, 4, 8):
+        parts = place_federations(costs, world)
+        assert sorted(i for p in parts for i in p) == list(range(90))
+        loads = [sum(costs[i] for i in p) for p in parts]
+        assert max(loads) <= 1.25 * (sum(costs) / world) + max(costs) * (world > 4)
+
+
+def test_two_rank_tune_returns_the_single_process_table(tmp_path):
+    """`tune` under torchrun (federation-parallel, H:83-106 over all ranks): same table, same winner, bit for bit."""
+    from fedb200.cli import main as cli_main
+    single, multi = str(tmp_path / "s.jsonl"), str(tmp_path / "m.jsonl")
+    common = ["tune", "--clients", "2", "--max-iter", "3", "--small", "--device", "cpu", "--quiet", "--synthetic-rows", "400"]
+    assert cli_main(common + ["--jsonl", single]) == 0
+    out = _torchrun(2, 29633, ["-m", "fedb200"] + common + ["--jsonl", multi])
+    assert out.returncode == 0, out.stderr[-2000:]
+    a = [json.loads(l) for l in open(single)]
+    b = [json.loads(l) for l in open(multi)]
+    assert len(a) == len(b) == 9
+    for ra, rb in zip(a, b):
+        assert ra["hidden"] == rb["hidden"] and ra["lr"] == rb["lr"]
+        assert ra["global_metrics"] == rb["global_metrics"] and ra["n_iter"] == rb["n_iter"]
+
+
+def test_two_rank_sklearn_avg_matches_single_process(tmp_path):
+    """`sklearn-avg` under torchrun (client-parallel: coefficient mean S:108-122 and pooled counts S:126-134 across ranks)."""
+    from fedb200.cli import main as cli_main
+    single, multi = str(tmp_path / "s.jsonl"), str(tmp_path / "m.jsonl")
+    common = ["sklearn-avg", "--clients", "4", "--rounds", "2", "--max-iter", "3", "--hidden", "8", "6", "--device", "cpu", "--quiet",
+              "--synthetic-rows", "800"]
+    assert cli_main(common + ["--jsonl", single]) == 0
+    out = _torchrun(2, 29634, ["-m", "fedb200"] + common + ["--jsonl", multi])
+    assert out.returncode == 0, out.stderr[-2000:]
+    a = [json.loads(l) for l in open(single)]
+    b = [json.loads(l) for l in open(multi)]
+    assert len(a) == len(b) == 2
+    for ra, rb in zip(a, b):
+        np.testing.assert_allclose(ra["global_metrics"], rb["global_metrics"], atol=1e-6)
+        np.testing.assert_allclose(ra["local_metrics"], rb["local_metrics"], atol=1e-6)

@@ -150,3 +150,38 @@ def test_shuffle_is_a_permutation_and_epoch_dependent():
     p1 = ref._feistel_perm(2000, 1, 1)
     assert sorted(p0.tolist()) == list(range(2000)) and sorted(p1.tolist()) == list(range(2000))
     assert (p0 != p1).mean() > 0.9
+
+
+def test_sklearn_mode_with_mt19937_stream_follows_sklearn_epoch_for_epoch(income_nomean):
+    """Parity mode (TrainHyper.shuffle_stream='mt19937'): same init draws, same mini-batches, same Adam / L2 / loss as
+    ``MLPClassifier(random_state=42)`` — the per-epoch training loss of the first ten epochs equals sklearn's float64 loss
+    curve to 1e-6 on the reference's rank-0 shard (S:17-22, S:77-83).  (Beyond a few dozen epochs float32 and float64
+    trajectories drift apart — sklearn itself stops after 259 epochs on float64 inputs and after 156 on the same data cast
+    to float32 — so whole-run numbers are compared with a tolerance, tests/test_modes.py.)"""
+    import warnings
+    from sklearn.neural_network import MLPClassifier
+    from fedb200 import FedEngine, FedProblem
+    from fedb200.data.partition import contiguous
+    d = income_nomean
+    sh = contiguous(len(d.X_train), 4)[0]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        sk = MLPClassifier(activation="relu", hidden_layer_sizes=(50, 400), learning_rate_init=0.004, max_iter=10, random_state=42)
+        sk.fit(d.X_train[sh], d.y_train[sh])
+    prob = FedProblem.sklearn_like(d.n_features, [sh]).with_hyper(shuffle_stream="mt19937")
+    eng = FedEngine([prob], d.X_train, d.y_train, device="cpu", max_rounds=2)
+    eng.reset_fit_state()
+    eng.enqueue_round_begin()
+    ours = []
+    for _ in range(10):
+        eng.enqueue_epoch(True)
+        ours.append(float(eng.last_loss[0]))
+    np.testing.assert_allclose(ours, sk.loss_curve_, rtol=0, atol=1e-6)
+    # ... and the device-side default stream is a different permutation of the same shard
+    prob_f = FedProblem.sklearn_like(d.n_features, [sh])
+    eng_f = FedEngine([prob_f], d.X_train, d.y_train, device="cpu", max_rounds=2)
+    eng_f.reset_fit_state()
+    eng_f.enqueue_round_begin()
+    eng_f.enqueue_epoch(True)
+    assert sorted(eng_f.idx_epoch[: len(sh)].tolist()) == sorted(sh.tolist())
+    assert abs(float(eng_f.last_loss[0]) - sk.loss_curve_[0]) > 1e-6
