@@ -679,7 +679,10 @@ class FedEngine:
         """One round the way a caller that streams data would run it: upload this step's
         inputs from (pinned) host memory, run the round, read the round's result (federation
         state: stop flag + the four global metrics) back to the host.  Returns ``FedbFedState``
-        records whose ``done``, ``stop`` and ``last`` fields are current (copy them if you keep them).  This mirrors what the reference does every round
+        records whose ``done``, ``stop`` and ``last`` fields are current; the record is an internal
+        buffer that the next call overwrites (copy what you keep), and on the polled path the round
+        kernel may still be retiring when this returns — its other fields (anchor, count, ...) are
+        valid only after a stream synchronisation.  This mirrors what the reference does every round
         (H2D of the shard C:65-66, D2H of the predictions C:83) minus the weight traffic.
         On CUDA the uploads, the round and the read-back are ONE graph launch (captured per
         pair of host buffers), followed by one stream synchronisation.  When the round is a single
@@ -700,10 +703,15 @@ class FedEngine:
                 return ent[2]
             # the round kernel stores four self-validating 16-byte chunks {done, stop, metric} into mapped pinned memory: poll
             # them instead of waiting for the whole kernel to retire, so the next launch overlaps this kernel's teardown
+            import time as _time
             want, spins, d = self._e2e_expect, 0, chunks["done"]
+            deadline = None
             while not (d[0] == want and d[1] == want and d[2] == want and d[3] == want):
                 spins += 1
-                if spins > 4000:                         # stopped federation (no new round) or an unusually slow step
+                if (spins & 255) == 0:                   # a time basis, not a spin count: 2 ms without a result -> synchronise
+                    now = _time.perf_counter()
+                    deadline = deadline or now + 2e-3
+                if deadline is not None and _time.perf_counter() > deadline:   # stopped federation (no new round) or a slow step
                     ent[1]()
                     self._e2e_expect = -1 if ent[2]["stop"][0] else int(ent[2]["done"][0]) + 1
                     return ent[2]

@@ -340,13 +340,13 @@ class GlooFedEngine(FedEngine):
                     self.hist_global.view(self.n_feds, self.max_rounds, 4)[f, r] = torch.from_numpy(gv).float()
                 st[f]["last"] = gv
                 if p.patience > 0:
-                    close = bool(st[f]["has_anchor"]) and bool(np.all(np.abs(gv - st[f]["anchor"]) <= p.atol + p.rtol * np.abs(st[f]["anchor"])))
-                    if close:
-                        st[f]["count"] -= 1
-                        if st[f]["count"] == 0:
-                            st[f]["stop_pending"] = 1
-                    else:
-                        st[f]["anchor"], st[f]["has_anchor"], st[f]["count"] = gv, 1, p.patience
+                    # the reference's rule (C:181-192) as restated once in fed/metrics.py, driven from the device-layout state
+                    from ..fed.metrics import METRIC_NAMES, EarlyStop
+                    es = EarlyStop(patience=p.patience, atol=p.atol, rtol=p.rtol, count=int(st[f]["count"]),
+                                   anchor=st[f]["anchor"].copy() if st[f]["has_anchor"] else None)
+                    if es.update(dict(zip(METRIC_NAMES, gv))):
+                        st[f]["stop_pending"] = 1
+                    st[f]["anchor"], st[f]["has_anchor"], st[f]["count"] = es.anchor, 1, es.count
                 st[f]["done"] = st[f]["round"]
             g_base += p.n_clients
 
