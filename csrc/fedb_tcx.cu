@@ -69,7 +69,7 @@ constexpr int SX_W3 = SX_W2L + 256 * 128;    // fp32 [256 units][8 classes]
 constexpr int SX_B3 = SX_W3 + 256 * 8 * 4;   // fp32 [8]
 constexpr int SX_END = SX_B3 + 256;
 constexpr int SX_SLOTS = SX_END;              // [CS senders][share] floats: the partials this CTA owns
-constexpr int SX_SLOTS_MAX = 227 * 1024 - 6144 - SX_SLOTS;   // (static shared memory of the kernel and its tails: < 5 KB, + 1 KB alignment)
+constexpr int SX_SLOTS_MAX = 227 * 1024 - 7168 - SX_SLOTS;   // (static shared memory of the kernel and its tails: < 6 KB, + 1 KB alignment)
 constexpr int SX_STAGE = SX_H1;               // outgoing partials [CS owners][share] (and the fp32 slab at launch) overlay H1..Z
 constexpr int SX_STAGE_MAX = 10 * XP;
 constexpr int DZ3_COL = 32;                   // first column of [dZ3 hi | dZ3 lo] inside the X panel
@@ -926,7 +926,7 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
       cluster_waited = true;
     }
     if (tid < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES && cnt[tid] != 0) {
-      if (a.tail_mode != 0 && gridDim.x == (unsigned)CS)   // single cluster: straight into the scoring CTA's shared memory
+      if ((a.tail_mode == 1 || a.tail_mode == 2) && gridDim.x == (unsigned)CS)   // single cluster: straight into the scoring CTA's shared memory
         asm volatile("red.relaxed.cluster.shared::cluster.add.u32 [%0], %1;" ::"r"(mapa(tc::smem_u32(&pre->cnt[tid]), CS - 1)), "r"((uint32_t)cnt[tid]) : "memory");
       else
         atomicAdd(a.conf + (size_t)g * FEDB_MAX_CLASSES * FEDB_MAX_CLASSES + tid, cnt[tid]);
@@ -954,14 +954,33 @@ __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
     cg::cluster_group cl = cg::this_cluster();
     const bool single = gridDim.x == cl.num_blocks();
     if (threadIdx.x < FEDB_MAX_CLASSES * FEDB_MAX_CLASSES) pre.cnt[threadIdx.x] = 0;
-    if (threadIdx.x == 0) { pre.have_fs = 0; pre.have_cnt = (a.tail_mode != 0 && single) ? 1 : 0; }
+    if (threadIdx.x == 0) { pre.have_fs = 0; pre.have_cnt = ((a.tail_mode == 1 || a.tail_mode == 2) && single) ? 1 : 0; }
     __syncthreads();
     // the scoring CTA's last warp (idle in every epilogue) fetches the federation record / state while the round runs
-    if (a.tail_mode != 0 && cl.block_rank() == cl.num_blocks() - 1 && (threadIdx.x >> 5) == XT / 32 - 1) tail_prefetch(a, &pre);
+    if ((a.tail_mode == 1 || a.tail_mode == 2) && cl.block_rank() == cl.num_blocks() - 1 && (threadIdx.x >> 5) == XT / 32 - 1) tail_prefetch(a, &pre);
   }
   const bool avg_done = round_body_x(a, smem_raw, &pre);
   if (a.tail_mode == 0) return;
   if (a.tail_mode == 2) { p2p_tail(a, &pre); return; }
+  if (a.tail_mode == 3) {   // many resident clients, cross-GPU: the rank's last cluster to finish runs the exchange
+    __shared__ unsigned int s_last3;
+    cg::cluster_group cl = cg::this_cluster();
+    const int CSz = (int)cl.num_blocks();
+    __threadfence();
+    cl.sync();
+    const unsigned int n_cl = gridDim.x / CSz;
+    if (n_cl > 1) {
+      if (cl.block_rank() == 0 && threadIdx.x == 0) {
+        const unsigned int last = (atomicInc(a.tail_count, n_cl - 1) == n_cl - 1) ? 1u : 0u;
+        for (int r = 0; r < CSz; ++r) *cl.map_shared_rank(&s_last3, r) = last;
+      }
+      cl.sync();
+      if (!s_last3) return;
+      __threadfence();
+    }
+    p2p_tail_many(a, &pre);
+    return;
+  }
   // the cluster that observes the last check-in runs the single-GPU aggregation tail (see k_local_round_tc)
   __shared__ unsigned int s_last;
   __shared__ unsigned char s_stop[TAIL_MAX_FEDS];
@@ -1102,4 +1121,22 @@ extern "C" int fedb_round_tcx_p2p(const FedbGroup* groups, int32_t cluster_size,
   a.n_steps = n_steps; a.do_eval = 1; a.prof = nullptr; a.tail_mode = 2; a.n_groups = 1; a.n_feds = 1; a.p2p = rank_dev;
   a.state_mirror = state_mirror;
   return launch_tcx(a, 1, cluster_size, stream);
+}
+
+// Multi-GPU round with ANY number of resident clients per rank in one launch per rank (p2p_tail_many): groups / n_groups are
+// this rank's resident clients, tail_count one zeroed uint32; everything else as fedb_round_tcx_p2p.
+extern "C" int fedb_round_tcx_p2p_many(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                                       const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m,
+                                       float* v, int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out,
+                                       int32_t* conf, float* scratch, int32_t n_steps, const FedbP2PRank* rank_dev,
+                                       uint32_t* tail_count, FedbFedState* state_mirror, void* stream) {
+  FEDB_REQUIRE(rank_dev != nullptr && tail_count != nullptr && n_groups > 0, "rank record and tail counter required");
+  FEDB_REQUIRE((x_host == nullptr) == (y_host == nullptr), "x_host and y_host come together");
+  TcArgs a{};
+  a.x_host = x_host; a.y_host = y_host;
+  a.groups = groups; a.X = X; a.y = y; a.idx = idx; a.params = params; a.m = m; a.v = v; a.step = step; a.active = active;
+  a.fed_state = fed_state; a.loss_out = loss_out; a.conf = conf; a.scratch = scratch; a.ldx = ldx; a.batch = 0;
+  a.n_steps = n_steps; a.do_eval = 1; a.prof = nullptr; a.tail_mode = 3; a.n_groups = n_groups; a.n_feds = 1; a.p2p = rank_dev;
+  a.tail_count = tail_count; a.state_mirror = state_mirror;
+  return launch_tcx(a, n_groups, cluster_size, stream);
 }

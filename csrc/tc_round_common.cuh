@@ -272,4 +272,120 @@ static __device__ void p2p_tail(const TcArgs& a, TailPre* pre = nullptr) {
   if (s_timeout && tid == 0) *R.err = FEDB_E_TIMEOUT;
 }
 
+// The same cross-GPU round for ANY number of resident clients per rank (tail_mode 3), executed by the last cluster of the
+// rank to finish: it first folds the resident clients' weighted slabs into this rank's partial, sum_k (w_k n_k) / N in
+// client order (C:110-115) — what k_fedavg_p2p's first phase does — publishes it (flag A; nothing is left to hide that
+// flight behind), pushes the tagged confusion counts of all resident clients, then sums the ranks' partials in rank order
+// over NVLink peer loads, writes the global model and every resident client's slab, and scores the round.  One launch per
+// rank per round; bit-identical to the local-round + k_fedavg_p2p pair.
+static __device__ void p2p_tail_many(const TcArgs& a, TailPre* pre = nullptr) {
+  cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+  const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank(), tid = threadIdx.x, NT = (int)blockDim.x;
+  __shared__ FedbP2PRank R;
+  for (int i = tid; i < (int)(sizeof(FedbP2PRank) / 4); i += NT)
+    reinterpret_cast<int32_t*>(&R)[i] = reinterpret_cast<const int32_t*>(a.p2p)[i];
+  __shared__ int s_timeout;
+  __shared__ unsigned char m_stop[TAIL_MAX_FEDS];
+  if (tid == 0) s_timeout = 0;
+  __syncthreads();
+  const uint64_t seq = *reinterpret_cast<volatile uint64_t*>(R.seq);
+  const int par = (int)(seq & 1);
+  const uint32_t tag = (uint32_t)((seq + 1) & 0xFF) << 24;
+  for (int f = tid; f < R.n_feds; f += NT) m_stop[f] = R.fed_state[f].stop ? 1 : 0;   // as it stands for THIS round
+  __syncthreads();
+  constexpr int C2 = FEDB_MAX_CLASSES * FEDB_MAX_CLASSES;
+  const int64_t conf_stride = (int64_t)R.conf_slots * C2;
+  const int nthr = CS * NT, gt = crank * NT + tid;
+  float* my_partial = reinterpret_cast<float*>(R.sym[R.rank] + R.sym_partial_off) + (int64_t)par * R.global_total;
+  // ---- 1. this rank's partial: the resident clients' terms in client order
+  for (int f = 0; f < R.n_feds; ++f) {
+    if (m_stop[f]) continue;
+    const FedbFed F = R.feds[f];
+    const int n4 = F.slab_size >> 2;
+    for (int e4 = gt; e4 < n4; e4 += nthr) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < F.n_clients; ++k) {
+        const FedbGroup* G = R.groups + F.first_group + k;
+        const float num = G->agg_num, den = G->agg_den;
+        const float4 w = __ldcg(reinterpret_cast<const float4*>(R.params + G->slab_off) + e4);
+        acc.x += __fdiv_rn(__fmul_rn(w.x, num), den); acc.y += __fdiv_rn(__fmul_rn(w.y, num), den);
+        acc.z += __fdiv_rn(__fmul_rn(w.z, num), den); acc.w += __fdiv_rn(__fmul_rn(w.w, num), den);
+      }
+      reinterpret_cast<float4*>(my_partial + F.global_off)[e4] = acc;
+    }
+  }
+  __threadfence();
+  cluster.sync();
+  const long long t0 = clock64();
+  uint64_t* my_flags = reinterpret_cast<uint64_t*>(R.sym[R.rank] + R.sym_flag_off);
+  if (crank == 0 && tid < R.world) {      // flag A: the cluster barrier ordered every CTA's partial stores before this thread
+    __threadfence_system();
+    st_release_sys_u64(reinterpret_cast<uint64_t*>(R.sym[tid] + R.sym_flag_off) + R.rank, seq + 1);
+  }
+  const int mrank = CS - 1, workers = CS > 1 ? CS - 1 : 1;
+  if (crank == mrank) {   // ---- 2. tagged confusion counts of every resident client into every peer's area
+    const int nconf = R.n_groups_local * C2;
+    for (int i = tid; i < nconf * R.world; i += NT) {
+      const int qq = i / nconf, w = i - qq * nconf;
+      st_relaxed_sys_u32(reinterpret_cast<uint32_t*>(R.sym[qq] + R.sym_conf_off) + (par * 8 + R.rank) * conf_stride + w,
+                         ((uint32_t)__ldcg(a.conf + w) & 0xFFFFFFu) | tag);
+    }
+  }
+  if (CS == 1 || crank != mrank) {   // ---- 3. sum the ranks' partials in rank order; global model + write-back
+    if (tid < R.world)
+      while (ld_acquire_sys_u64(my_flags + tid) < seq + 1)
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+    __syncthreads();
+    const int wt = (CS == 1 ? 0 : crank) * NT + tid, wn = workers * NT;
+    for (int f = 0; f < R.n_feds; ++f) {
+      if (m_stop[f]) continue;
+      const FedbFed F = R.feds[f];
+      float4* glob = reinterpret_cast<float4*>(R.global + F.global_off);
+      const int n4 = F.slab_size >> 2;
+      for (int e4 = wt; e4 < n4; e4 += wn) {
+        float4 pr[8];
+#pragma unroll
+        for (int qq = 0; qq < 8; ++qq)
+          if (qq < R.world)
+            pr[qq] = ld_relaxed_sys_f4(reinterpret_cast<const float*>(R.sym[qq] + R.sym_partial_off) + (int64_t)par * R.global_total + F.global_off + 4 * e4);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int qq = 0; qq < 8; ++qq)
+          if (qq < R.world) { acc.x += pr[qq].x; acc.y += pr[qq].y; acc.z += pr[qq].z; acc.w += pr[qq].w; }
+        glob[e4] = acc;
+        if (R.write_back)
+          for (int k = 0; k < F.n_clients; ++k) reinterpret_cast<float4*>(R.params + R.groups[F.first_group + k].slab_off)[e4] = acc;
+      }
+    }
+  }
+  if (crank == mrank) {              // ---- 4. metrics from every rank's counts, early stop, next round's begin
+    __shared__ int pool[C2];
+    int* conf_all = (pre && R.n_groups_total <= 8) ? pre->conf_all : R.conf_all;
+    for (int i = tid; i < R.n_groups_total * C2; i += NT) {
+      const int slot = i / C2, w = i - slot * C2;
+      const int qq = R.conf_src_rank[slot], ls = R.conf_src_slot[slot];
+      const int32_t* cq = reinterpret_cast<const int32_t*>(R.sym[R.rank] + R.sym_conf_off) + (par * 8 + qq) * conf_stride + ls * C2 + w;
+      uint32_t v = (uint32_t)ld_relaxed_sys_i32(cq);
+      while ((v & 0xFF000000u) != tag) {
+        if (clock64() - t0 > R.timeout_cycles) { s_timeout = 1; break; }
+        v = (uint32_t)ld_relaxed_sys_i32(cq);
+      }
+      conf_all[i] = (int32_t)(v & 0xFFFFFFu);
+    }
+    __syncthreads();
+    if (tid < 32 && R.do_metrics)
+      for (int f = 0; f < R.n_feds; ++f) {
+        if (m_stop[f]) continue;
+        round_metrics_ni(R.feds_global + f, R.fed_state + f, f, R.n_groups_total, conf_all, R.hist_local, R.hist_global, pool,
+                         a.state_mirror ? a.state_mirror + f : nullptr,
+                         a.state_mirror ? reinterpret_cast<char*>(a.state_mirror) + ((sizeof(FedbFedState) * R.n_feds + 15) & ~size_t(15)) + 64 * f : nullptr);
+      }
+    __syncthreads();
+    for (int i = tid; i < R.n_groups_local * C2; i += NT) a.conf[i] = 0;
+    if (tid == 0) *reinterpret_cast<volatile uint64_t*>(R.seq) = seq + 1;
+  }
+  __syncthreads();
+  if (s_timeout && tid == 0) *R.err = FEDB_E_TIMEOUT;
+}
+
 }  // namespace fedb

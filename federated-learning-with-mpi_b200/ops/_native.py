@@ -244,6 +244,7 @@ OPTIONAL_SIGS = {
     "fedb_local_round_tcx": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P], _I32),
     "fedb_round_tcx": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _P, _P, _P, _I32, _P, _P, _P, _P], _I32),
     "fedb_round_tcx_p2p": ([_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P], _I32),
+    "fedb_round_tcx_p2p_many": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P, _P], _I32),
     "fedb_noalloc_scratch_floats": ([], _I64),
     "fedb_wide_gather_x": ([_P, _I32, _P, _I32, _P, _P, _I32, _I32, _P], _I32),
     "fedb_wide_shadow": ([_P, _P, _I64, _P], _I32),

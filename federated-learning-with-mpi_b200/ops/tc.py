@@ -163,3 +163,16 @@ def round_tc_p2p(tb, cluster_size: int, X, y, idx, params, m, v, step, active, f
                                     nat.cuda_stream()))
     from . import kernels as K
     K._count()
+
+
+def round_tcx_p2p_many(tb, cluster_size: int, X, y, idx, params, m, v, step, active, fed_state, loss_out, conf, scratch, n_steps: int,
+                       rank_dev, tail_count, state_mirror=None, host_inputs=None) -> None:
+    """Multi-GPU round in one launch per rank with any number of resident clients (fedb_round_tcx_p2p_many)."""
+    lib = nat.lib(required=True)
+    xh, yh = host_inputs if host_inputs is not None else (None, None)
+    nat.check(lib.fedb_round_tcx_p2p_many(nat.ptr(tb.d_groups), tb.n_groups, cluster_size, nat.ptr(X), X.shape[1], nat.ptr(y), nat.ptr(xh),
+                                          nat.ptr(yh), nat.ptr(idx), nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(step), nat.ptr(active),
+                                          nat.ptr(fed_state), nat.ptr(loss_out), nat.ptr(conf), nat.ptr(scratch), n_steps, nat.ptr(rank_dev),
+                                          nat.ptr(tail_count), nat.ptr(state_mirror), nat.cuda_stream()))
+    from . import kernels as K
+    K._count()

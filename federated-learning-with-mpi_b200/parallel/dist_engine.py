@@ -147,10 +147,13 @@ class DistFedEngine(FedEngine):
         return True   # k_fedavg_p2p ends with the next round's begin bookkeeping
 
     def _fused_p2p_ok(self) -> bool:
-        """One federation with exactly one resident client on the tensor-core path: the whole multi-GPU
-        round is ONE launch per rank (aggregation inside the round kernel, fedb_round_tc_p2p)."""
-        return (self.tc_variant is not None and self.n_feds == 1 and self.n_groups == 1 and self.world <= 8
-                and os.environ.get("FEDB200_NO_FUSED_P2P") is None and getattr(self, "_nvls", None) is None)
+        """One federation on the tensor-core path: the whole multi-GPU round is ONE launch per rank — aggregation inside the
+        round kernel (fedb_round_tc[x]_p2p for one resident client per rank, the reference's own topology C:36;
+        fedb_round_tcx_p2p_many for several, split-operand kernel only)."""
+        if not (self.tc_variant is not None and self.n_feds == 1 and self.world <= 8
+                and os.environ.get("FEDB200_NO_FUSED_P2P") is None and getattr(self, "_nvls", None) is None):
+            return False
+        return self.n_groups == 1 or (self.tc_variant == "x2" and self.params_total <= self.FUSED_TAIL_MAX_FLOATS)
 
     def _result_is_mirrored(self) -> bool:
         return self._fused_p2p_ok()
@@ -162,6 +165,11 @@ class DistFedEngine(FedEngine):
         if self._fused_p2p_ok():
             from ..ops import tc
             E = max(p.hyper.local_epochs for p in self.problems)
+            if self.n_groups > 1:
+                tc.round_tcx_p2p_many(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step,
+                                      self.active, self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, self.tail_count,
+                                      state_mirror=self._state_pinned, host_inputs=host_inputs)
+                return
             tc.round_tc_p2p(self.tb, self.tc_cluster, self.X, self.y, self.idx, self.params, self.m, self.v, self.step, self.active,
                             self.fed_state, self.loss, self.conf, self.scratch, E, self.rank_dev, state_mirror=self._state_pinned,
                             host_inputs=host_inputs, variant=self.tc_variant)

@@ -319,6 +319,15 @@ int fedb_round_tcx_p2p(const FedbGroup* groups, int32_t cluster_size, float* X, 
                        const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf, float* scratch,
                        int32_t n_steps, const FedbP2PRank* rank_dev, FedbFedState* state_mirror, void* stream);
 
+/* The multi-GPU round in one launch per rank for ANY number of resident clients: the rank's last cluster to finish folds its
+ * clients' weighted slabs into the rank partial (C:110-115), then runs the cross-GPU exchange, write-back, metrics and early
+ * stop; tail_count = one zeroed uint32.  Bit-identical to fedb_local_round_tcx + fedb_fedavg_p2p. */
+int fedb_round_tcx_p2p_many(const FedbGroup* groups, int32_t n_groups, int32_t cluster_size, float* X, int32_t ldx, int32_t* y,
+                            const float* x_host, const int32_t* y_host, const int32_t* idx, float* params, float* m, float* v,
+                            int32_t* step, const int32_t* active, FedbFedState* fed_state, float* loss_out, int32_t* conf,
+                            float* scratch, int32_t n_steps, const FedbP2PRank* rank_dev, uint32_t* tail_count,
+                            FedbFedState* state_mirror, void* stream);
+
 /* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
  * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
 int32_t fedb_gemm_args_size(void);

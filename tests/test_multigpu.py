@@ -56,6 +56,19 @@ def test_two_gpu_global_model_is_bitwise_the_single_gpu_one(tmp_path, precision)
     assert np.array_equal(sep["global_"], want) and np.array_equal(sep["hist"], h["global"])
 
 
+def test_two_gpu_many_clients_per_rank_in_one_launch(tmp_path):
+    """Six clients on two GPUs (three per rank): one launch per rank per round (the rank's last cluster folds its clients into
+    the rank partial and runs the cross-GPU exchange) — bit-identical to the local-round + stand-alone aggregation pair."""
+    import numpy as np
+    fused = _dist_run(tmp_path, "many_fused", 29553, 6, 700, 10, "tc32")
+    assert int(fused["launches"]) == 1 and "p2p-fedavg" in str(fused["kernels"][0])
+    sep = _dist_run(tmp_path, "many_sep", 29554, 6, 700, 10, "tc32", {"FEDB200_NO_FUSED_P2P": "1"})
+    assert int(sep["launches"]) > 1
+    assert np.array_equal(fused["global_"], sep["global_"]) and np.array_equal(fused["globals_all"][0], fused["globals_all"][1])
+    assert np.array_equal(fused["hist"], sep["hist"]) and np.array_equal(fused["local"], sep["local"])
+    assert fused["hist"][0, -1, 0] > 0.6
+
+
 def test_two_gpu_bench_fused_and_standalone_aggregation_agree():
     fused = _bench(29541)
     assert fused["n_gpus"] == 2 and fused["value"] > 0 and any("p2p-fedavg" in k for k in fused["kernels"])
