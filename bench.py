@@ -383,6 +383,12 @@ def run_ours_modes(args):
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         return float(t.item()), out
 
+    if args.config == "sklearn" and world > SK_CLIENTS:
+        if rank == 0:
+            print(json.dumps({"impl": "ours", "unavailable": f"config 2 has {SK_CLIENTS} clients: at most {SK_CLIENTS} GPUs (one client each)"}))
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+        return
     if args.config == "sklearn":
         prob = FedProblem.sklearn_like(data.n_features, contiguous(len(data.X_train), SK_CLIENTS))
         mk = (lambda: DistFedEngine([prob], data.X_train, data.y_train, data.X_test, data.y_test, rank=rank, world=world,
