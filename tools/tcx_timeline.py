@@ -1,6 +1,6 @@
 """Per-CTA phase timeline of k_round_tcx (globaltimer ns; every CTA of the first cluster stamps its thread 0).
 
-    python tools/tcx_timeline.py [rows_per_client] [clients]
+    python tools/tcx_timeline.py [rows_per_client] [clients] [cold]      ("cold": flush L2 with a 256 MiB memset before the launch)
 """
 import sys
 
@@ -25,8 +25,11 @@ if __name__ == "__main__":
     e = FedEngine([FedProblem.custom(14, 2, shards, patience=0)], d.X_train, d.y_train, device="cuda", max_rounds=64, precision="tc32")
     e.prime()
     prof = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if (len(sys.argv) > 3 and sys.argv[3] == "cold") else None
     for it in range(4):
         prof.zero_()
+        if flush is not None:
+            flush.zero_()
         tc.round_tc(e.tb, e.tc_cluster, e.X, e.y, e.idx, e.params, e.m, e.v, e.step, e.active, e.fed_state, e.loss, e.conf, e.scratch,
                     1, e.global_, e.hist_local, e.hist_global, e.tail_count, prof, variant="x2")
         torch.cuda.synchronize()
