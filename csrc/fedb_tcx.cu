@@ -234,24 +234,36 @@ __device__ __forceinline__ RowRegsX fetch_row_x(const TcArgs& a, int64_t pos, bo
 // neighbouring lanes (tools/host_pull_bench.cu: the request size is what matters over the host link), written through
 // to the device-resident X / y.  Threads 0..255 fetch (row t / 4, chunk t % 4) — which is exactly what row thread
 // (row, part) needs, so the hand-over goes through shared memory (the H1 panel, idle at that point).
-__device__ __forceinline__ RowRegsX host_rows_x(uint8_t* sm, const TcArgs& a, int64_t pos0, int nvalid, int tid, int row, int part, bool rowt) {
+struct HostRegsX {
+  float4 v;
+  int grow, label;
+};
+// part 1 (issued as early as possible: the loads cross the host link, ~2 us): threads 0..255 fetch (row t / 4, chunk t % 4)
+__device__ __forceinline__ HostRegsX host_fetch_x(const TcArgs& a, int64_t pos0, int nvalid, int tid) {
+  HostRegsX h;
+  h.v = make_float4(0.f, 0.f, 0.f, 0.f);
+  h.grow = -1;
+  h.label = 0;
+  const int rl = tid >> 2, c = tid & 3;
+  if (tid < 4 * XR && rl < nvalid) {
+    h.grow = __ldg(a.idx + pos0 + rl);
+    h.v = __ldcv(reinterpret_cast<const float4*>(a.x_host + (size_t)h.grow * a.ldx) + c);
+    if (c == 0) h.label = __ldcv(a.y_host + h.grow);
+  }
+  return h;
+}
+// part 2: write-through to X / y and hand-over to the row threads through shared memory
+__device__ __forceinline__ RowRegsX host_deliver_x(uint8_t* sm, const TcArgs& a, const HostRegsX& h, int tid, int row, int part, bool rowt) {
   float* stage = reinterpret_cast<float*>(sm + SX_H1);           // 64 rows x 16 floats, then 64 labels
   int* stage_lab = reinterpret_cast<int*>(sm + SX_H1 + XR * 64);
   if (tid < 4 * XR) {
     const int rl = tid >> 2, c = tid & 3;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    int label = 0;
-    if (rl < nvalid) {
-      const int grow = __ldg(a.idx + pos0 + rl);
-      v = __ldcv(reinterpret_cast<const float4*>(a.x_host + (size_t)grow * a.ldx) + c);
-      *(reinterpret_cast<float4*>(const_cast<float*>(a.X) + (size_t)grow * a.ldx) + c) = v;
-      if (c == 0) {
-        label = __ldcv(a.y_host + grow);
-        const_cast<int32_t*>(a.y)[grow] = label;
-      }
+    if (h.grow >= 0) {
+      *(reinterpret_cast<float4*>(const_cast<float*>(a.X) + (size_t)h.grow * a.ldx) + c) = h.v;
+      if (c == 0) const_cast<int32_t*>(a.y)[h.grow] = h.label;
     }
-    *reinterpret_cast<float4*>(stage + rl * 16 + 4 * c) = v;
-    if (c == 0) stage_lab[rl] = label;
+    *reinterpret_cast<float4*>(stage + rl * 16 + 4 * c) = h.v;
+    if (c == 0) stage_lab[rl] = h.label;
   }
   __syncthreads();
   RowRegsX r;
@@ -442,7 +454,10 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
   RowRegsX rr;
   rr.label = 0;
   rr.q = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (!a.x_host && rowt) rr = fetch_row_x(a, G.idx_off + b0 + q * XR + row, q < ntiles && q * XR + row < nb, part);
+  HostRegsX hr;
+  hr.v = make_float4(0.f, 0.f, 0.f, 0.f); hr.grow = -1; hr.label = 0;
+  if (a.x_host) hr = host_fetch_x(a, G.idx_off + b0 + q * XR, q < ntiles ? min(XR, nb - q * XR) : 0, tid);
+  else if (rowt) rr = fetch_row_x(a, G.idx_off + b0 + q * XR + row, q < ntiles && q * XR + row < nb, part);
   tc::mbar_wait(&wbar, wph); wph ^= 1;
   convert_weights_x(sm, landing, s);
   STAMP(1);
@@ -478,8 +493,12 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
       const bool acc = my_tiles > 0;
       const int r = tile * XR + row;
       const bool valid = rowt && r < nb;
-      if (a.x_host) rr = host_rows_x(sm, a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid, row, part, rowt);
-      else if (rowt && !first_fetch) rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+      if (a.x_host) {
+        if (!first_fetch) hr = host_fetch_x(a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid);
+        rr = host_deliver_x(sm, a, hr, tid, row, part, rowt);
+      } else if (rowt && !first_fetch) {
+        rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+      }
       first_fetch = false;
       const int label = rr.label;
       if (rowt) store_row_x(sm, rr, valid, s, row, part);
@@ -846,8 +865,12 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
       const int r = tile * XR + row;
       const bool valid = rowt && r < nb;
       if (!(ntiles <= CS && a.n_steps > 0)) {   // (single tile per CTA: the X panel from the training step is still in place)
-        if (a.x_host) rr = host_rows_x(sm, a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid, row, part, rowt);
-        else if (rowt && !first_fetch) rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+        if (a.x_host) {
+          if (!first_fetch) hr = host_fetch_x(a, G.idx_off + b0 + tile * XR, min(XR, nb - tile * XR), tid);
+          rr = host_deliver_x(sm, a, hr, tid, row, part, rowt);
+        } else if (rowt && !first_fetch) {
+          rr = fetch_row_x(a, G.idx_off + b0 + r, valid, part);
+        }
         first_fetch = false;
         if (rowt) store_row_x(sm, rr, valid, s, row, part);
       }
@@ -950,6 +973,9 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
 __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ TailPre pre;
+  __shared__ unsigned char s_stop[TAIL_MAX_FEDS];   // stop flags as they stand for THIS round (only a tail ever writes them)
+  if (a.tail_mode == 1)
+    for (int f = threadIdx.x; f < a.n_feds; f += XT) s_stop[f] = a.fed_state_rw[f].stop ? 1 : 0;
   {
     cg::cluster_group cl = cg::this_cluster();
     const bool single = gridDim.x == cl.num_blocks();
@@ -983,13 +1009,11 @@ __global__ void __launch_bounds__(XT, 1) k_round_tcx(TcArgs a) {
   }
   // the cluster that observes the last check-in runs the single-GPU aggregation tail (see k_local_round_tc)
   __shared__ unsigned int s_last;
-  __shared__ unsigned char s_stop[TAIL_MAX_FEDS];
   cg::cluster_group cluster = cg::this_cluster();
   const int CS = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
-  for (int f = threadIdx.x; f < a.n_feds; f += XT) s_stop[f] = a.fed_state_rw[f].stop ? 1 : 0;
-  __threadfence();
-  cluster.sync();
   const unsigned int n_clusters = gridDim.x / CS;
+  if (n_clusters > 1) __threadfence();   // (single cluster: nothing of this round went through global atomics; the barrier orders the rest)
+  cluster.sync();
   if (n_clusters > 1) {
     if (crank == 0 && threadIdx.x == 0) {
       const unsigned int last = (atomicInc(a.tail_count, n_clusters - 1) == n_clusters - 1) ? 1u : 0u;
