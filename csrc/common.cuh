@@ -90,6 +90,24 @@ __host__ __device__ inline void philox4x32(uint32_t c[4], uint32_t k0, uint32_t 
   }
 }
 
+// keyed Feistel bijection on [0, n) by cycle walking: the per-epoch reshuffle of a shard (k_shuffle and the persistent fit kernels)
+__device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n, int half_bits, uint32_t ka, uint32_t kb) {
+  const uint32_t mask = (1u << half_bits) - 1u;
+  uint32_t x = i;
+  do {
+    uint32_t l = x >> half_bits, r = x & mask;
+#pragma unroll
+    for (int round = 0; round < 4; ++round) {
+      uint32_t c[4] = {r, (uint32_t)round, ka, kb};
+      philox4x32(c, 0xA511E9B3u, 0x5851F42Du);
+      const uint32_t nl = r, nr = l ^ (c[0] & mask);
+      l = nl; r = nr;
+    }
+    x = (l << half_bits) | r;
+  } while (x >= n);
+  return x;
+}
+
 __device__ __forceinline__ float act_fwd(float z, int act) {
   switch (act) {
     case FEDB_ACT_RELU: return fmaxf(z, 0.f);

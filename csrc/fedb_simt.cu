@@ -276,23 +276,6 @@ __global__ void k_round_begin(const FedbFed* __restrict__ feds, FedbFedState* __
 // ---------------------------------------------------------------------------------------
 // shuffle: keyed Feistel bijection on [0, n) by cycle walking
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n, int half_bits, uint32_t ka, uint32_t kb) {
-  const uint32_t mask = (1u << half_bits) - 1u;
-  uint32_t x = i;
-  do {
-    uint32_t l = x >> half_bits, r = x & mask;
-#pragma unroll
-    for (int round = 0; round < 4; ++round) {
-      uint32_t c[4] = {r, (uint32_t)round, ka, kb};
-      philox4x32(c, 0xA511E9B3u, 0x5851F42Du);
-      const uint32_t nl = r, nr = l ^ (c[0] & mask);
-      l = nl; r = nr;
-    }
-    x = (l << half_bits) | r;
-  } while (x >= n);
-  return x;
-}
-
 __global__ void k_shuffle(const FedbGroup* __restrict__ groups, const int32_t* __restrict__ idx_in,
                           int32_t* __restrict__ idx_out, const int32_t* __restrict__ epoch,
                           const int32_t* __restrict__ active, uint32_t s0, uint32_t s1) {

@@ -479,6 +479,15 @@ class FedEngine:
         K.epoch_end(self.tb, self.batch_stats, self.n_batches, h.tol, h.n_iter_no_change, h.max_iter, self.active,
                     self.epoch, self.no_improve, self.best_loss, self.last_loss)
 
+    def _fit_tc_mask(self) -> Optional[np.ndarray]:
+        """bool per client: trained by the tensor-core fit kernel.  None: not on this engine (CPU, MT19937 parity stream,
+        FEDB200_FIT=launches | cluster forces the CUDA-core paths)."""
+        if self.device.type != "cuda" or self._uses_shuffle_table() or os.environ.get("FEDB200_FIT") in ("launches", "cluster"):
+            return None
+        if getattr(self, "_tc_fit_mask", None) is None:
+            self._tc_fit_mask = K.fitx_eligible(self.tb.groups)
+        return self._tc_fit_mask
+
     def _fit_in_one_launch(self) -> bool:
         """Whether :meth:`fit_local` runs as one persistent launch (fedb_fit_cluster: a cluster per client loops over epochs and
         mini-batches on the device) instead of one graph replay per epoch.  Opt-in with FEDB200_FIT=cluster: the results are
@@ -493,6 +502,19 @@ class FedEngine:
         """Train every client until its loss stalls (SK:750-777) or ``max_iter`` epochs.
         Returns the number of epochs each client ran (sklearn's ``n_iter_``)."""
         max_iter = max_iter or max(p.hyper.max_iter for p in self.problems)
+        tc_mask = self._fit_tc_mask()
+        if tc_mask is not None and bool(tc_mask.any()):
+            # K2b on the tensor cores (csrc/fedb_fitx.cu): the whole fit of every eligible client in ONE launch, epoch loop and
+            # stopping rule on the device; clients of other shapes follow on the CUDA-core kernels below
+            h = self.problems[0].hyper
+            act_tc = torch.from_numpy(tc_mask.astype(np.int32)).to(self.device)
+            K.fit_tcx(self.tb, self.params, self.m, self.v, self.X, self.y, self.idx, self.idx_epoch, self.step, act_tc, self.fed_state,
+                      self.epoch, self.no_improve, self.best_loss, self.last_loss, self.loss, h.tol, h.n_iter_no_change, h.max_iter,
+                      max_iter, shuffle, self.seed + 0x5EED)
+            if bool(tc_mask.all()):
+                self.active.fill_(1)
+                return self.epoch.cpu().numpy().copy()
+            self.active.copy_(1 - act_tc)
         if self._fit_in_one_launch():
             # K2b, persistent form: epochs, mini-batches and the stopping rule all run on the device (fedb_fit_cluster)
             h = self.problems[0].hyper

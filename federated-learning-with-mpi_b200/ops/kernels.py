@@ -201,3 +201,26 @@ def fedavg(tb: DeviceTables, fed_state, params, global_, conf, hist_local, hist_
     else:
         ref.fedavg(tb.groups, tb.feds, fed_state, tb.max_slab, params, global_, conf, hist_local, hist_global,
                    write_back, do_metrics, begin_next)
+
+
+def fitx_eligible(groups: np.ndarray) -> np.ndarray:
+    """bool[n_groups]: which clients the tensor-core fit kernel (csrc/fedb_fitx.cu) can train: 2 hidden ReLU layers,
+    in <= 15, h1 <= 63, h2 <= 512, out <= 8."""
+    lib = nat.lib(required=True)
+    out = np.zeros(len(groups), dtype=bool)
+    for i, g in enumerate(groups):
+        d = g["dims"]
+        out[i] = (int(g["n_layers"]) == 3 and int(g["act"]) == nat.ACT_IDS["relu"]
+                  and bool(lib.fedb_fitx_fits(int(d[0]), int(d[1]), int(d[2]), int(d[3]))))
+    return out
+
+
+def fit_tcx(tb: DeviceTables, params, m, v, X, y, idx_in, idx_epoch, step, active, fed_state, epoch, no_improve, best_loss, last_loss,
+            loss_out, tol: float, n_iter_no_change: int, max_iter: int, max_epochs: int, shuffle: bool, seed: int) -> None:
+    """The whole local fit of every active client in one launch on the tensor cores (fedb_fit_tcx)."""
+    nat.check(_L().fedb_fit_tcx(nat.ptr(tb.d_groups), tb.n_groups, nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(X), X.shape[1],
+                                nat.ptr(y), nat.ptr(idx_in), nat.ptr(idx_epoch), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
+                                nat.ptr(epoch), nat.ptr(no_improve), nat.ptr(best_loss), nat.ptr(last_loss), nat.ptr(loss_out),
+                                float(tol), int(n_iter_no_change), int(max_iter), int(max_epochs), int(bool(shuffle)),
+                                seed & (2 ** 64 - 1), nat.cuda_stream()))
+    _count()
