@@ -413,12 +413,18 @@ def run_ours_modes(args):
             ms_e2e, _ = timed(e2e)
         epochs = int(np.asarray(h["n_iter"]).max(axis=1).sum())
         value = K / (ms / 1e3)
+        tcm = eng._fit_tc_mask()
+        if tcm is not None and bool(tcm.all()):      # one launch fits every client to convergence (csrc/fedb_fitx.cu)
+            launches = K * 4
+            kernels = ["k_round_begin", "k_fit_tcx[shuffle+fwd+bwd+Adam+stopping rule, all epochs]", "k_eval", eng.kernel_names[-1]]
+        else:
+            launches = epochs * (2 + 2 * eng.n_batches) + 3 * K
+            kernels = ["k_shuffle", "k_fwd_bwd", "k_reduce_opt", "k_epoch_end", "k_eval", eng.kernel_names[-1]]
         test = eng.evaluate_global("test")[0]
         rec.update({"value": value, "ms_per_step": ms / K, "vs_baseline": value / BASELINE_SK_ROUNDS_PER_SEC, "dtype": "fp32",
                     "e2e": {"value": K / (ms_e2e / 1e3), "unit": "rounds/s", "ms_per_step": ms_e2e / K,
                             "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4), "d2h_bytes_per_step": int(eng.fed_state.numel())},
-                    "gpu_launches": epochs * (2 + 2 * eng.n_batches) + 3 * K, "epochs_longest_client": epochs,
-                    "kernels": ["k_shuffle", "k_fwd_bwd", "k_reduce_opt", "k_epoch_end", "k_eval", eng.kernel_names[-1]],
+                    "gpu_launches": launches, "epochs_longest_client": epochs, "kernels": kernels,
                     "pooled_train_accuracy_per_round": [float(x) for x in h["global"][0, -K:, 0]],
                     "held_out_accuracy_of_the_averaged_model": test["accuracy"], "clocks": clk.summary()})
         eng.check_errors()
@@ -444,8 +450,10 @@ def run_ours_modes(args):
                                     "tables, the fits, the read-back of every federation's metrics and weights",
                             "h2d_bytes_per_step": int(data.X_train.size * 4 + data.X_test.size * 4 + 10000 * 4),
                             "d2h_bytes_per_step": int(sum(sum(w.size for w in r["weights"][0]) + sum(b.size for b in r["weights"][1]) for r in out["results"]) * 4)},
-                    "gpu_launches": timing.get("epochs", 0) * timing.get("launches_per_epoch", 0) + 3 * K,
-                    "kernels": ["k_shuffle", "k_fwd_bwd", "k_reduce_opt", "k_epoch_end", "k_eval", "k_fedavg"],
+                    "gpu_launches": timing.get("epochs", 0) * timing.get("launches_per_epoch", 0) + (3 + (1 if timing.get("tc_clients", 0) else 0)) * K,
+                    "clients_on_tensor_cores": [timing.get("tc_clients", 0), timing.get("clients", 0)],
+                    "kernels": ["k_fit_tcx (2-hidden-layer shapes with h1 <= 63)", "k_shuffle", "k_fwd_bwd", "k_reduce_opt", "k_epoch_end", "k_eval",
+                                "k_fedavg"],
                     "best": {"hidden_layer_sizes": list(out["best_params"]["hidden_layer_sizes"]), "learning_rate": out["best_params"]["learning_rate"],
                              "accuracy": out["best_metrics"]["accuracy"]}, "clocks": clk.summary()})
     if rank == 0:

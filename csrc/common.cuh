@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <type_traits>
+
 #include "../include/fedb200.h"
 
 namespace fedb {
@@ -180,6 +182,26 @@ __device__ __forceinline__ float opt_update(const FedbGroup& G, const StepScalar
     return w - sc.lr_eff * m / (sqrtf(v) + G.eps);
   } else {
     // SKO SGDOptimizer: velocity = momentum*velocity - lr*g ; nesterov looks ahead
+    m = G.momentum * m - sc.lr_eff * g;
+    const float upd = G.nesterov ? (G.momentum * m - sc.lr_eff * g) : m;
+    return w + upd;
+  }
+}
+
+// opt_update with the optimizer kind as a compile-time constant: callers that update many independent parameters per thread
+// branch ONCE around straight-line code, so the square-root / division chains overlap.  Same expressions, same results.
+template <int OPT>
+__device__ __forceinline__ float opt_update_t(const FedbGroup& G, const StepScalars& sc, float w, float g, float& m, float& v) {
+  if (OPT == FEDB_OPT_ADAM_TORCH) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    const float denom = sqrtf(v) * sc.inv_sqrt_bc2 + G.eps;
+    return w - sc.lr_eff * (m / denom);
+  } else if (OPT == FEDB_OPT_ADAM_SKLEARN) {
+    m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+    v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+    return w - sc.lr_eff * m / (sqrtf(v) + G.eps);
+  } else {
     m = G.momentum * m - sc.lr_eff * g;
     const float upd = G.nesterov ? (G.momentum * m - sc.lr_eff * g) : m;
     return w + upd;

@@ -15,8 +15,10 @@
 // Consequences: layer 1 is replicated (K = 16, negligible); the logits need one exchange per tile — every CTA writes its
 // partial row sums into all peers' shared memory, one cluster barrier, everyone adds the four partials in rank order —;
 // dW2 / db2 / dW3 of a CTA's slice are COMPLETE in its own TMEM (it saw all rows), so the bulk of the model (96 %) never
-// crosses a CTA boundary: the owner applies Adam straight from the accumulators and rewrites its own operand panels, master
-// weights and moments staying in global memory (L2) where only this CTA touches them; the backward pass is linear in dH1,
+// crosses a CTA boundary: the owner applies Adam straight from the accumulators and rewrites its own operand panels; the
+// fp32 master weights and both moments of the slice live in TENSOR MEMORY for the whole fit (3 x 64 columns in the same
+// lane / column geometry as the dW2 accumulator: a thread reads gradient, weight, m and v of its 16 elements with four
+// tcgen05.ld and puts them back with three tcgen05.st, no global memory in the step); the backward pass is linear in dH1,
 // so each CTA turns its PARTIAL dH1 = dZ2_slice W2_slice into a partial dW1 / db1 (50 x 16 numbers), which are exchanged like
 // the logits and applied redundantly by all four CTAs to their replicated copy of W1 (fp32 master and moments in shared
 // memory).  Three cluster barriers per mini-batch of 200 rows, no other synchronisation between CTAs, none between clients.
@@ -55,7 +57,14 @@ constexpr int G1_FLOATS = 64 * 16 + 16;
 constexpr int FX_END = FX_G1 + FNC * G1_FLOATS * 4;
 static_assert(FX_END + 1024 + 4096 <= 227 * 1024, "fit kernel: shared memory map too large");
 // TMEM columns
-constexpr uint32_t TF_D1 = 0, TF_D2 = 64, TF_DW2 = 192, TF_DW1 = 256, TF_DW3 = 288, TF_ZX = 304;
+// TMEM columns: accumulators D1 (layer-1 pre-activations, later the partial dH1), D2 (my slice of layer 2), DW2 / DW1 / DW3
+// (weight gradients); ZX (the exchange of a row's four partial logits) reuses D1 while it is dead.  Then the optimizer state
+// of the slice, resident for the whole fit: W / M / V [128 units][64] (column 63 = b2), S3 = {W3[0], W3[1], m, m, v, v} per unit.
+constexpr uint32_t TF_D1 = 0, TF_D2 = 64, TF_DW2 = 192, TF_DW1 = 256, TF_DW3 = 288, TF_ZX = TF_D1;
+constexpr uint32_t TF_W = 304, TF_M = 368, TF_V = 432, TF_S3 = 496;
+// Adam's square root and division as single MUFU approximations (2 ulp) instead of the IEEE sequences: the error of a step is
+// 2^-22 of lr, far below the rounding of the fp32 weight it is added to; the step is instruction-issue bound otherwise.
+constexpr bool FITX_FAST = true;
 
 struct FitXArgs {
   const FedbGroup* groups;
@@ -77,6 +86,7 @@ struct FitXArgs {
   double tol;
   int ldx, n_iter_no_change, max_iter, max_epochs, shuffle;
   uint32_t s0, s1;
+  long long* prof;   // optional: globaltimer stamps of thread 0 of every CTA of client 0 during the first mini-batch, [NC][32]
 };
 
 struct ShapeF {
@@ -91,6 +101,8 @@ __device__ __forceinline__ void st_cluster_f1(uint32_t a, const float x) {
 __device__ __forceinline__ void st_cluster_f4(uint32_t a, const float4 v) {
   asm volatile("st.shared::cluster.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_barrier() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -100,6 +112,26 @@ __device__ __forceinline__ void handoff_f() {
   tc::tc_fence_before();
   tc::fence_async_smem();
   __syncthreads();
+}
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float y;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// opt_update_t (common.cuh) with the fast square root / division
+template <int OPT>
+__device__ __forceinline__ float opt_upd_x(const FedbGroup& G, const StepScalars& sc, float w, float g, float& m, float& v) {
+  if (!FITX_FAST || OPT == FEDB_OPT_SGD) return opt_update_t<OPT>(G, sc, w, g, m, v);
+  m = fmaf(G.beta1, m, (1.f - G.beta1) * g);
+  v = fmaf(G.beta2, v, (1.f - G.beta2) * g * g);
+  if (OPT == FEDB_OPT_ADAM_TORCH) return w - sc.lr_eff * __fdividef(m, sqrt_approx(v) * sc.inv_sqrt_bc2 + G.eps);
+  return w - __fdividef(sc.lr_eff * m, sqrt_approx(v) + G.eps);
+}
+__device__ __forceinline__ float opt_upd_any(const FedbGroup& G, const StepScalars& sc, float w, float g, float& m, float& v) {
+  if (G.opt == FEDB_OPT_ADAM_SKLEARN) return opt_upd_x<FEDB_OPT_ADAM_SKLEARN>(G, sc, w, g, m, v);
+  if (G.opt == FEDB_OPT_ADAM_TORCH) return opt_upd_x<FEDB_OPT_ADAM_TORCH>(G, sc, w, g, m, v);
+  return opt_upd_x<FEDB_OPT_SGD>(G, sc, w, g, m, v);
 }
 
 // split-fp16 writers into THIS CTA's panels (weights are held scaled by WS)
@@ -189,7 +221,9 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float red_f[4][9];        // per-warp partial sums of the four part-0 warps: loss + db3[8]
-  __shared__ float red_ss[FT / 32];    // per-warp partial sums of squares
+  __shared__ float red_ss[FT / 32];    // per-warp partial sums of squares: my slice (after its update) ...
+  __shared__ float red_ss1[FT / 32];   // ... and layer 1 (before its update)
+  __shared__ float s_ss_slice;         // ||W||^2 of my slice as it stands: the L2 term of the NEXT step's loss
   __shared__ StepScalars sc_s;
   __shared__ FedbGroup Gs;
   __shared__ int s_alive;
@@ -227,6 +261,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
   const int lane128 = (warp & 3) * 32 + lane;   // data row inside the tile = TMEM lane
   const int part = warp >> 2;                   // column quarter of every epilogue
   const int row = lane128;
+  const int c1 = 16 * part;
   float* Pg = a.params + G.slab_off;
   float* Mg = a.m + G.slab_off;
   float* Vg = a.v + G.slab_off;
@@ -237,7 +272,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
     tc::mbar_init(&bar, 1);
     tc::fence_mbar_init();
   }
-  for (int i = tid; i < (FX_ZP - FX_W1) / 16; i += FT) *reinterpret_cast<uint4*>(sm + FX_W1 + i * 16) = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < (FX_ZP - FX_X) / 16; i += FT) *reinterpret_cast<uint4*>(sm + FX_X + i * 16) = make_uint4(0, 0, 0, 0);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -253,18 +288,68 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
   uint8_t* const h1_hi = sm + FX_H1;
   uint8_t* const h1_lo = sm + FX_H1 + FP;
 
-  // ---- operand image: my slice of W2 / b2 / W3 from the master copy; layer 1 and b3 replicated, with their moments
+  // ---- my slice of W2 / b2 / W3 from the master copy: fp32 weights and moments into tensor memory, split operands into
+  //      the panels (thread = unit j of the slice x a 16-column part); layer 1 and b3 replicated in shared memory
   {
-    const int nq = s.ld1 >> 2;
-    for (int t = tid; t < s.nj * nq; t += FT) {
-      const int j = t / nq, c4 = t - j * nq;
-      put_w2f(sm, j, 4 * c4, __ldcg(reinterpret_cast<const float4*>(Pg + s.w_off1 + (s.J0 + j) * s.ld1) + c4));
+    const int j = lane128;
+    const bool mine = j < s.nj;
+    const int e0 = s.w_off1 + (s.J0 + (mine ? j : 0)) * s.ld1;
+    float ss0 = 0.f;
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      const int c0 = c1 + 8 * hf;
+      float w8[8], m8[8], v8[8];
+#pragma unroll
+      for (int i4 = 0; i4 < 2; ++i4) {
+        const int col = c0 + 4 * i4;
+        const bool in = mine && col < s.ld1;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 w = in ? __ldcg(reinterpret_cast<const float4*>(Pg + e0 + col)) : z4;
+        const float4 mm = in ? __ldcg(reinterpret_cast<const float4*>(Mg + e0 + col)) : z4;
+        const float4 vv = (in && use_v) ? __ldcg(reinterpret_cast<const float4*>(Vg + e0 + col)) : z4;
+        w8[4 * i4] = w.x; w8[4 * i4 + 1] = w.y; w8[4 * i4 + 2] = w.z; w8[4 * i4 + 3] = w.w;
+        m8[4 * i4] = mm.x; m8[4 * i4 + 1] = mm.y; m8[4 * i4 + 2] = mm.z; m8[4 * i4 + 3] = mm.w;
+        v8[4 * i4] = vv.x; v8[4 * i4 + 1] = vv.y; v8[4 * i4 + 2] = vv.z; v8[4 * i4 + 3] = vv.w;
+        ss0 += w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
+      }
+      if (part == 3 && hf == 1) {   // column 63 (beyond h1 <= 63, a zero so far) carries b2: it multiplies H1's constant-1 column
+        const int e = s.b_off1 + s.J0 + (mine ? j : 0);
+        w8[7] = mine ? __ldcg(Pg + e) : 0.f;
+        m8[7] = mine ? __ldcg(Mg + e) : 0.f;
+        v8[7] = (mine && use_v) ? __ldcg(Vg + e) : 0.f;
+      }
+      tc::tmem_st8(tl + TF_W + c0, w8);
+      tc::tmem_st8(tl + TF_M + c0, m8);
+      tc::tmem_st8(tl + TF_V + c0, v8);
+      put_w2f(sm, j, c0, make_float4(w8[0], w8[1], w8[2], w8[3]));
+      put_w2f(sm, j, c0 + 4, make_float4(w8[4], w8[5], w8[6], w8[7]));
     }
-    __syncthreads();   // (ld1 = 64: the last segment of a row covers column 63; b2 goes in after it)
-    for (int j = tid; j < s.nj; j += FT) {
-      put_b2f(sm, j, __ldcg(Pg + s.b_off1 + s.J0 + j));
-      for (int k = 0; k < s.C; ++k) W3s[j * 8 + k] = __ldcg(Pg + s.w_off2 + k * s.ld2 + s.J0 + j);
+    if (part == 0) {   // head weights of classes 0, 1 of unit j with their moments
+      float s3[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s3[i] = 0.f;
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        if (mine && k < s.C) {
+          const int e = s.w_off2 + k * s.ld2 + s.J0 + j;
+          s3[k] = __ldcg(Pg + e);
+          s3[2 + k] = __ldcg(Mg + e);
+          s3[4 + k] = use_v ? __ldcg(Vg + e) : 0.f;
+          ss0 += s3[k] * s3[k];
+        }
+      tc::tmem_st8(tl + TF_S3, s3);
     }
+    if (part == 2 && mine)
+      for (int k = 2; k < s.C; ++k) {
+        const float w = __ldcg(Pg + s.w_off2 + k * s.ld2 + s.J0 + j);
+        ss0 += w * w;
+      }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss0 += __shfl_xor_sync(0xffffffffu, ss0, o);
+    if (lane == 0) red_ss[warp] = ss0;
+    tc::tmem_st_wait();
+    for (int jj = tid; jj < s.nj; jj += FT)
+      for (int k = 0; k < s.C; ++k) W3s[jj * 8 + k] = __ldcg(Pg + s.w_off2 + k * s.ld2 + s.J0 + jj);
     for (int t = tid; t < s.h1 * 16; t += FT) {
       const int i = t >> 4, col = t & 15;
       int e = -1;
@@ -280,6 +365,11 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
       b3s[16 + tid] = use_v ? __ldcg(Vg + s.b_off2 + tid) : 0.f;
     }
     __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int w = 0; w < FT / 32; ++w) t += red_ss[w];
+      s_ss_slice = t;
+    }
     for (int t = tid; t < s.h1 * 4; t += FT) {
       const int i = t >> 2, c4 = t & 3;
       put_w1f(sm, i, 4 * c4, *reinterpret_cast<const float4*>(M1 + i * 16 + 4 * c4));
@@ -289,6 +379,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
   __syncthreads();
   cluster_barrier();   // every CTA of the cluster is running: its shared memory may be written from here on
 
+#define FSTAMP(i) do { if (a.prof && g == 0 && tid == 0 && ep == 0 && b == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); a.prof[q * 32 + (i)] = t_; } } while (0)
 #define FIT_MMA_PHASE(ISSUE)             \
   do {                                   \
     if (tid == 0) {                      \
@@ -303,7 +394,6 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
 
   const int nch2 = s.N2 >> 4;
   const int ch_lo = part * (nch2 >> 2) + min(part, nch2 & 3), ch_hi = ch_lo + (nch2 >> 2) + (part < (nch2 & 3) ? 1 : 0);
-  const int c1 = 16 * part;
   int t_step = a.step[g];
   const int ep_base = a.epoch[g];   // epochs completed before this launch (also keys the reshuffle)
   int eps_run = 0, no_imp = a.no_improve[g];
@@ -326,6 +416,30 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
       cluster_barrier();
     }
     double acc_loss = 0.0;   // thread 0: sum over mini-batches of (row losses + 0.5 alpha ||W||^2), SK:353-361
+    // Input rows run two tiles ahead of the math: the row INDEX of the tile after next and the DATA of the next tile are in
+    // flight while a tile computes, so neither of the two dependent loads is ever waited for.
+    auto pos_of = [&](int bb, int tt) -> int {   // position in the shard of this thread's row of tile tt of mini-batch bb, or -1
+      const int b0_ = bb * bs;
+      if (b0_ >= n) return -1;
+      const int r_ = tt * FR + row;
+      return r_ < min(bs, n - b0_) ? b0_ + r_ : -1;
+    };
+    auto advance = [&](int& bb, int& tt) {
+      const int nt_ = (min(bs, max(0, n - bb * bs)) + FR - 1) / FR;
+      if (++tt >= nt_) { tt = 0; ++bb; }
+    };
+    float4 nx = make_float4(0.f, 0.f, 0.f, 0.f);
+    int nlabel = 0, ngrow = -1, pb = 0, pt = 0;   // (pb, pt): the tile whose row index is in ngrow
+    if (row < min(bs, n)) {
+      const int grow = __ldcg(idxsrc + G.idx_off + row);
+      nx = __ldg(reinterpret_cast<const float4*>(a.X + (size_t)grow * a.ldx) + part);
+      nlabel = __ldg(a.y + grow);
+    }
+    advance(pb, pt);
+    {
+      const int p1 = pos_of(pb, pt);
+      if (p1 >= 0) ngrow = __ldcg(idxsrc + G.idx_off + p1);
+    }
 
     for (int b = 0; b < nbatches; ++b) {
       const int b0 = b * bs, nb = min(bs, n - b0);
@@ -336,23 +450,19 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
 #pragma unroll
       for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] = 0.f;
 
+      FSTAMP(0);
       for (int tile = 0; tile < ntiles; ++tile) {
         const bool acc = tile > 0;
         const int r = tile * FR + row;
         const bool valid = r < nb;
-        // ---- this thread's four input columns of data row r ------------------------------------------------
+        // ---- this thread's four input columns of data row r (fetched one tile ahead) ---------------------------------
         int label = 0;
         {
-          float f[4] = {0.f, 0.f, 0.f, 0.f};
-          if (valid) {
-            const int grow = __ldcg(idxsrc + G.idx_off + b0 + r);
-            const float4 x = __ldg(reinterpret_cast<const float4*>(a.X + (size_t)grow * a.ldx) + part);
-            f[0] = x.x; f[1] = x.y; f[2] = x.z; f[3] = x.w;
-            label = __ldg(a.y + grow);
-          }
+          float f[4] = {nx.x, nx.y, nx.z, nx.w};
+          label = nlabel;
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            if (4 * part + i >= s.d0) f[i] = 0.f;
+            if (4 * part + i >= s.d0 || !valid) f[i] = 0.f;
           if (part == 3) f[3] = valid ? 1.f : 0.f;   // column 15: the bias input
           uint32_t h0, l0, h1, l1;
           split2(f[0], f[1], h0, l0);
@@ -360,9 +470,23 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           *reinterpret_cast<uint2*>(sm + FX_X + tc::panel_off(row, 4 * part)) = make_uint2(h0, h1);
           *reinterpret_cast<uint2*>(sm + FX_X + tc::panel_off(row, 16 + 4 * part)) = make_uint2(l0, l1);
         }
+        {   // the next tile's data (its index arrived a tile ago) and the index of the tile after it
+          nx = make_float4(0.f, 0.f, 0.f, 0.f);
+          nlabel = 0;
+          if (ngrow >= 0) {
+            nx = __ldg(reinterpret_cast<const float4*>(a.X + (size_t)ngrow * a.ldx) + part);
+            nlabel = __ldg(a.y + ngrow);
+          }
+          advance(pb, pt);
+          const int p2 = pos_of(pb, pt);
+          ngrow = -1;
+          if (p2 >= 0) ngrow = __ldcg(idxsrc + G.idx_off + p2);
+        }
         handoff_f();
+        if (tile == 0) FSTAMP(1);
         // ---- layer 1 (replicated in the four CTAs) ----------------------------------------------------------
         FIT_MMA_PHASE(mma.fwd1());
+        if (tile == 0) FSTAMP(2);
         uint32_t mask1 = 0;
         {
           float v[16];
@@ -377,8 +501,10 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           st_panel8(h1_hi, h1_lo, row, c1 + 8, v + 8);
         }
         handoff_f();
+        if (tile == 0) FSTAMP(3);
         // ---- my slice of layer 2, partial logits -------------------------------------------------------------
         FIT_MMA_PHASE(mma.fwd2(s.N2));
+        if (tile == 0) FSTAMP(4);
         float z[FEDB_MAX_CLASSES], dz3[FEDB_MAX_CLASSES];
 #pragma unroll
         for (int k = 0; k < FEDB_MAX_CLASSES; ++k) z[k] = dz3[k] = 0.f;
@@ -415,6 +541,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
         tc::tc_fence_before();
         __syncthreads();
         tc::tc_fence_after();
+        if (tile == 0) FSTAMP(5);
         const int par = (int)(tile_ctr & 1u);
         ++tile_ctr;
         if (part == 0) {
@@ -432,6 +559,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
             }
         }
         cluster_barrier();
+        if (tile == 0) FSTAMP(6);
         {
           const float* zp = zpart + (size_t)par * FNC * 8 * FR + row;
 #pragma unroll
@@ -472,8 +600,12 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           *reinterpret_cast<uint4*>(sm + FX_X + tc::panel_off(row, 40)) = dl;
         }
         handoff_f();
+        if (tile == 0) FSTAMP(7);
         // ---- head weight gradient of my slice (needs H2), then dZ2 overwrites H2 ---------------------------------
+        // (measured: running the first chunk of the next epilogue under these MMAs and waiting only before its stores made the
+        //  FOLLOWING MMA phases slower by more than it saved: 18.3 against 17.2 us for the two tiles)
         FIT_MMA_PHASE(mma.wgrad3(acc));
+        if (tile == 0) FSTAMP(8);
 #pragma unroll 1
         for (int ch = ch_lo; ch < ch_hi; ++ch) {
           const int c0 = ch << 4;
@@ -500,8 +632,10 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           st_panel8(pz, pz + 2 * FP, row, (c0 & 63) + 8, d + 8);
         }
         handoff_f();
+        if (tile == 0) FSTAMP(9);
         // ---- partial dH1 = dZ2_slice W2_slice ; dW2_slice += dZ2_slice^T H1 -----------------------------------------
         FIT_MMA_PHASE(mma.dgrad2_wgrad2(s.N2, acc));
+        if (tile == 0) FSTAMP(10);
         {
           float v[16];
           tc::tmem_ld16(tl + TF_D1 + c1, v);
@@ -512,8 +646,11 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           st_panel8(h1_hi, h1_lo, row, c1 + 8, v + 8);
         }
         handoff_f();
+        if (tile == 0) FSTAMP(11);
         FIT_MMA_PHASE(mma.wgrad1(acc));
+        if (tile == 0) FSTAMP(12);
       }  // tiles
+      FSTAMP(13);
 
       // ---- layer-1 partial gradients -> every CTA of the cluster (they are summed after the barrier below) -----------------
       if (part == 1) {
@@ -546,76 +683,103 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           if (lane == 0) red_f[warp][i] = x;
         }
       }
-      if (tid == 0) sc_s = step_scalars_fast(G, t_step);
-      __syncthreads();
-      const StepScalars sc = sc_s;
-      const float al = G.alpha * inv_n;
-
-      // ---- my slice: Adam straight from the accumulators (complete: this CTA saw every row), new values into my panels ----
-      float ss = 0.f;   // sum of squares of the weights (before the update) for the L2 term of the loss
-      {
-        const int j = lane128;
-        float gq[16];
-        tc::tmem_ld16(tl + TF_DW2 + c1, gq);
-        tc::tmem_ld_wait();
-        if (j < s.nj) {
-#pragma unroll
-          for (int i4 = 0; i4 < 4; ++i4) {
-            const int col = c1 + 4 * i4;
-            if (col < s.ld1) {
-              const int e = s.w_off1 + (s.J0 + j) * s.ld1 + col;
-              float4 w = *reinterpret_cast<const float4*>(Pg + e), mm = *reinterpret_cast<const float4*>(Mg + e);
-              float4 vv = use_v ? *reinterpret_cast<const float4*>(Vg + e) : make_float4(0.f, 0.f, 0.f, 0.f);
-              ss += w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
-              w.x = opt_update(G, sc, w.x, fmaf(al, w.x, gq[4 * i4] * gscale), mm.x, vv.x);
-              w.y = opt_update(G, sc, w.y, fmaf(al, w.y, gq[4 * i4 + 1] * gscale), mm.y, vv.y);
-              w.z = opt_update(G, sc, w.z, fmaf(al, w.z, gq[4 * i4 + 2] * gscale), mm.z, vv.z);
-              w.w = opt_update(G, sc, w.w, fmaf(al, w.w, gq[4 * i4 + 3] * gscale), mm.w, vv.w);
-              // (columns h1 .. ld1-1 are padding: their gradient and weight are exact zeros and stay so)
-              *reinterpret_cast<float4*>(Pg + e) = w;
-              *reinterpret_cast<float4*>(Mg + e) = mm;
-              if (use_v) *reinterpret_cast<float4*>(Vg + e) = vv;
-              put_w2f(sm, j, col, w);
-            }
-          }
-          if (part == 3) {   // column 63 multiplied the constant-1 input: db2
-            const int e = s.b_off1 + s.J0 + j;
-            float w = Pg[e], mm = Mg[e], vv = use_v ? Vg[e] : 0.f;
-            w = opt_update(G, sc, w, gq[15] * gscale, mm, vv);
-            Pg[e] = w; Mg[e] = mm;
-            if (use_v) Vg[e] = vv;
-            put_b2f(sm, j, w);
-          }
-        }
-        if (part == 0) {     // head weights of my slice: dW3[k][j] = DW3[j][k] + DW3[j][8 + k]
-          tc::tmem_ld16(tl + TF_DW3, gq);
-          tc::tmem_ld_wait();
-          if (j < s.nj) {
-#pragma unroll
-            for (int k = 0; k < FEDB_MAX_CLASSES; ++k)
-              if (k < s.C) {
-                const int e = s.w_off2 + k * s.ld2 + s.J0 + j;
-                float w = Pg[e], mm = Mg[e], vv = use_v ? Vg[e] : 0.f;
-                ss += w * w;
-                w = opt_update(G, sc, w, fmaf(al, w, (gq[k] + gq[8 + k]) * gscale), mm, vv);
-                Pg[e] = w; Mg[e] = mm;
-                if (use_v) Vg[e] = vv;
-                W3s[j * 8 + k] = w;
-              }
-          }
-        }
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-      if (lane == 0) red_ss[warp] = ss;
-      __syncthreads();
       if (tid == 0) {
-        float t = 0.f;
-        for (int w = 0; w < FT / 32; ++w) t += red_ss[w];
+        sc_s = step_scalars_fast(G, t_step);
+        const float t = s_ss_slice;   // my slice's ||W||^2 before this step's update (kept from the previous update)
 #pragma unroll
         for (int rk = 0; rk < FNC; ++rk) st_cluster_f1(mapa(sm_u + FX_G1 + (uint32_t)(q * G1_FLOATS + 64 * 16) * 4u, rk), t);
       }
-      cluster_barrier();   // every CTA's layer-1 partials and slice sums have landed everywhere
+      __syncthreads();
+      cluster_arrive();   // my layer-1 partials and slice sum are on their way; the wait follows the slice optimizer
+      FSTAMP(14);
+      const StepScalars sc = sc_s;
+      const float al = G.alpha * inv_n;
+
+      // ---- my slice: Adam straight from the accumulators (complete: this CTA saw every row) on the state in tensor memory,
+      //      new operands into my panels.  The optimizer kind is decided ONCE around straight-line code, so the independent
+      //      chains of a thread overlap.
+      float ss = 0.f;   // sum of squares of the NEW weights: the L2 term of the next step's loss
+      {
+        const int j = lane128;
+        const bool mine = j < s.nj;
+        auto update_all = [&](auto tag) {
+          constexpr int OPT = decltype(tag)::value;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = c1 + 8 * hf;
+            float g8[8], w8[8], m8[8], v8[8];
+            tc::tmem_ld8(tl + TF_DW2 + c0, g8);
+            tc::tmem_ld8(tl + TF_W + c0, w8);
+            tc::tmem_ld8(tl + TF_M + c0, m8);
+            tc::tmem_ld8(tl + TF_V + c0, v8);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const bool is_b2 = hf == 1 && i == 7 && part == 3;   // column 63: no L2 term, not part of ||W||^2
+              const float w = w8[i], gr = g8[i] * gscale;
+              const float wn = opt_upd_x<OPT>(G, sc, w, is_b2 ? gr : fmaf(al, w, gr), m8[i], v8[i]);
+              ss += (is_b2 || !mine) ? 0.f : wn * wn;
+              // (columns h1 .. 62 are padding: gradient and weight are exact zeros and stay so; lanes beyond the slice are
+              //  kept at zero whatever the accumulator rows there hold)
+              w8[i] = mine ? wn : 0.f;
+              m8[i] = mine ? m8[i] : 0.f;
+              v8[i] = mine ? v8[i] : 0.f;
+            }
+            tc::tmem_st8(tl + TF_W + c0, w8);
+            tc::tmem_st8(tl + TF_M + c0, m8);
+            tc::tmem_st8(tl + TF_V + c0, v8);
+            put_w2f(sm, j, c0, make_float4(w8[0], w8[1], w8[2], w8[3]));
+            put_w2f(sm, j, c0 + 4, make_float4(w8[4], w8[5], w8[6], w8[7]));
+          }
+          if (part == 0) {   // head weights of classes 0, 1: dW3[k][j] = DW3[j][k] + DW3[j][8 + k]
+            float s3[8], g3[16];
+            tc::tmem_ld8(tl + TF_S3, s3);
+            tc::tmem_ld16(tl + TF_DW3, g3);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const float w = s3[k];
+              const float wn = opt_upd_x<OPT>(G, sc, w, fmaf(al, w, (g3[k] + g3[8 + k]) * gscale), s3[2 + k], s3[4 + k]);
+              const bool on = mine && k < s.C;
+              ss += on ? wn * wn : 0.f;
+              s3[k] = on ? wn : 0.f;
+              s3[2 + k] = on ? s3[2 + k] : 0.f;
+              s3[4 + k] = on ? s3[4 + k] : 0.f;
+              if (on) W3s[j * 8 + k] = wn;
+            }
+            tc::tmem_st8(tl + TF_S3, s3);
+          }
+        };
+        FSTAMP(18);
+        if (G.opt == FEDB_OPT_ADAM_SKLEARN) update_all(std::integral_constant<int, FEDB_OPT_ADAM_SKLEARN>{});
+        else if (G.opt == FEDB_OPT_ADAM_TORCH) update_all(std::integral_constant<int, FEDB_OPT_ADAM_TORCH>{});
+        else update_all(std::integral_constant<int, FEDB_OPT_SGD>{});
+        FSTAMP(19);
+        if (part == 2 && s.C > 2 && mine) {   // head weights of further classes (rare): state in global memory
+          float g3[16];
+          tc::tmem_ld16(tl + TF_DW3, g3);
+          tc::tmem_ld_wait();
+          for (int k = 2; k < s.C; ++k) {
+            const int e = s.w_off2 + k * s.ld2 + s.J0 + j;
+            float w0 = Pg[e], mm = Mg[e], vv = use_v ? Vg[e] : 0.f, gk = 0.f;
+#pragma unroll
+            for (int t = 2; t < 8; ++t) gk = (t == k) ? (g3[t] + g3[8 + t]) * gscale : gk;
+            const float w = opt_upd_any(G, sc, w0, fmaf(al, w0, gk), mm, vv);
+            ss += w * w;
+            Pg[e] = w; Mg[e] = mm;
+            if (use_v) Vg[e] = vv;
+            W3s[j * 8 + k] = w;
+          }
+        }
+        tc::tmem_st_wait();
+        FSTAMP(20);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+      if (lane == 0) red_ss[warp] = ss;    // (summed by thread 0 after the block barrier of the layer-1 phase)
+      FSTAMP(15);
+      cluster_wait();      // every CTA's layer-1 partials and slice sums have landed everywhere
+      FSTAMP(16);
 
       // ---- layer 1 and b3: the same update in all four CTAs, on their replicated fp32 copies in shared memory ------------------
       float ss1 = 0.f;
@@ -635,9 +799,9 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           float w = M1[o + l], mm = M1[1024 + o + l], vv = M1[2048 + o + l];
           if (col < s.d0) {
             ss1 += w * w;
-            w = opt_update(G, sc, w, fmaf(al, w, gk[l]), mm, vv);
+            w = opt_upd_any(G, sc, w, fmaf(al, w, gk[l]), mm, vv);
           } else if (col == 15) {
-            w = opt_update(G, sc, w, gk[l], mm, vv);
+            w = opt_upd_any(G, sc, w, gk[l], mm, vv);
           }
           M1[o + l] = w; M1[1024 + o + l] = mm; M1[2048 + o + l] = vv;
           wn[l] = w;
@@ -647,22 +811,24 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
       if (tid >= FT - 32 && lane < s.C) {   // b3 (its gradient is the same in every CTA)
         float w = b3s[lane], mm = b3s[8 + lane], vv = b3s[16 + lane];
         const float gr = (red_f[0][1 + lane] + red_f[1][1 + lane]) + (red_f[2][1 + lane] + red_f[3][1 + lane]);
-        w = opt_update(G, sc, w, gr, mm, vv);
+        w = opt_upd_any(G, sc, w, gr, mm, vv);
         b3s[lane] = w; b3s[8 + lane] = mm; b3s[16 + lane] = vv;
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) ss1 += __shfl_xor_sync(0xffffffffu, ss1, o);
-      if (lane == 0) red_ss[warp] = ss1;
+      if (lane == 0) red_ss1[warp] = ss1;
       tc::fence_async_smem();
       __syncthreads();
       if (tid == 0) {
-        float t1 = 0.f;
-        for (int w = 0; w < FT / 32; ++w) t1 += red_ss[w];
+        float t1 = 0.f, t2 = 0.f;
+        for (int w = 0; w < FT / 32; ++w) { t1 += red_ss1[w]; t2 += red_ss[w]; }
+        s_ss_slice = t2;
         const float ss_all = ((g1part[0 * G1_FLOATS + 1024] + g1part[1 * G1_FLOATS + 1024]) + (g1part[2 * G1_FLOATS + 1024] + g1part[3 * G1_FLOATS + 1024])) + t1;
         const float rowloss = (red_f[0][0] + red_f[1][0]) + (red_f[2][0] + red_f[3][0]);
         acc_loss += (double)rowloss + 0.5 * (double)G.alpha * (double)ss_all;
         last_batch_loss = rowloss * inv_n;
       }
+      FSTAMP(17);
     }  // mini-batches
 
     // ---- end of the epoch: loss curve and the tol / n_iter_no_change rule (SK:750-777), identical in every CTA ----------
@@ -679,8 +845,53 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
     __syncthreads();
   }
 #undef FIT_MMA_PHASE
+#undef FSTAMP
 
-  // ---- write back what lived on chip: layer 1, b3 and their moments (CTA 0), counters and the loss curve state --------------
+  // ---- write back what lived on chip: every CTA its slice (weights and moments from tensor memory); layer 1, b3 and their
+  //      moments, the counters and the loss curve state by CTA 0 ----------------------------------------------------------------
+  {
+    const int j = lane128;
+    const bool mine = j < s.nj;
+    const int e0 = s.w_off1 + (s.J0 + (mine ? j : 0)) * s.ld1;
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      const int c0 = c1 + 8 * hf;
+      float w8[8], m8[8], v8[8];
+      tc::tmem_ld8(tl + TF_W + c0, w8);
+      tc::tmem_ld8(tl + TF_M + c0, m8);
+      tc::tmem_ld8(tl + TF_V + c0, v8);
+      tc::tmem_ld_wait();
+      if (part == 3 && hf == 1) {
+        if (mine) {
+          const int e = s.b_off1 + s.J0 + j;
+          Pg[e] = w8[7]; Mg[e] = m8[7];
+          if (use_v) Vg[e] = v8[7];
+        }
+        w8[7] = m8[7] = v8[7] = 0.f;   // column 63 of the master row (present when ld1 = 64) is padding
+      }
+#pragma unroll
+      for (int i4 = 0; i4 < 2; ++i4) {
+        const int col = c0 + 4 * i4;
+        if (mine && col < s.ld1) {
+          *reinterpret_cast<float4*>(Pg + e0 + col) = make_float4(w8[4 * i4], w8[4 * i4 + 1], w8[4 * i4 + 2], w8[4 * i4 + 3]);
+          *reinterpret_cast<float4*>(Mg + e0 + col) = make_float4(m8[4 * i4], m8[4 * i4 + 1], m8[4 * i4 + 2], m8[4 * i4 + 3]);
+          if (use_v) *reinterpret_cast<float4*>(Vg + e0 + col) = make_float4(v8[4 * i4], v8[4 * i4 + 1], v8[4 * i4 + 2], v8[4 * i4 + 3]);
+        }
+      }
+    }
+    if (part == 0) {
+      float s3[8];
+      tc::tmem_ld8(tl + TF_S3, s3);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        if (mine && k < s.C) {
+          const int e = s.w_off2 + k * s.ld2 + s.J0 + j;
+          Pg[e] = s3[k]; Mg[e] = s3[2 + k];
+          if (use_v) Vg[e] = s3[4 + k];
+        }
+    }
+  }
   if (q == 0) {
     for (int t = tid; t < s.h1 * 16; t += FT) {
       const int i = t >> 4, col = t & 15;
@@ -728,7 +939,7 @@ extern "C" int fedb_fit_tcx(const FedbGroup* groups, int32_t n_groups, float* pa
                             const int32_t* y, const int32_t* idx_in, int32_t* idx_epoch, int32_t* step, int32_t* active,
                             const FedbFedState* fed_state, int32_t* epoch, int32_t* no_improve, double* best_loss, double* last_loss,
                             float* loss_out, double tol, int32_t n_iter_no_change, int32_t max_iter, int32_t max_epochs,
-                            int32_t shuffle, uint64_t seed, void* stream) {
+                            int32_t shuffle, uint64_t seed, long long* prof, void* stream) {
   FEDB_REQUIRE(n_groups > 0 && max_epochs >= 0, "bad sizes");
   FEDB_REQUIRE(ldx >= 16 && ldx % 4 == 0, "feature rows must be padded to >= 16 floats");
   FEDB_REQUIRE(m != nullptr && v != nullptr, "moment arenas required");
@@ -737,6 +948,7 @@ extern "C" int fedb_fit_tcx(const FedbGroup* groups, int32_t n_groups, float* pa
   a.step = step; a.active = active; a.fed_state = fed_state; a.epoch = epoch; a.no_improve = no_improve; a.best_loss = best_loss;
   a.last_loss = last_loss; a.loss_out = loss_out; a.tol = tol; a.ldx = ldx; a.n_iter_no_change = n_iter_no_change;
   a.max_iter = max_iter; a.max_epochs = max_epochs; a.shuffle = shuffle; a.s0 = (uint32_t)seed; a.s1 = (uint32_t)(seed >> 32);
+  a.prof = prof;
   const int smem = FX_END + 1024;
   FEDB_CUDA_OK(cudaFuncSetAttribute((const void*)k_fit_tcx, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   cudaLaunchConfig_t cfg{};

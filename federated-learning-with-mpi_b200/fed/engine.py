@@ -48,6 +48,8 @@ class FedEngine:
             nat.lib(required=True)  # fail loudly rather than run a fallback on a GPU box
         self.max_rounds = int(max_rounds)
         self.seed = int(seed)
+        # FEDB200_FIT=launches | cluster pins the sklearn-style fit of THIS engine to the CUDA-core kernels (read once, here)
+        self._fit_mode = os.environ.get("FEDB200_FIT", "")
         self.n_train = len(X_train)
         self.n_test = 0 if X_test is None else len(X_test)
         nf = X_train.shape[1]
@@ -482,7 +484,7 @@ class FedEngine:
     def _fit_tc_mask(self) -> Optional[np.ndarray]:
         """bool per client: trained by the tensor-core fit kernel.  None: not on this engine (CPU, MT19937 parity stream,
         FEDB200_FIT=launches | cluster forces the CUDA-core paths)."""
-        if self.device.type != "cuda" or self._uses_shuffle_table() or os.environ.get("FEDB200_FIT") in ("launches", "cluster"):
+        if self.device.type != "cuda" or self._uses_shuffle_table() or self._fit_mode in ("launches", "cluster"):
             return None
         if getattr(self, "_tc_fit_mask", None) is None:
             self._tc_fit_mask = K.fitx_eligible(self.tb.groups)
@@ -496,7 +498,7 @@ class FedEngine:
         client's 7, and short graph nodes cost less than the three cluster barriers per mini-batch."""
         if self.device.type != "cuda" or self.tb.smem_bytes <= 0 or self._uses_shuffle_table():
             return False
-        return os.environ.get("FEDB200_FIT", "launches") == "cluster"
+        return self._fit_mode == "cluster"
 
     def fit_local(self, max_iter: Optional[int] = None, shuffle: bool = True, check_every: int = 8) -> np.ndarray:
         """Train every client until its loss stalls (SK:750-777) or ``max_iter`` epochs.
@@ -505,7 +507,9 @@ class FedEngine:
         tc_mask = self._fit_tc_mask()
         if tc_mask is not None and bool(tc_mask.any()):
             # K2b on the tensor cores (csrc/fedb_fitx.cu): the whole fit of every eligible client in ONE launch, epoch loop and
-            # stopping rule on the device; clients of other shapes follow on the CUDA-core kernels below
+            # stopping rule on the device; clients of other shapes follow on the CUDA-core kernels below.  (Measured on the
+            # 90-federation grid: putting the one launch on a second stream next to the CUDA-core epochs changes the total by
+            # under 1 % - the 576 CTAs hold every SM while they run - so the two parts simply follow each other.)
             h = self.problems[0].hyper
             act_tc = torch.from_numpy(tc_mask.astype(np.int32)).to(self.device)
             K.fit_tcx(self.tb, self.params, self.m, self.v, self.X, self.y, self.idx, self.idx_epoch, self.step, act_tc, self.fed_state,
@@ -515,6 +519,12 @@ class FedEngine:
                 self.active.fill_(1)
                 return self.epoch.cpu().numpy().copy()
             self.active.copy_(1 - act_tc)
+        self._fit_cuda_cores(max_iter, shuffle, check_every)
+        self.active.fill_(1)
+        return self.epoch.cpu().numpy().copy()
+
+    def _fit_cuda_cores(self, max_iter: int, shuffle: bool, check_every: int) -> None:
+        """The fit of the clients whose ``active`` flag is set, on the fp32 CUDA-core kernels."""
         if self._fit_in_one_launch():
             # K2b, persistent form: epochs, mini-batches and the stopping rule all run on the device (fedb_fit_cluster)
             h = self.problems[0].hyper
@@ -523,9 +533,7 @@ class FedEngine:
                           self.scratch, self.step, self.active, self.fed_state, self.epoch, self.no_improve, self.best_loss,
                           self.last_loss, self.loss, self.batch_stats, self.n_batches, h.tol, h.n_iter_no_change, h.max_iter,
                           max_iter, shuffle, self.seed + 0x5EED)
-            n_iter = self.epoch.cpu().numpy().copy()
-            self.active.fill_(1)
-            return n_iter
+            return
         use_graph = self.device.type == "cuda"
         if use_graph and "epochx1" not in self._graphs:
             snap = self._snapshot()
@@ -542,8 +550,6 @@ class FedEngine:
             it += n
             if not bool(self.active.any()):
                 break
-        self.active.fill_(1)
-        return self.epoch.cpu().numpy().copy()
 
     # ----------------------------------------------------------------------------- results
     def history(self) -> Dict[str, np.ndarray]:

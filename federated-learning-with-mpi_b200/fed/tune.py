@@ -84,7 +84,11 @@ def run_grid(data, n_clients: int = 4, hidden_grid=HIDDEN_GRID, lr_grid=LR_GRID,
             t1.record()
             torch.cuda.synchronize()
             timing["device_ms"] = timing.get("device_ms", 0.0) + t0.elapsed_time(t1)
-            timing["epochs"] = timing.get("epochs", 0) + int(n_iter.max())
+            tcm = eng._fit_tc_mask()                                   # clients fitted by the one tensor-core launch
+            cc = n_iter[~tcm] if tcm is not None else n_iter
+            timing["epochs"] = timing.get("epochs", 0) + (int(cc.max()) if len(cc) else 0)
+            timing["tc_clients"] = int(tcm.sum()) if tcm is not None else 0
+            timing["clients"] = int(len(n_iter))
             timing["launches_per_epoch"] = 1 + eng.n_batches * 2 + 1      # shuffle, (fwd_bwd + reduce_opt) per mini-batch, epoch_end
         eng.check_errors()
         h = eng.history()

@@ -247,7 +247,7 @@ OPTIONAL_SIGS = {
     "fedb_round_tcx_p2p_many": ([_P, _I32, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P, _P], _I32),
     "fedb_fitx_smem_bytes": ([], _I64),
     "fedb_fitx_fits": ([_I32, _I32, _I32, _I32], _I32),
-    "fedb_fit_tcx": ([_P, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _F64, _I32, _I32, _I32, _I32, _U64, _P], _I32),
+    "fedb_fit_tcx": ([_P, _I32, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _F64, _I32, _I32, _I32, _I32, _U64, _P, _P], _I32),
     "fedb_noalloc_scratch_floats": ([], _I64),
     "fedb_wide_gather_x": ([_P, _I32, _P, _I32, _P, _P, _I32, _I32, _P], _I32),
     "fedb_wide_shadow": ([_P, _P, _I64, _P], _I32),

@@ -216,11 +216,11 @@ def fitx_eligible(groups: np.ndarray) -> np.ndarray:
 
 
 def fit_tcx(tb: DeviceTables, params, m, v, X, y, idx_in, idx_epoch, step, active, fed_state, epoch, no_improve, best_loss, last_loss,
-            loss_out, tol: float, n_iter_no_change: int, max_iter: int, max_epochs: int, shuffle: bool, seed: int) -> None:
+            loss_out, tol: float, n_iter_no_change: int, max_iter: int, max_epochs: int, shuffle: bool, seed: int, prof=None) -> None:
     """The whole local fit of every active client in one launch on the tensor cores (fedb_fit_tcx)."""
     nat.check(_L().fedb_fit_tcx(nat.ptr(tb.d_groups), tb.n_groups, nat.ptr(params), nat.ptr(m), nat.ptr(v), nat.ptr(X), X.shape[1],
                                 nat.ptr(y), nat.ptr(idx_in), nat.ptr(idx_epoch), nat.ptr(step), nat.ptr(active), nat.ptr(fed_state),
                                 nat.ptr(epoch), nat.ptr(no_improve), nat.ptr(best_loss), nat.ptr(last_loss), nat.ptr(loss_out),
                                 float(tol), int(n_iter_no_change), int(max_iter), int(max_epochs), int(bool(shuffle)),
-                                seed & (2 ** 64 - 1), nat.cuda_stream()))
+                                seed & (2 ** 64 - 1), nat.ptr(prof), nat.cuda_stream()))
     _count()

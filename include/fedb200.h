@@ -328,6 +328,19 @@ int fedb_round_tcx_p2p_many(const FedbGroup* groups, int32_t n_groups, int32_t c
                             float* scratch, int32_t n_steps, const FedbP2PRank* rank_dev, uint32_t* tail_count,
                             FedbFedState* state_mirror, void* stream);
 
+/* K2b on the tensor cores: the sklearn-style local fit (fedb_fit_cluster's contract: mini-batch Adam / SGD with the L2 term,
+ * loss curve, tol / n_iter_no_change rule, per-epoch reshuffle, up to max_epochs further epochs) of every client in ONE
+ * launch, epoch loop on the device.  A cluster of 4 CTAs per client splits hidden layer 2 (tcgen05 on split fp16 operands,
+ * fp32 accumulators in tensor memory).  fedb_fitx_fits: 2 hidden ReLU layers, in <= 15, h1 <= 63, h2 <= 512, out <= 8.
+ * prof (optional, device): per-CTA globaltimer stamps for tools/fitx_timeline.py; pass NULL otherwise. */
+int64_t fedb_fitx_smem_bytes(void);
+int32_t fedb_fitx_fits(int32_t d0, int32_t h1, int32_t h2, int32_t n_out);
+int fedb_fit_tcx(const FedbGroup* groups, int32_t n_groups, float* params, float* m, float* v, const float* X, int32_t ldx,
+                 const int32_t* y, const int32_t* idx_in, int32_t* idx_epoch, int32_t* step, int32_t* active,
+                 const FedbFedState* fed_state, int32_t* epoch, int32_t* no_improve, double* best_loss, double* last_loss,
+                 float* loss_out, double tol, int32_t n_iter_no_change, int32_t max_iter, int32_t max_epochs, int32_t shuffle,
+                 uint64_t seed, long long* prof, void* stream);
+
 /* K2d: grouped tcgen05 GEMM with fused epilogues (forward bias+ReLU, dgrad ReLU mask, weight gradient
  * + optimizer); args_host is read on the host.  M % 128 == 0, N % 16 == 0, K % 16 == 0. */
 int32_t fedb_gemm_args_size(void);
