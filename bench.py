@@ -405,10 +405,10 @@ def run_ours_modes(args):
             eng.init_params()
 
             def e2e():
-                for _ in range(K):
+                for r in range(K):      # the same K warm-started rounds as above, one public call per round
                     eng.X.copy_(xh, non_blocking=True)
                     eng.y.copy_(yh, non_blocking=True)
-                    run_sklearn_rounds(eng, 1, "warm_start")
+                    run_sklearn_rounds(eng, 1, "warm_start", fresh=(r == 0))
                     eng.fed_state_host()
             ms_e2e, _ = timed(e2e)
         epochs = int(np.asarray(h["n_iter"]).max(axis=1).sum())

@@ -30,12 +30,14 @@ POLICIES = ("warm_start", "reference_faithful", "sklearn_literal")
 
 
 def run_sklearn_rounds(engine: FedEngine, rounds: int = 5, policy: str = "warm_start", log: Optional[flog.RunLog] = None,
-                       shuffle: bool = True) -> Dict:
+                       shuffle: bool = True, fresh: bool = True) -> Dict:
+    """``fresh=False`` continues a run this engine already started (round 1 of this call starts from the state the previous
+    call left: the averaged weights under warm_start) instead of re-initialising."""
     if policy not in POLICIES:
         raise ValueError(f"policy must be one of {POLICIES}")
     n_iter_hist: List[np.ndarray] = []
     for r in range(rounds):
-        if policy == "reference_faithful" or r == 0:
+        if policy == "reference_faithful" or (r == 0 and fresh):
             engine.init_params()
         engine.reset_fit_state(keep_no_improvement=(policy == "sklearn_literal" and r > 0))
         if engine._begin_is_fused():

@@ -8,7 +8,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "federated-learning-with-mpi_b200", "_lib", "libfedb200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
 # file stem -> substring of the mangled kernel name (template arguments spelled as nvcc mangles them)
-KERNELS = [("tcx_round", "k_round_tcx"), ("tc_local_round", "k_local_round_tc"), ("gemm_pair", "k_gemm_tma2ILb0"), ("gemm_pair_opt", "k_gemm_tma2ILb1"),
+KERNELS = [("tcx_round", "k_round_tcx"), ("tcx_fit", "k_fit_tcx"), ("tc_local_round", "k_local_round_tc"), ("gemm_pair", "k_gemm_tma2ILb0"), ("gemm_pair_opt", "k_gemm_tma2ILb1"),
            ("gemm_pair_persistent", "k_gemm_tma2pILb0"), ("gemm_pair_persistent_opt", "k_gemm_tma2pILb1"), ("gemm_tma", "k_gemm_tmaE"),
            ("gemm_cpasync", "k_gemm_tcE"), ("fedavg_p2p", "k_fedavg_p2p"), ("simt_fwd_bwd", "k_fwd_bwd"), ("simt_reduce_opt", "k_reduce_opt"),
            ("simt_fit_cluster", "k_fit_cluster"), ("simt_eval", "k_evalE"), ("simt_fedavg", "k_fedavgE"), ("wide_head_bwd", "k_wide_head_bwd"),
