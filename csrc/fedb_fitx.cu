@@ -189,12 +189,16 @@ struct IssuerF {
   }
   __device__ __forceinline__ void dgrad2_wgrad2(int N2, bool acc) const {
     const uint32_t id4 = idesc_f16(128, 64, false, true);   // partial dH1 = dZ2_slice W2_slice
-#pragma unroll 1
-    for (int c = 0; c < (N2 >> 4); ++c) {
-      const int p = c >> 2, k = c & 3, wrow = c * 16 * 128;
-      tc::mma_bf16(tmem + TF_D1, kd(FX_Z + (2 + p) * FP + 32 * k), md(FX_W2 + wrow), id4, c > 0);
-      tc::mma_bf16(tmem + TF_D1, kd(FX_Z + p * FP + 32 * k), md(FX_W2L + wrow), id4, true);
-      tc::mma_bf16(tmem + TF_D1, kd(FX_Z + p * FP + 32 * k), md(FX_W2 + wrow), id4, true);
+    // (fully unrolled under a uniform predicate: every descriptor is a compile-time constant; as run-time values each costs
+    //  the single issuing thread a move into the uniform registers, ~25 cycles per MMA)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c < (N2 >> 4)) {
+        const int p = c >> 2, k = c & 3, wrow = c * 16 * 128;
+        tc::mma_bf16(tmem + TF_D1, kd(FX_Z + (2 + p) * FP + 32 * k), md(FX_W2 + wrow), id4, c > 0);
+        tc::mma_bf16(tmem + TF_D1, kd(FX_Z + p * FP + 32 * k), md(FX_W2L + wrow), id4, true);
+        tc::mma_bf16(tmem + TF_D1, kd(FX_Z + p * FP + 32 * k), md(FX_W2 + wrow), id4, true);
+      }
     }
     const uint32_t id5 = idesc_f16(128, 64, true, true);    // dW2_slice += dZ2_slice^T H1
 #pragma unroll
@@ -382,7 +386,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
 #define FSTAMP(i) do { if (a.prof && g == 0 && tid == 0 && ep == 0 && b == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); a.prof[q * 32 + (i)] = t_; } } while (0)
 #define FIT_MMA_PHASE(ISSUE)             \
   do {                                   \
-    if (tid == 0) {                      \
+    if (warp == 0 && tc::elect_one()) {      \
       tc::tc_fence_after();              \
       ISSUE;                             \
       tc::mma_commit(&bar);              \
@@ -446,6 +450,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
       const int ntiles = (nb + FR - 1) / FR;
       const float inv_n = 1.f / (float)nb, gscale = inv_n * (1.f / DZS);
       t_step += 1;
+      if (tid == 0) sc_s = step_scalars_fast(G, t_step);   // (read after the block barrier that follows the tiles)
       float loss_acc = 0.f, db3_acc[FEDB_MAX_CLASSES];
 #pragma unroll
       for (int k = 0; k < FEDB_MAX_CLASSES; ++k) db3_acc[k] = 0.f;
@@ -647,6 +652,9 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
         }
         handoff_f();
         if (tile == 0) FSTAMP(11);
+        // (measured: a second X panel, so that these MMAs go out with the next tile's first group and its rows are staged here,
+        //  saves a wait per tile but makes every descriptor that names an X panel a run-time value; the single issuing thread
+        //  then spends ~25 cycles more per MMA moving them to uniform registers: 18.2 against 17.2 us for the two tiles)
         FIT_MMA_PHASE(mma.wgrad1(acc));
         if (tile == 0) FSTAMP(12);
       }  // tiles
@@ -684,7 +692,6 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
         }
       }
       if (tid == 0) {
-        sc_s = step_scalars_fast(G, t_step);
         const float t = s_ss_slice;   // my slice's ||W||^2 before this step's update (kept from the previous update)
 #pragma unroll
         for (int rk = 0; rk < FNC; ++rk) st_cluster_f1(mapa(sm_u + FX_G1 + (uint32_t)(q * G1_FLOATS + 64 * 16) * 4u, rk), t);

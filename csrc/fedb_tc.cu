@@ -400,7 +400,7 @@ __device__ __forceinline__ void local_round_body(const TcArgs& a, uint8_t* smem_
 
 #define FEDB_MMA_PHASE(ISSUE)            \
   do {                                   \
-    if (tid == 0) {                      \
+    if (warp == 0 && tc::elect_one()) {  \
       tc::tc_fence_after();              \
       ISSUE;                             \
       tc::mma_commit(&bar);              \

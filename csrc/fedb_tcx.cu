@@ -406,7 +406,7 @@ __device__ __forceinline__ bool round_body_x(const TcArgs& a, uint8_t* smem_raw,
 
 #define FEDB_MMA_PHASE(ISSUE)            \
   do {                                   \
-    if (tid == 0) {                      \
+    if (warp == 0 && tc::elect_one()) {  \
       tc::tc_fence_after();              \
       ISSUE;                             \
       tc::mma_commit(&bar);              \

@@ -47,6 +47,14 @@ __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64
 }
 
 // Arrive on an mbarrier when all previously issued tcgen05.mma of this thread have completed.
+// One lane of a converged warp (elect.sync): the MMA-issuing thread.  Guarding the issue with this instead of `tid == 0`
+// tells the compiler that exactly one lane runs it; under a plain divergent branch it wraps EVERY tcgen05.mma in a loop
+// over the active lanes (ELECT / UTCHMMA / BRA.U.ANY).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(p));
+  return p != 0;
+}
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
