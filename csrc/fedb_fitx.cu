@@ -653,8 +653,8 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
         handoff_f();
         if (tile == 0) FSTAMP(11);
         // (measured: a second X panel, so that these MMAs go out with the next tile's first group and its rows are staged here,
-        //  saves a wait per tile but makes every descriptor that names an X panel a run-time value; the single issuing thread
-        //  then spends ~25 cycles more per MMA moving them to uniform registers: 18.2 against 17.2 us for the two tiles)
+        //  saves a wait per tile, but staging the next tile here and the longer first MMA group cost more than that:
+        //  16.5 against 16.0 us for the two tiles)
         FIT_MMA_PHASE(mma.wgrad1(acc));
         if (tile == 0) FSTAMP(12);
       }  // tiles

@@ -75,8 +75,9 @@ __global__ void __launch_bounds__(T_THREADS) k_gemm_tma(const __grid_constant__ 
   if (p.epilogue == FEDB_GEMM_WGRAD_OPT && tid == 64) sc_s = step_scalars_fast(Gs, p.step[g]);
 
   if (warp == 0) {
-    // ===== TMA producer (one lane) =====
-    if (lane == 0) {
+    // ===== TMA producer (one lane, elected: see fedb_gemm_tma2.cu) =====
+    __syncwarp();
+    if (tc::elect_one()) {
       for (int kt = 0; kt < KT; ++kt) {
         const int s = kt % STAGES, k0 = kt * BK;
         if (kt >= STAGES) tc::mbar_wait(&empty_bar[s], ((kt / STAGES) - 1) & 1);
@@ -89,8 +90,9 @@ __global__ void __launch_bounds__(T_THREADS) k_gemm_tma(const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one lane) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one lane, elected) =====
+    __syncwarp();
+    if (tc::elect_one()) {
       const uint32_t idesc = tc::make_idesc_bf16(BM, n_cnt, p.a_mn != 0, p.b_mn != 0);
       for (int kt = 0; kt < KT; ++kt) {
         const int s = kt % STAGES;

@@ -128,7 +128,10 @@ k_gemm_tma2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ===== TMA producer (one lane per CTA): own A rows + own half of B; completion on the LEADER's full barrier =====
-    if (lane == 0) {
+    // (elected with elect.sync, not `lane == 0`: under a plain divergent branch the compiler wraps every UTMALDG / UTCHMMA in
+    //  a loop over the active lanes)
+    __syncwarp();
+    if (tc::elect_one()) {
       for (int kt = 0; kt < KT && ok; ++kt) {
         const int s = kt % STAGES, k0 = kt * BK;
         if (kt >= STAGES) ok = mbar_wait_to(&empty_bar[s], ((kt / STAGES) - 1) & 1);
@@ -144,7 +147,8 @@ k_gemm_tma2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1 && rank == 0) {
     // ===== MMA issuer: one lane of the leader CTA drives both SMs' tensor cores =====
-    if (lane == 0) {
+    __syncwarp();
+    if (tc::elect_one()) {
       const uint32_t idesc = tc::make_idesc_bf16(2 * BM, BN, p.a_mn != 0, p.b_mn != 0);
       for (int kt = 0; kt < KT && ok; ++kt) {
         const int s = kt % STAGES;

@@ -90,7 +90,10 @@ k_gemm_tma2p(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                                            // a static trip count, so the kernel always terminates
   if (warp == 0) {
     // ===== TMA producer (one lane per CTA): own A rows + own half of B; completion on the LEADER's full barrier =====
-    if (lane == 0) {
+    // (elected with elect.sync, not `lane == 0`: under a plain divergent branch the compiler wraps every UTMALDG / UTCHMMA in
+    //  a loop over the active lanes)
+    __syncwarp();
+    if (tc::elect_one()) {
       int it = 0;
       for (int t = cid; t < n_tiles; t += n_clusters) {
         const TileCoord c = tile_coord(t, tiles_m, tiles_n, rank);
@@ -111,7 +114,8 @@ k_gemm_tma2p(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
   } else if (warp == 1) {
     // ===== MMA issuer: one lane of the leader CTA drives both SMs' tensor cores, two accumulators in turn =====
-    if (rank == 0 && lane == 0) {
+    __syncwarp();
+    if (rank == 0 && tc::elect_one()) {
       const uint32_t idesc = tc::make_idesc_bf16(2 * BM, BN, p.a_mn != 0, p.b_mn != 0);
       int it = 0, tc_n = 0;
       for (int t = cid; t < n_tiles; t += n_clusters, ++tc_n) {
