@@ -118,9 +118,53 @@ __device__ void layer_forward(const float* __restrict__ W, const float* __restri
 }
 
 // dW[j][k] = sum_r dz[j][r] a[k][r]  (tile partial), db[j] = sum_r dz[j][r]
+// Wide inputs (ld >= 160; measured: it loses on ld = 100, where a layer has 50 such tasks for 16 warps): a WARP takes 8
+// outputs x 128 inputs, lane l the inputs l, l + 32, l + 64, l + 96 of the group, so the
+// activation loads of a warp hit 32 different banks (the 4-consecutive-inputs-per-thread mapping below puts them on 8: a
+// 4-way conflict on the loads that feed two thirds of the FMAs) and the dz loads are broadcasts; 12 shared-memory wavefronts
+// per 32 FMA instructions instead of 20 per 16.  Each dW element still adds its rows in order: bit-identical.
+__device__ void layer_wgrad_wide(const float* dz, const float* a, int d_in_ld, int d_out, float* __restrict__ gW) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int njb = (d_out + 7) >> 3, nkg = (d_in_ld + 127) >> 7;
+  for (int task = warp; task < njb * nkg; task += nwarps) {
+    const int jb = task / nkg, kg = task - jb * nkg;
+    const int j0 = jb * 8, kbase = kg * 128 + lane;
+    const float* dp[8];
+    const float* xp[4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dp[i] = dz + min(j0 + i, d_out - 1) * LDS;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) xp[c] = a + min(kbase + 32 * c, d_in_ld - 1) * LDS;
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+#pragma unroll 2
+    for (int r = 0; r < FEDB_TILE_ROWS; ++r) {
+      float x[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) x[c] = xp[c][r];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = dp[i][r];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[i][c] = fmaf(d, x[c], acc[i][c]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (j0 + i < d_out) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (kbase + 32 * c < d_in_ld) gW[(size_t)(j0 + i) * d_in_ld + kbase + 32 * c] = acc[i][c];
+      }
+  }
+}
+
 __device__ void layer_wgrad(const float* dz, const float* a, int d_in_ld, int d_out, float* __restrict__ gW,
                             float* __restrict__ gb) {
   const int njb = (d_out + 3) >> 2, nkb = d_in_ld >> 2;
+  if (d_in_ld >= 160) layer_wgrad_wide(dz, a, d_in_ld, d_out, gW);
+  else
   for (int blk = threadIdx.x; blk < njb * nkb; blk += blockDim.x) {
     const int jb = blk / nkb, kb = blk - jb * nkb;
     const int j0 = jb * 4, k0 = kb * 4;
@@ -181,6 +225,109 @@ __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d
       const int k = k0 + kk;
       const float av = a_l[k * LDS + lane];
       dz_prev[k * LDS + lane] = (k < d_in) ? acc[kk] * act_bwd(av, act) : 0.f;
+    }
+  }
+}
+
+// ---- models whose weights do not fit next to the activations --------------------------------------------------------------
+// Reading such a layer's weights straight from global memory makes every warp wait an L2 round trip per float4 (the
+// activations' carve-out leaves L1 too small to hold a 160-320 KB matrix): the (400, 200) / (200, 400) / (100, 400) corners of
+// the grid ran 5-10x slower per FLOP than the shapes that fit.  Instead the CTA streams the matrix through whatever shared
+// memory is left (launches ask for the full 227 KB): a block of consecutive rows is copied with every thread's loads in flight
+// (coalesced, one L2 round trip per block), the layer loops read it at shared-memory latency, next block.  The order in which
+// each output accumulates its terms is the one of the plain loops, so the results are bit-identical.
+template <int WS>
+__device__ __forceinline__ void stage_rows(const float* __restrict__ W, int n_floats, float* wbuf) {
+  for (int i = threadIdx.x * 4; i < n_floats; i += blockDim.x * 4) *reinterpret_cast<float4*>(wbuf + i) = ldw4<WS>(W + i);
+}
+
+template <int WS>
+__device__ void layer_forward_chunked(const float* __restrict__ W, const float* __restrict__ b, int ld, int d_out, const float* a_in,
+                                      float* a_out, int act, bool apply_act, float* wbuf, int rpc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  constexpr int JT = 8;                                // outputs per warp task: 4 activation + 8 weight loads per 32 FMAs
+  for (int j0 = 0; j0 < d_out; j0 += rpc) {            // rpc: rows per block, a multiple of 8
+    const int nr = min(rpc, d_out - j0);
+    stage_rows<WS>(W + (size_t)j0 * ld, nr * ld, wbuf);
+    __syncthreads();
+    const int njb = (nr + JT - 1) / JT;
+    for (int jb = warp; jb < njb; jb += nwarps) {
+      const int jl0 = jb * JT;
+      const float* w[JT];
+      float acc[JT];
+#pragma unroll
+      for (int jj = 0; jj < JT; ++jj) {
+        const int jl = min(jl0 + jj, nr - 1);
+        w[jj] = wbuf + jl * ld;
+        acc[jj] = ldw1<WS>(b + j0 + jl);
+      }
+#pragma unroll 2
+      for (int k = 0; k < ld; k += 4) {
+        const float a0 = a_in[(k + 0) * LDS + lane], a1 = a_in[(k + 1) * LDS + lane];
+        const float a2 = a_in[(k + 2) * LDS + lane], a3 = a_in[(k + 3) * LDS + lane];
+#pragma unroll
+        for (int jj = 0; jj < JT; ++jj) {
+          const float4 q = *reinterpret_cast<const float4*>(w[jj] + k);
+          acc[jj] = fmaf(a0, q.x, acc[jj]);
+          acc[jj] = fmaf(a1, q.y, acc[jj]);
+          acc[jj] = fmaf(a2, q.z, acc[jj]);
+          acc[jj] = fmaf(a3, q.w, acc[jj]);
+        }
+      }
+#pragma unroll
+      for (int jj = 0; jj < JT; ++jj) {
+        const int j = j0 + jl0 + jj;             // (the last block also writes the zero rows up to ru4(d_out))
+        if (j < ru4(d_out)) {
+          float v = 0.f;
+          if (j < d_out) v = apply_act ? act_fwd(acc[jj], act) : acc[jj];
+          a_out[j * LDS + lane] = v;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+constexpr int DGRAD_TMAX = 8;   // column blocks of 4 a warp keeps accumulators for: ld <= 4 * 8 * (warps per CTA)
+template <int WS>
+__device__ void layer_dgrad_chunked(const float* __restrict__ W, int ld, int d_in, int d_out, const float* dz, const float* a_l,
+                                    float* dz_prev, int act, float* wbuf, int rpc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int nkb = ld >> 2;
+  float acc[DGRAD_TMAX][4];
+#pragma unroll
+  for (int t = 0; t < DGRAD_TMAX; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+  for (int j0 = 0; j0 < d_out; j0 += rpc) {
+    const int nr = min(rpc, d_out - j0);
+    stage_rows<WS>(W + (size_t)j0 * ld, nr * ld, wbuf);
+    __syncthreads();
+#pragma unroll 2
+    for (int j = 0; j < nr; ++j) {
+      const float d = dz[(j0 + j) * LDS + lane];
+      const float* wr = wbuf + j * ld + 4 * warp;
+#pragma unroll
+      for (int t = 0; t < DGRAD_TMAX; ++t) {
+        if (warp + t * nwarps < nkb) {           // warp-uniform
+          const float4 q = *reinterpret_cast<const float4*>(wr + 4 * t * nwarps);
+          acc[t][0] = fmaf(d, q.x, acc[t][0]);
+          acc[t][1] = fmaf(d, q.y, acc[t][1]);
+          acc[t][2] = fmaf(d, q.z, acc[t][2]);
+          acc[t][3] = fmaf(d, q.w, acc[t][3]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int t = 0; t < DGRAD_TMAX; ++t) {
+    const int kb = warp + t * nwarps;
+    if (kb < nkb) {
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const int k = kb * 4 + kk;
+        const float av = a_l[k * LDS + lane];
+        dz_prev[k * LDS + lane] = (k < d_in) ? acc[t][kk] * act_bwd(av, act) : 0.f;
+      }
     }
   }
 }
@@ -314,6 +461,8 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
   const SlabLayout lay = slab_layout(G.dims, L);
   const SmemPlan sp = smem_plan(G.dims, L);
   const bool ws = sp.total_floats + lay.end <= smem_floats;  // weights fit next to the activations
+  const int spare = smem_floats - sp.total_floats;           // otherwise: what is left streams the matrices block by block
+  float* wbuf = smem + sp.total_floats;
   const float* P = params + G.slab_off;
   float* rec = scratch + G.scratch_off + (size_t)tile * (G.slab_size + FEDB_LOSS_SLOTS);
   int* ylab = reinterpret_cast<int*>(smem + sp.misc_off);
@@ -329,8 +478,11 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
   __syncthreads();
 
   for (int l = 0; l < L; ++l) {
+    const int rpc = (spare / lay.ld[l]) & ~7;      // rows of this layer's matrix that fit in the shared memory left over
     if (ws) layer_forward<1>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                                 smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    else if (rpc >= 16) layer_forward_chunked<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                                                           smem + sp.a_off[l + 1], G.act, l + 1 < L, wbuf, rpc);
     else layer_forward<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                               smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
@@ -377,8 +529,12 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
     const float* dzc = smem + sp.dz_off[cur];
     layer_wgrad(dzc, smem + sp.a_off[l], lay.ld[l], G.dims[l + 1], rec + lay.w_off[l], rec + lay.b_off[l]);
     if (l > 0) {
+      const int rpc = spare / lay.ld[l];
       if (ws) layer_dgrad<1>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                                 smem + sp.dz_off[cur ^ 1], G.act);
+      else if (rpc >= 16 && (lay.ld[l] >> 2) <= DGRAD_TMAX * (int)(blockDim.x >> 5))
+        layer_dgrad_chunked<COH ? 2 : 0>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
+                                         smem + sp.dz_off[cur ^ 1], G.act, wbuf, rpc);
       else layer_dgrad<COH ? 2 : 0>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                               smem + sp.dz_off[cur ^ 1], G.act);
     }
@@ -630,8 +786,11 @@ k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ job
   load_tile(X, ldx, y, idx, J.idx_off + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
   __syncthreads();
   for (int l = 0; l < L; ++l) {
+    const int rpc = ((smem_floats - sp.total_floats) / lay.ld[l]) & ~7;
     if (ws) layer_forward<true>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                                 smem + sp.a_off[l + 1], G.act, l + 1 < L);
+    else if (rpc >= 16) layer_forward_chunked<0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                                                 smem + sp.a_off[l + 1], G.act, l + 1 < L, smem + sp.total_floats, rpc);
     else layer_forward<false>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                               smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
@@ -762,7 +921,7 @@ extern "C" int64_t fedb_simt_smem_bytes(const int32_t* dims, int32_t n_layers) {
   const int64_t bytes = (int64_t)sp.total_floats * 4, with_w = bytes + (int64_t)lay.end * 4;
   const int64_t cap = 227 * 1024 - 64;     // the kernels' few static __shared__ variables count against the same limit
   if (with_w <= cap) return with_w;  // weights staged in shared memory
-  return bytes <= cap ? bytes : -1;
+  return bytes <= cap ? cap : -1;    // everything, so that the matrices can stream through what the activations leave
 }
 
 // Opt in to >48 KB of dynamic shared memory once per (device, function) — the attribute belongs to the device's context, so

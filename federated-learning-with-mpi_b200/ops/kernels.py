@@ -10,6 +10,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+import os
+
 import numpy as np
 import torch
 
@@ -83,7 +85,9 @@ def simt_smem_bytes(dims, n_layers: int) -> int:
     if b > cap:
         raise ValueError(f"MLP {d} needs {b} bytes of shared memory per CTA in the SIMT kernels (max {cap}); "
                          "use the wide (layer-wise tcgen05 GEMM) path")
-    return b
+    # weights that do not fit stream through whatever the activations leave (csrc/fedb_simt.cu, layer_*_chunked):
+    # ask for everything.  FEDB200_SIMT_STREAM=0 keeps the old behaviour (weights read from global memory in the layer loops).
+    return b if os.environ.get("FEDB200_SIMT_STREAM", "1") == "0" else cap
 
 
 def upload_table(arr: np.ndarray, device) -> torch.Tensor:
