@@ -289,11 +289,31 @@ __device__ void layer_forward_chunked(const float* __restrict__ W, const float* 
 }
 
 constexpr int DGRAD_TMAX = 8;   // column blocks of 4 a warp keeps accumulators for: ld <= 4 * 8 * (warps per CTA)
+// NT = how many column blocks THIS warp owns (kb = warp + t * nwarps < nkb), a compile-time constant so that the inner loop is
+// straight-line code: one dz load, NT broadcast float4 loads, 4 NT FMAs per weight row (with the test inside the loop the
+// kernel executed three instructions per FMA).
+template <int NT>
+__device__ __forceinline__ void dgrad_rows_nt(float (&acc)[DGRAD_TMAX][4], const float* dp, const float* wr, int nr, int ld, int tstride) {
+#pragma unroll 4
+  for (int j = 0; j < nr; ++j) {
+    const float d = dp[j * LDS];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const float4 q = *reinterpret_cast<const float4*>(wr + j * ld + t * tstride);
+      acc[t][0] = fmaf(d, q.x, acc[t][0]);
+      acc[t][1] = fmaf(d, q.y, acc[t][1]);
+      acc[t][2] = fmaf(d, q.z, acc[t][2]);
+      acc[t][3] = fmaf(d, q.w, acc[t][3]);
+    }
+  }
+}
+
 template <int WS>
 __device__ void layer_dgrad_chunked(const float* __restrict__ W, int ld, int d_in, int d_out, const float* dz, const float* a_l,
                                     float* dz_prev, int act, float* wbuf, int rpc) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int nkb = ld >> 2;
+  const int nt = nkb > warp ? (nkb - warp + nwarps - 1) / nwarps : 0;   // warp-uniform, <= DGRAD_TMAX
   float acc[DGRAD_TMAX][4];
 #pragma unroll
   for (int t = 0; t < DGRAD_TMAX; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
@@ -301,20 +321,18 @@ __device__ void layer_dgrad_chunked(const float* __restrict__ W, int ld, int d_i
     const int nr = min(rpc, d_out - j0);
     stage_rows<WS>(W + (size_t)j0 * ld, nr * ld, wbuf);
     __syncthreads();
-#pragma unroll 2
-    for (int j = 0; j < nr; ++j) {
-      const float d = dz[(j0 + j) * LDS + lane];
-      const float* wr = wbuf + j * ld + 4 * warp;
-#pragma unroll
-      for (int t = 0; t < DGRAD_TMAX; ++t) {
-        if (warp + t * nwarps < nkb) {           // warp-uniform
-          const float4 q = *reinterpret_cast<const float4*>(wr + 4 * t * nwarps);
-          acc[t][0] = fmaf(d, q.x, acc[t][0]);
-          acc[t][1] = fmaf(d, q.y, acc[t][1]);
-          acc[t][2] = fmaf(d, q.z, acc[t][2]);
-          acc[t][3] = fmaf(d, q.w, acc[t][3]);
-        }
-      }
+    const float* dp = dz + j0 * LDS + lane;
+    const float* wr = wbuf + 4 * warp;
+    switch (nt) {
+      case 0: break;
+      case 1: dgrad_rows_nt<1>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 2: dgrad_rows_nt<2>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 3: dgrad_rows_nt<3>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 4: dgrad_rows_nt<4>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 5: dgrad_rows_nt<5>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 6: dgrad_rows_nt<6>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      case 7: dgrad_rows_nt<7>(acc, dp, wr, nr, ld, 4 * nwarps); break;
+      default: dgrad_rows_nt<8>(acc, dp, wr, nr, ld, 4 * nwarps); break;
     }
     __syncthreads();
   }
