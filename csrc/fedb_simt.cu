@@ -236,56 +236,102 @@ __device__ void layer_dgrad(const float* __restrict__ W, int ld, int d_in, int d
 // memory is left (launches ask for the full 227 KB): a block of consecutive rows is copied with every thread's loads in flight
 // (coalesced, one L2 round trip per block), the layer loops read it at shared-memory latency, next block.  The order in which
 // each output accumulates its terms is the one of the plain loops, so the results are bit-identical.
-template <int WS>
-__device__ __forceinline__ void stage_rows(const float* __restrict__ W, int n_floats, float* wbuf) {
-  for (int i = threadIdx.x * 4; i < n_floats; i += blockDim.x * 4) *reinterpret_cast<float4*>(wbuf + i) = ldw4<WS>(W + i);
+// Asynchronous 16-byte copies global -> shared (through L2, so also right for weights other CTAs rewrote earlier in the
+// kernel): block i + 1 of a matrix is in flight while the warps work on block i.
+__device__ __forceinline__ void cp_async16(float* dst, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// rows [0, n_rows) x columns [k0, k0 + kc) of a row-major matrix -> dst[row * kc + col] (kc a multiple of 4)
+__device__ __forceinline__ void stage_cols_async(const float* __restrict__ W, int ld, int n_rows, int k0, int kc, float* dst) {
+  const int q = kc >> 2;
+  for (int e = threadIdx.x; e < n_rows * q; e += blockDim.x) {
+    const int row = e / q, c4 = e - row * q;
+    cp_async16(dst + row * kc + 4 * c4, W + (size_t)row * ld + k0 + 4 * c4);
+  }
+  cp_async_commit();
+}
+// n_floats consecutive floats (whole rows) -> dst
+__device__ __forceinline__ void stage_rows_async(const float* __restrict__ W, int n_floats, float* dst) {
+  for (int i = threadIdx.x * 4; i < n_floats; i += blockDim.x * 4) cp_async16(dst + i, W + i);
+  cp_async_commit();
+}
+
+// Forward with streamed weights: the matrix goes through shared memory in blocks of COLUMNS (all outputs x kc inputs), each
+// warp keeps the accumulators of its NT tasks of 8 outputs across the blocks (every warp has work in every block; blocks of
+// rows left 11 of 16 warps idle on a 200 x 400 layer), inputs in ascending order as in layer_forward: bit-identical.
+constexpr int FWD_TMAX = 4;   // tasks of 8 outputs per warp: d_out <= 8 * 4 * (warps per CTA)
+template <int NT>
+__device__ __forceinline__ void fwd_cols_nt(float (&acc)[FWD_TMAX][8], const float* a_in, const float* wb, int kc, int k0, int lane,
+                                            int task0, int tstride) {
+  // (the block holds ru8(d_out) rows: a last, partial task reads unstaged rows whose accumulators are never stored)
+  const float* a = a_in + k0 * LDS + lane;
+  const float* w0 = wb + task0 * 8 * kc;
+  const int ts = tstride * 8 * kc;
+#pragma unroll 2
+  for (int k = 0; k < kc; k += 4) {
+    const float a0 = a[(k + 0) * LDS], a1 = a[(k + 1) * LDS], a2 = a[(k + 2) * LDS], a3 = a[(k + 3) * LDS];
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) {
+        const float4 q = *reinterpret_cast<const float4*>(w0 + t * ts + jj * kc + k);
+        acc[t][jj] = fmaf(a0, q.x, acc[t][jj]);
+        acc[t][jj] = fmaf(a1, q.y, acc[t][jj]);
+        acc[t][jj] = fmaf(a2, q.z, acc[t][jj]);
+        acc[t][jj] = fmaf(a3, q.w, acc[t][jj]);
+      }
+  }
 }
 
 template <int WS>
 __device__ void layer_forward_chunked(const float* __restrict__ W, const float* __restrict__ b, int ld, int d_out, const float* a_in,
-                                      float* a_out, int act, bool apply_act, float* wbuf, int rpc) {
+                                      float* a_out, int act, bool apply_act, float* wbuf, int kc_max) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  constexpr int JT = 8;                                // outputs per warp task: 4 activation + 8 weight loads per 32 FMAs
-  for (int j0 = 0; j0 < d_out; j0 += rpc) {            // rpc: rows per block, a multiple of 8
-    const int nr = min(rpc, d_out - j0);
-    stage_rows<WS>(W + (size_t)j0 * ld, nr * ld, wbuf);
+  const int njb = (d_out + 7) >> 3;
+  const int nt = njb > warp ? (njb - warp + nwarps - 1) / nwarps : 0;   // warp-uniform, <= FWD_TMAX
+  float acc[FWD_TMAX][8];
+#pragma unroll
+  for (int t = 0; t < FWD_TMAX; ++t)
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) acc[t][jj] = ldw1<WS>(b + min((warp + t * nwarps) * 8 + jj, d_out - 1));
+  const int nblk = (ld + kc_max - 1) / kc_max;
+  float* const buf0 = wbuf;
+  float* const buf1 = wbuf + ((d_out + 7) & ~7) * kc_max;
+  stage_cols_async(W, ld, d_out, 0, min(kc_max, ld), buf0);
+  for (int c = 0; c < nblk; ++c) {
+    const int k0 = c * kc_max, kc = min(kc_max, ld - k0);
+    if (c + 1 < nblk) {
+      stage_cols_async(W, ld, d_out, k0 + kc_max, min(kc_max, ld - k0 - kc_max), (c & 1) ? buf0 : buf1);
+      cp_async_wait_but_one();
+    } else {
+      cp_async_wait_all();
+    }
     __syncthreads();
-    const int njb = (nr + JT - 1) / JT;
-    for (int jb = warp; jb < njb; jb += nwarps) {
-      const int jl0 = jb * JT;
-      const float* w[JT];
-      float acc[JT];
-#pragma unroll
-      for (int jj = 0; jj < JT; ++jj) {
-        const int jl = min(jl0 + jj, nr - 1);
-        w[jj] = wbuf + jl * ld;
-        acc[jj] = ldw1<WS>(b + j0 + jl);
-      }
-#pragma unroll 2
-      for (int k = 0; k < ld; k += 4) {
-        const float a0 = a_in[(k + 0) * LDS + lane], a1 = a_in[(k + 1) * LDS + lane];
-        const float a2 = a_in[(k + 2) * LDS + lane], a3 = a_in[(k + 3) * LDS + lane];
-#pragma unroll
-        for (int jj = 0; jj < JT; ++jj) {
-          const float4 q = *reinterpret_cast<const float4*>(w[jj] + k);
-          acc[jj] = fmaf(a0, q.x, acc[jj]);
-          acc[jj] = fmaf(a1, q.y, acc[jj]);
-          acc[jj] = fmaf(a2, q.z, acc[jj]);
-          acc[jj] = fmaf(a3, q.w, acc[jj]);
-        }
-      }
-#pragma unroll
-      for (int jj = 0; jj < JT; ++jj) {
-        const int j = j0 + jl0 + jj;             // (the last block also writes the zero rows up to ru4(d_out))
-        if (j < ru4(d_out)) {
-          float v = 0.f;
-          if (j < d_out) v = apply_act ? act_fwd(acc[jj], act) : acc[jj];
-          a_out[j * LDS + lane] = v;
-        }
-      }
+    const float* wb = (c & 1) ? buf1 : buf0;
+    switch (nt) {
+      case 0: break;
+      case 1: fwd_cols_nt<1>(acc, a_in, wb, kc, k0, lane, warp, nwarps); break;
+      case 2: fwd_cols_nt<2>(acc, a_in, wb, kc, k0, lane, warp, nwarps); break;
+      case 3: fwd_cols_nt<3>(acc, a_in, wb, kc, k0, lane, warp, nwarps); break;
+      default: fwd_cols_nt<4>(acc, a_in, wb, kc, k0, lane, warp, nwarps); break;
     }
     __syncthreads();
   }
+#pragma unroll
+  for (int t = 0; t < FWD_TMAX; ++t)
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) {
+      const int j = (warp + t * nwarps) * 8 + jj;
+      if (j < ru4(d_out)) {                      // (also the zero rows up to ru4(d_out): the next layer's K pad)
+        float v = 0.f;
+        if (j < d_out) v = apply_act ? act_fwd(acc[t][jj], act) : acc[t][jj];
+        a_out[j * LDS + lane] = v;
+      }
+    }
 }
 
 constexpr int DGRAD_TMAX = 8;   // column blocks of 4 a warp keeps accumulators for: ld <= 4 * 8 * (warps per CTA)
@@ -317,12 +363,21 @@ __device__ void layer_dgrad_chunked(const float* __restrict__ W, int ld, int d_i
   float acc[DGRAD_TMAX][4];
 #pragma unroll
   for (int t = 0; t < DGRAD_TMAX; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
-  for (int j0 = 0; j0 < d_out; j0 += rpc) {
-    const int nr = min(rpc, d_out - j0);
-    stage_rows<WS>(W + (size_t)j0 * ld, nr * ld, wbuf);
+  const int nblk = (d_out + rpc - 1) / rpc;     // blocks of rpc rows, two buffers: block c + 1 loads while block c is used
+  float* const buf0 = wbuf;
+  float* const buf1 = wbuf + rpc * ld;
+  stage_rows_async(W, min(rpc, d_out) * ld, buf0);
+  for (int c = 0; c < nblk; ++c) {
+    const int j0 = c * rpc, nr = min(rpc, d_out - j0);
+    if (c + 1 < nblk) {
+      stage_rows_async(W + (size_t)(j0 + rpc) * ld, min(rpc, d_out - j0 - rpc) * ld, (c & 1) ? buf0 : buf1);
+      cp_async_wait_but_one();
+    } else {
+      cp_async_wait_all();
+    }
     __syncthreads();
     const float* dp = dz + j0 * LDS + lane;
-    const float* wr = wbuf + 4 * warp;
+    const float* wr = ((c & 1) ? buf1 : buf0) + 4 * warp;
     switch (nt) {
       case 0: break;
       case 1: dgrad_rows_nt<1>(acc, dp, wr, nr, ld, 4 * nwarps); break;
@@ -496,11 +551,13 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
   __syncthreads();
 
   for (int l = 0; l < L; ++l) {
-    const int rpc = (spare / lay.ld[l]) & ~7;      // rows of this layer's matrix that fit in the shared memory left over
+    // columns of this layer's matrix per block: two blocks of (all outputs x kc) fit in the shared memory left over
+    const int kc = min(lay.ld[l], (spare / (2 * ((G.dims[l + 1] + 7) & ~7))) & ~3);
     if (ws) layer_forward<1>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                                 smem + sp.a_off[l + 1], G.act, l + 1 < L);
-    else if (rpc >= 16) layer_forward_chunked<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
-                                                           smem + sp.a_off[l + 1], G.act, l + 1 < L, wbuf, rpc);
+    else if (kc >= 16 && G.dims[l + 1] <= 8 * FWD_TMAX * (int)(blockDim.x >> 5))
+      layer_forward_chunked<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                                         smem + sp.a_off[l + 1], G.act, l + 1 < L, wbuf, kc);
     else layer_forward<COH ? 2 : 0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                               smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
@@ -547,10 +604,10 @@ __device__ void fwd_bwd_tile(const FedbGroup& G, int g, int tile, const float* p
     const float* dzc = smem + sp.dz_off[cur];
     layer_wgrad(dzc, smem + sp.a_off[l], lay.ld[l], G.dims[l + 1], rec + lay.w_off[l], rec + lay.b_off[l]);
     if (l > 0) {
-      const int rpc = spare / lay.ld[l];
+      const int rpc = min(G.dims[l + 1], spare / (2 * lay.ld[l]));   // rows per block, two blocks resident
       if (ws) layer_dgrad<1>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                                 smem + sp.dz_off[cur ^ 1], G.act);
-      else if (rpc >= 16 && (lay.ld[l] >> 2) <= DGRAD_TMAX * (int)(blockDim.x >> 5))
+      else if (rpc >= 8 && (lay.ld[l] >> 2) <= DGRAD_TMAX * (int)(blockDim.x >> 5))
         layer_dgrad_chunked<COH ? 2 : 0>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
                                          smem + sp.dz_off[cur ^ 1], G.act, wbuf, rpc);
       else layer_dgrad<COH ? 2 : 0>(P + lay.w_off[l], lay.ld[l], G.dims[l], G.dims[l + 1], dzc, smem + sp.a_off[l],
@@ -804,11 +861,12 @@ k_eval(const FedbGroup* __restrict__ groups, const FedbEvalJob* __restrict__ job
   load_tile(X, ldx, y, idx, J.idx_off + r0, nvalid, lay.ld[0], smem + sp.a_off[0], ylab);
   __syncthreads();
   for (int l = 0; l < L; ++l) {
-    const int rpc = ((smem_floats - sp.total_floats) / lay.ld[l]) & ~7;
+    const int kc = min(lay.ld[l], ((smem_floats - sp.total_floats) / (2 * ((G.dims[l + 1] + 7) & ~7))) & ~3);
     if (ws) layer_forward<true>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                                 smem + sp.a_off[l + 1], G.act, l + 1 < L);
-    else if (rpc >= 16) layer_forward_chunked<0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
-                                                 smem + sp.a_off[l + 1], G.act, l + 1 < L, smem + sp.total_floats, rpc);
+    else if (kc >= 16 && G.dims[l + 1] <= 8 * FWD_TMAX * (int)(blockDim.x >> 5))
+      layer_forward_chunked<0>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
+                               smem + sp.a_off[l + 1], G.act, l + 1 < L, smem + sp.total_floats, kc);
     else layer_forward<false>(P + lay.w_off[l], P + lay.b_off[l], lay.ld[l], G.dims[l + 1], smem + sp.a_off[l],
                               smem + sp.a_off[l + 1], G.act, l + 1 < L);
     __syncthreads();
