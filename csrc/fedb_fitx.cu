@@ -521,7 +521,10 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           tc::tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i], 0.f) * INV_WS, HMAX);
-          if (s.C <= 2) {
+          if (s.C == 1) {          // the scripts' sigmoid head: one output
+#pragma unroll
+            for (int i = 0; i < 16; ++i) z[0] = fmaf(v[i], W3s[(c0 + i) * 8], z[0]);
+          } else if (s.C == 2) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const float2 w = *reinterpret_cast<const float2*>(W3s + (c0 + i) * 8);
@@ -591,7 +594,7 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
             const float p = 1.f / (1.f + expf(-z[0]));
             const float eps = 1.1920929e-07f;   // SKB:273-274 clips probabilities at dtype eps
             const float pc = fminf(fmaxf(p, eps), 1.f - eps), yt = (float)label;
-            loss = -(yt * logf(pc) + (1.f - yt) * logf(1.f - pc));
+            if (part == 0) loss = -(yt * logf(pc) + (1.f - yt) * logf(1.f - pc));   // (only part 0 books the loss)
             dz3[0] = (p - yt) * DZS;
           }
         }
@@ -617,7 +620,10 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
           float v[16], d[16];
           tc::tmem_ld16(tl + TF_D2 + c0, v);
           tc::tmem_ld_wait();
-          if (s.C <= 2) {
+          if (s.C == 1) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) d[i] = dz3[0] * W3s[(c0 + i) * 8];
+          } else if (s.C == 2) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const float2 w = *reinterpret_cast<const float2*>(W3s + (c0 + i) * 8);
