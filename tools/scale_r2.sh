@@ -1,6 +1,6 @@
 # Round-2 scaling session on one 8-GPU box: headline config at 1/2/4/8 GPUs (driver protocol 20/5 and a longer 300/20 run),
 # 1 / 4 / 16 clients per GPU at 8 GPUs, the sklearn-avg and grid configs at 1 and 8 GPUs, the wide config at 1 and 8.
-#   bash tools/scale_r2.sh            (everything)        bash tools/scale_r2.sh quick   (headline only)
+#   bash tools/scale_r2.sh            (everything)        bash tools/scale_r2.sh quick   (headline only)      bash tools/scale_r2.sh final
 OUT=gpurun_out/scale_r2
 mkdir -p $OUT
 run() {  # run N name args...
@@ -11,8 +11,14 @@ run() {  # run N name args...
     timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2970$N bench.py --gpus $N "$@" 2> $OUT/$name.err | grep "^{" > $OUT/$name.json
   fi
 }
+if [ "$1" = "final" ]; then   # the short session: 300-step headline at every N, driver protocol at 8, grid at 8, sklearn at 4
+  for N in 1 2 4 8; do run $N income_${N} --steps 300 --warmup 20; done
+  run 8 income_8_driver --steps 20 --warmup 5
+  run 8 grid_8 --config grid --steps 2 --warmup 1; run 4 sklearn_4 --config sklearn
+else
 for N in 1 2 4 8; do run $N income_${N}_driver --steps 20 --warmup 5; run $N income_${N} --steps 300 --warmup 20; done
-if [ "$1" != "quick" ]; then
+fi
+if [ "$1" != "quick" ] && [ "$1" != "final" ]; then
   for C in 4 16; do run 8 income_8_cpg$C --steps 200 --warmup 10 --clients-per-gpu $C; run 1 income_1_cpg$C --steps 200 --warmup 10 --clients-per-gpu $C; done
   run 8 sklearn_8 --config sklearn; run 4 sklearn_4 --config sklearn
   run 8 grid_8 --config grid; run 4 grid_4 --config grid
