@@ -175,3 +175,31 @@ def test_early_stop_freezes_state(income):
     before = gpu.params.clone()
     gpu.run(4, unroll=4)
     assert torch.equal(before, gpu.params)
+
+
+def test_streamed_weights_are_bit_identical_to_global_reads(income_nomean, monkeypatch):
+    """Models whose weights do not fit next to the activations ((100, 400), (400, 200), (200, 400)): the layer loops that stream the
+    matrices through the left-over shared memory (column-blocked forward, row-blocked dgrad, cp.async double buffering, wide
+    weight-gradient mapping) against the plain loops that read them from global memory (FEDB200_SIMT_STREAM=0, read when the
+    tables are built): same parameters, moments and losses bit for bit after three epochs, and the same evaluation counts."""
+    def fit(stream):
+        monkeypatch.setenv("FEDB200_SIMT_STREAM", stream)
+        monkeypatch.setenv("FEDB200_FIT", "launches")
+        probs = [FedProblem.sklearn_like(14, make_shards("contiguous", 3000, 2), hidden=h, lr=0.004, init="sklearn_glorot")
+                 for h in ((100, 400), (400, 200), (200, 400), (50, 400))]
+        e = FedEngine(probs, income_nomean.X_train[:3000], income_nomean.y_train[:3000], income_nomean.X_test, income_nomean.y_test,
+                      device="cuda", max_rounds=2)
+        e.reset_fit_state()
+        e.enqueue_round_begin()
+        n = e.fit_local(max_iter=3)
+        e.enqueue_eval_local()
+        e.enqueue_aggregate()
+        torch.cuda.synchronize()
+        return e, n
+    a, na = fit("1")
+    b, nb = fit("0")
+    assert a.tb.smem_bytes > b.tb.smem_bytes            # the streaming launch asks for everything
+    assert np.array_equal(na, nb) and na.max() == 3
+    assert torch.equal(a.params, b.params) and torch.equal(a.m, b.m) and torch.equal(a.v, b.v)
+    assert torch.equal(a.last_loss, b.last_loss) and torch.equal(a.conf, b.conf)
+    assert torch.equal(a.global_, b.global_)
