@@ -158,3 +158,30 @@ def test_reference_faithful_round_against_the_reference_numbers(income_nomean):
         assert tuple(shape) == tuple(gshape)
         assert abs(std - gstd) <= 0.06 * gstd + 1e-12, (shape, std, gstd)
         assert abs(mean - gmean) <= 0.05 * max(gstd, abs(gmean)), (shape, mean, gmean)
+
+
+def test_warm_start_rounds_can_be_continued_call_by_call(income_nomean):
+    """run_sklearn_rounds(fresh=False) continues from the state the previous call left: 1 + 1 + 1 rounds, one call each (what
+    bench.py's end-to-end loop does), are the same three rounds as one call of 3."""
+    a = _sk_engine(income_nomean, max_iter=6)
+    ha = run_sklearn_rounds(a, rounds=3, policy="warm_start")
+    b = _sk_engine(income_nomean, max_iter=6)
+    for r in range(3):
+        hb = run_sklearn_rounds(b, rounds=1, policy="warm_start", fresh=(r == 0))
+    assert torch.equal(a.params, b.params) and torch.equal(a.global_, b.global_)
+    assert np.array_equal(ha["global"], hb["global"]) and np.array_equal(ha["n_iter"][-1], hb["n_iter"][-1])
+
+
+def test_simt_kernels_ask_for_all_shared_memory_when_weights_must_stream(monkeypatch):
+    """ops.kernels.simt_smem_bytes: models whose weights fit are sized exactly; models whose weights do not fit get the whole
+    227 KB (the layer loops stream the matrices through what the activations leave) unless FEDB200_SIMT_STREAM=0."""
+    from fedb200.ops.kernels import simt_smem_bytes
+    cap = 227 * 1024 - 64
+    small = simt_smem_bytes([14, 50, 400, 1], 3)
+    assert small < cap                                      # 14-50-400-1: activations + 86 KB of weights fit
+    assert simt_smem_bytes([14, 400, 200, 1], 3) == cap
+    monkeypatch.setenv("FEDB200_SIMT_STREAM", "0")
+    acts_only = simt_smem_bytes([14, 400, 200, 1], 3)
+    assert acts_only < cap and acts_only == (16 + 400 + 200 + 4 + 400 + 200) * 33 * 4 + 256
+    with pytest.raises(ValueError):
+        simt_smem_bytes([14, 4096, 4096, 2], 3)
