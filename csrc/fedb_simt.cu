@@ -758,10 +758,39 @@ __global__ void k_epoch_end(const FedbGroup* __restrict__ groups, int n_groups, 
                             int max_batches, int nblk, double tol, int n_iter_no_change, int max_iter,
                             int32_t* __restrict__ active, int32_t* __restrict__ epoch, int32_t* __restrict__ no_improve,
                             double* __restrict__ best_loss, double* __restrict__ last_loss) {
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n_groups || !active[g]) return;
-  epoch_end_group<false>(groups[g], g, batch_stats, max_batches, nblk, tol, n_iter_no_change, max_iter, active, epoch, no_improve,
-                         best_loss, last_loss);
+  // A WARP per client: the lanes fetch 128 block sums at a time (coalesced, all in flight) and every lane adds them in
+  // block order through shuffles — the same sequence of double additions as epoch_end_group, so the loss curve is
+  // bit-identical, without one thread's chain of ~860 dependent global loads (86 us per epoch for an 86 K-parameter model).
+  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (g >= n_groups || !active[g]) return;     // warp-uniform
+  const FedbGroup& G = groups[g];
+  const int n = G.n_rows;
+  const int bs = G.batch_size > 0 ? min(G.batch_size, n) : n;
+  const int nbatches = (n + bs - 1) / bs;
+  double accumulated = 0.0;
+  for (int b = 0; b < nbatches; ++b) {
+    const double* row = batch_stats + ((size_t)g * max_batches + b) * (2 + nblk);
+    double ss = 0.0;
+    for (int k0 = 0; k0 < nblk; k0 += 128) {
+      double v[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) v[c] = (k0 + 32 * c + lane < nblk) ? row[2 + k0 + 32 * c + lane] : 0.0;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int cnt = min(32, nblk - k0 - 32 * c);
+        for (int i = 0; i < cnt; ++i) ss += __shfl_sync(0xffffffffu, v[c], i);
+      }
+    }
+    accumulated += row[0] + 0.5 * (double)G.alpha * ss;
+  }
+  if (lane == 0) {
+    const double loss = accumulated / (double)n;
+    last_loss[g] = loss;
+    epoch[g] += 1;
+    if (loss > best_loss[g] - tol) no_improve[g] += 1; else no_improve[g] = 0;
+    if (loss < best_loss[g]) best_loss[g] = loss;
+    if (no_improve[g] > n_iter_no_change || epoch[g] >= max_iter) active[g] = 0;
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1086,7 +1115,7 @@ extern "C" int fedb_epoch_end(const FedbGroup* groups, int32_t n_groups, const d
                               int32_t* epoch, int32_t* no_improve, double* best_loss, double* last_loss,
                               void* stream) {
   const int nblk = (max_slab / 4 + NTHREADS - 1) / NTHREADS;
-  k_epoch_end<<<(n_groups + 127) / 128, 128, 0, (cudaStream_t)stream>>>(groups, n_groups, batch_stats, max_batches, nblk,
+  k_epoch_end<<<(n_groups + 3) / 4, 128, 0, (cudaStream_t)stream>>>(groups, n_groups, batch_stats, max_batches, nblk,
                                                                       tol, n_iter_no_change, max_iter, active, epoch,
                                                                       no_improve, best_loss, last_loss);
   FEDB_LAUNCH_OK();
