@@ -203,3 +203,26 @@ def test_streamed_weights_are_bit_identical_to_global_reads(income_nomean, monke
     assert torch.equal(a.params, b.params) and torch.equal(a.m, b.m) and torch.equal(a.v, b.v)
     assert torch.equal(a.last_loss, b.last_loss) and torch.equal(a.conf, b.conf)
     assert torch.equal(a.global_, b.global_)
+
+
+@pytest.mark.parametrize("hidden,act", [((300, 300, 60), "tanh"), ((520, 40), "relu"), ((96, 500), "logistic"), ((24, 510, 30), "relu")])
+def test_streamed_weights_odd_shapes_bitwise(income, monkeypatch, hidden, act):
+    """Shapes around the limits of the streamed loops (three hidden layers, other activations, 3 classes' worth of head rows,
+    d_out = 520 > 512 and ld = 520 > 512 that fall back to the plain loops layer by layer, partial last blocks): two full
+    rounds (train, eval, FedAvg) with Adam on the fp32 CUDA-core path, streamed against global reads, bit for bit."""
+    from fedb200.models.spec import MLPSpec
+
+    def run(stream):
+        monkeypatch.setenv("FEDB200_SIMT_STREAM", stream)
+        spec = MLPSpec.classifier(14, hidden, 2, "softmax_ce", act)
+        prob = FedProblem(spec, make_shards("contiguous", 900, 3), TrainHyper(batch_size=200, local_epochs=1), patience=0)
+        e = FedEngine([prob], income.X_train[:900], income.y_train[:900], income.X_test, income.y_test, device="cuda", max_rounds=4,
+                      precision="fp32")
+        h = e.run(2, unroll=1)
+        torch.cuda.synchronize()
+        return e, h
+    a, ha = run("1")
+    b, hb = run("0")
+    assert a.tb.smem_bytes >= b.tb.smem_bytes
+    assert torch.equal(a.params, b.params) and torch.equal(a.m, b.m) and torch.equal(a.v, b.v) and torch.equal(a.global_, b.global_)
+    assert np.array_equal(ha["global"], hb["global"]) and np.isfinite(ha["global"]).all()
