@@ -768,11 +768,12 @@ __global__ void __launch_bounds__(FT, 1) k_fit_tcx(FitXArgs a) {
         else if (G.opt == FEDB_OPT_ADAM_TORCH) update_all(std::integral_constant<int, FEDB_OPT_ADAM_TORCH>{});
         else update_all(std::integral_constant<int, FEDB_OPT_SGD>{});
         FSTAMP(19);
-        if (part == 2 && s.C > 2 && mine) {   // head weights of further classes (rare): state in global memory
+        if (part == 2 && s.C > 2) {   // head weights of further classes (rare): state in global memory
+          // (tcgen05.ld is warp-collective: every lane of the part-2 warps executes it, whether or not its unit is in the slice)
           float g3[16];
           tc::tmem_ld16(tl + TF_DW3, g3);
           tc::tmem_ld_wait();
-          for (int k = 2; k < s.C; ++k) {
+          for (int k = 2; k < s.C && mine; ++k) {
             const int e = s.w_off2 + k * s.ld2 + s.J0 + j;
             float w0 = Pg[e], mm = Mg[e], vv = use_v ? Vg[e] : 0.f, gk = 0.f;
 #pragma unroll

@@ -126,3 +126,35 @@ def test_mixed_engine_routes_each_client_to_its_kernel(income_nomean):
     assert len(out["results"]) == 6
     for r in out["results"]:
         assert 0.75 < r["global"][0] < 1.0 and np.all(r["n_iter"] >= 1), r["hidden_layer_sizes"]
+
+
+@pytest.mark.parametrize("n_classes,hidden", [(2, (50, 100)), (4, (40, 130)), (7, (33, 72))])
+def test_softmax_heads_match_the_cuda_core_path(income_nomean, monkeypatch, n_classes, hidden):
+    """The kernel's other head: softmax + cross-entropy with 2, 4 and 7 outputs (the partial-logit exchange, dW3 and db3 for every
+    class, the head rows beyond the first two whose optimizer state stays in global memory), momentum SGD so that rounding is all
+    that may differ.  Labels: the income label refined by quantiles of two features, so every class is populated."""
+    d = income_nomean
+    rows = 3000
+    X = d.X_train[:rows]
+    y = d.y_train[:rows].astype(np.int64)
+    if n_classes > 2:
+        y = (y + 2 * (X[:, 0] > np.median(X[:, 0])) + 4 * (X[:, 2] > np.median(X[:, 2]))) % n_classes
+    from fedb200.models.spec import MLPSpec
+    hyper = TrainHyper(opt="sgd", lr=0.02, momentum=0.9, alpha=1e-4, lr_step_size=0, lr_gamma=1.0, batch_size=200, max_iter=300)
+    mk = lambda: FedEngine([FedProblem(MLPSpec.classifier(d.n_features, hidden, n_classes, "softmax_ce"), contiguous(rows, 2), hyper,
+                                       weighting="uniform", metric_mode="pooled", patience=0, init="sklearn_glorot", init_seed=3,
+                                       init_per_client=False)], X, y.astype(d.y_train.dtype), device="cuda", max_rounds=2)
+    monkeypatch.setenv("FEDB200_FIT", "launches")
+    simt = mk()
+    monkeypatch.delenv("FEDB200_FIT")
+    tcx = mk()
+    assert simt._fit_tc_mask() is None and tcx._fit_tc_mask() is not None and bool(tcx._fit_tc_mask().all())
+    for e in (simt, tcx):
+        n = _fit_epochs(e, 2, True)
+        assert n.tolist() == [2, 2]
+    np.testing.assert_allclose(tcx.last_loss.cpu().numpy(), simt.last_loss.cpu().numpy(), rtol=5e-5)
+    assert float(simt.last_loss.min()) > 0.05
+    dd = (tcx.params - simt.params).abs() / simt.params.abs().max()
+    assert float(dd.quantile(0.97)) <= 1e-6 and float(dd.max()) <= 2e-3
+    pad = ~simt.problems[0].spec.param_mask().repeat(2)
+    assert float(tcx.params.cpu()[pad].abs().max()) == 0.0
