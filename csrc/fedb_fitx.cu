@@ -150,12 +150,6 @@ __device__ __forceinline__ void put_w1f(uint8_t* sm, int i, int col, const float
   *reinterpret_cast<uint2*>(sm + FX_W1 + tc::panel_off(i, col)) = make_uint2(h0, h1);
   *reinterpret_cast<uint2*>(sm + FX_W1 + tc::panel_off(i, 16 + col)) = make_uint2(l0, l1);
 }
-__device__ __forceinline__ void put_b2f(uint8_t* sm, int j, float b) {
-  b *= WS;
-  const __half h = __float2half_rn(b);
-  *reinterpret_cast<__half*>(sm + FX_W2 + tc::panel_off(j, 63)) = h;
-  *reinterpret_cast<__half*>(sm + FX_W2L + tc::panel_off(j, 63)) = __float2half_rn(b - __half2float(h));
-}
 
 // All MMAs are issued by one thread.  Inside a group of three products the two small cross terms go first.
 struct IssuerF {
