@@ -172,7 +172,11 @@ class FedEngine:
         self.tb = K.DeviceTables.build(groups, feds, self.device)
         self.idx = torch.from_numpy(self.idx_host).to(self.device)
         # training tiles
-        tiles = [(gi, t) for gi in range(G) for t in range(int(groups[gi]["max_tiles"]))]
+        # (largest models first: CTAs are dispatched in list order, and a 32-row tile of an 86 K-parameter model runs ~50x longer
+        #  than one of a 1 K-parameter model; with the long tiles at the END of the list a packed grid's launch ended with a
+        #  wave of them on a mostly idle GPU)
+        order = sorted(range(G), key=lambda gi: -int(groups[gi]["slab_size"]))
+        tiles = [(gi, t) for gi in order for t in range(int(groups[gi]["max_tiles"]))]
         self.train_tiles_np = np.array(tiles, dtype=np.int32).view(nat.TILE_DTYPE).reshape(-1)
         self.train_tiles = K.upload_table(self.train_tiles_np, self.device)
         self.n_batches = max(
@@ -268,7 +272,8 @@ class FedEngine:
     def enqueue_local_step(self, batch: int = 0, idx: Optional[torch.Tensor] = None, stats: bool = False) -> None:
         """One optimizer step of every active client on minibatch ``batch`` (2 launches)."""
         idx = self.idx if idx is None else idx
-        K.fwd_bwd(self.tb, self.train_tiles, len(self.train_tiles_np), self.params, self.X, self.y, idx, batch,
+        tiles, n_tiles = getattr(self, "_step_tiles", None) or (self.train_tiles, len(self.train_tiles_np))
+        K.fwd_bwd(self.tb, tiles, n_tiles, self.params, self.X, self.y, idx, batch,
                   self.scratch, self.step, self.active, self.fed_state)
         K.reduce_opt(self.tb, self.params, self.m, self.v, self.scratch, batch, self.step, self.active, self.fed_state,
                      self.loss, self.batch_stats if stats else None, self.n_batches)
@@ -512,16 +517,43 @@ class FedEngine:
             # under 1 % - the 576 CTAs hold every SM while they run - so the two parts simply follow each other.)
             h = self.problems[0].hyper
             act_tc = torch.from_numpy(tc_mask.astype(np.int32)).to(self.device)
+            # (the kernel clears a client's flag in act_tc when its fit stops, so the complement for the CUDA-core clients is
+            #  built from the host mask: taken from act_tc afterwards it re-activated every converged tensor-core client for
+            #  one more epoch on the CUDA cores)
+            act_cc = torch.from_numpy((~tc_mask).astype(np.int32)).to(self.device)
             K.fit_tcx(self.tb, self.params, self.m, self.v, self.X, self.y, self.idx, self.idx_epoch, self.step, act_tc, self.fed_state,
                       self.epoch, self.no_improve, self.best_loss, self.last_loss, self.loss, h.tol, h.n_iter_no_change, h.max_iter,
                       max_iter, shuffle, self.seed + 0x5EED)
             if bool(tc_mask.all()):
                 self.active.fill_(1)
                 return self.epoch.cpu().numpy().copy()
-            self.active.copy_(1 - act_tc)
-        self._fit_cuda_cores(max_iter, shuffle, check_every)
+            self.active.copy_(act_cc)
+        # the fit's launches carry only the tiles they need: none of the clients the tensor-core kernel took, and per client
+        # the tiles of one mini-batch (the general list reserves at least 8), largest models first
+        self._step_tiles = self._fit_tile_list(tc_mask)
+        try:
+            self._fit_cuda_cores(max_iter, shuffle, check_every)
+        finally:
+            self._step_tiles = None
         self.active.fill_(1)
         return self.epoch.cpu().numpy().copy()
+
+    def _fit_tile_list(self, tc_mask: Optional[np.ndarray]):
+        if getattr(self, "_fit_tiles", None) is None:
+            groups = self.tb.groups
+            order = sorted(range(len(groups)), key=lambda gi: -int(groups[gi]["slab_size"]))
+            tiles = []
+            for gi in order:
+                if tc_mask is not None and tc_mask[gi]:
+                    continue
+                n, bs = int(groups[gi]["n_rows"]), int(groups[gi]["batch_size"])
+                rows = min(bs, n) if bs > 0 else n
+                tiles += [(gi, t) for t in range(min(int(groups[gi]["max_tiles"]), -(-rows // nat.TILE_ROWS)))]
+            if not tiles:
+                tiles = [(0, 0)]
+            arr = np.array(tiles, dtype=np.int32).view(nat.TILE_DTYPE).reshape(-1)
+            self._fit_tiles = (K.upload_table(arr, self.device), len(arr))
+        return self._fit_tiles
 
     def _fit_cuda_cores(self, max_iter: int, shuffle: bool, check_every: int) -> None:
         """The fit of the clients whose ``active`` flag is set, on the fp32 CUDA-core kernels."""
