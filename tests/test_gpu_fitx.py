@@ -158,3 +158,30 @@ def test_softmax_heads_match_the_cuda_core_path(income_nomean, monkeypatch, n_cl
     assert float(dd.quantile(0.97)) <= 1e-6 and float(dd.max()) <= 2e-3
     pad = ~simt.problems[0].spec.param_mask().repeat(2)
     assert float(tcx.params.cpu()[pad].abs().max()) == 0.0
+
+
+def test_tensor_core_clients_are_left_alone_by_the_cuda_core_epochs(income_nomean):
+    """A packed engine with one federation the tensor-core kernel takes ((50, 100)) and one it does not ((100,)): the first
+    federation's clients must come out of fit_local exactly as they do from an engine that holds only them — same epochs, same
+    parameters and moments bit for bit.  (The complement mask for the CUDA-core clients was once derived from the flags the fit
+    kernel clears when a client stops, which re-activated every converged tensor-core client for one more CUDA-core epoch.)"""
+    d = income_nomean
+    rows = 2000
+    shards = contiguous(rows, 2)
+    tc = lambda: FedProblem.sklearn_like(d.n_features, shards, hidden=(50, 100), lr=0.004)
+    cc = lambda: FedProblem.sklearn_like(d.n_features, shards, hidden=(100,), lr=0.01)
+    mk = lambda probs: FedEngine(probs, d.X_train[:rows], d.y_train[:rows], device="cuda", max_rounds=2)
+    mixed, pure = mk([tc(), cc()]), mk([tc()])
+    assert mixed._fit_tc_mask().tolist() == [True, True, False, False] and pure._fit_tc_mask().tolist() == [True, True]
+    out = []
+    for e in (mixed, pure):
+        e.reset_fit_state()
+        e.enqueue_round_begin()
+        out.append(e.fit_local(max_iter=60))
+        torch.cuda.synchronize()
+    assert out[0][:2].tolist() == out[1].tolist() and out[0][2:].min() >= 1
+    n = 2 * pure.problems[0].spec.slab_size
+    o = int(mixed.tb.groups[0]["slab_off"])
+    assert int(pure.tb.groups[0]["slab_off"]) == 0
+    assert torch.equal(mixed.params[o:o + n], pure.params[:n]) and torch.equal(mixed.m[o:o + n], pure.m[:n])
+    assert torch.equal(mixed.epoch[:2], pure.epoch) and torch.equal(mixed.step[:2], pure.step)
