@@ -185,3 +185,31 @@ def test_simt_kernels_ask_for_all_shared_memory_when_weights_must_stream(monkeyp
     assert acts_only < cap and acts_only == (16 + 400 + 200 + 4 + 400 + 200) * 33 * 4 + 256
     with pytest.raises(ValueError):
         simt_smem_bytes([14, 4096, 4096, 2], 3)
+
+
+def test_fit_tile_list_is_pruned_and_ordered(income_nomean):
+    """FedEngine._fit_tile_list: one mini-batch's tiles per client (the general list reserves at least 8), largest models first,
+    clients the tensor-core fit kernel takes left out."""
+    from fedb200.ops import _native as nat
+    shards = make_shards("contiguous", 600, 2)
+    probs = [FedProblem.sklearn_like(14, shards, hidden=h, max_iter=3) for h in ((8,), (40, 30), (16,))]
+    eng = FedEngine(probs, income_nomean.X_train[:600], income_nomean.y_train[:600], device="cpu", max_rounds=2)
+    assert len(eng.train_tiles_np) == 6 * 8
+    # heavy first in the general list too
+    assert [int(o) for o in eng.train_tiles_np["owner"][:16:8]] == [2, 3]
+    t, n = eng._fit_tile_list(None)
+    tiles = t.numpy().view(nat.TILE_DTYPE).reshape(-1)
+    need = -(-200 // nat.TILE_ROWS)                      # mini-batches of 200 rows
+    assert n == 6 * need and sorted(set(int(x) for x in tiles["tile"])) == list(range(need))
+    assert [int(o) for o in tiles["owner"][::need]] == [2, 3, 4, 5, 0, 1]
+    eng._fit_tiles = None
+    t, n = eng._fit_tile_list(np.array([False, False, True, True, False, False]))
+    tiles = t.numpy().view(nat.TILE_DTYPE).reshape(-1)
+    assert n == 4 * need and set(int(o) for o in tiles["owner"]) == {0, 1, 4, 5}
+    # and a fit through the pruned list is the fit through the general one
+    a = _sk_engine(income_nomean, max_iter=5)
+    na = a.fit_local()
+    b = _sk_engine(income_nomean, max_iter=5)
+    b._fit_tile_list = lambda mask: (b.train_tiles, len(b.train_tiles_np))
+    nb = b.fit_local()
+    assert np.array_equal(na, nb) and torch.equal(a.params, b.params)
